@@ -1,0 +1,223 @@
+// =====================================================================================
+// device_math.cuh -- scalar arithmetic of the neural-SDF renderer, sm_100a device side.
+//
+// Every function states the reference lines it replaces (paths relative to the
+// reference repo root).  The translation unit is compiled with -fmad=false, so the ONLY
+// fused multiply-adds are the explicit fmaf()/fma() below; their placement is the
+// "arithmetic contract" of DESIGN.md (the contraction pattern nvcc -fmad=true produces
+// for the reference's expressions), which makes every result reproducible bit for bit.
+// =====================================================================================
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace nsdf {
+
+struct f3 { float x, y, z; };
+
+// helper_math.h:1248-1253 dot(float3,float3): y*y first, then fma x, then fma z.
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.x, b.x, a.y * b.y)); }
+
+// helper_math.h:1309-1313 normalize = v * rsqrtf(dot(v,v)).  MUFU.RSQ is replaced by the
+// correctly rounded 1/sqrt (the header's own host fallback, helper_math.h:62-65).
+__device__ __forceinline__ float rsqrt_det(float x) { return __fdiv_rn(1.0f, __fsqrt_rn(x)); }
+__device__ __forceinline__ f3 normalize3(f3 v) {
+    const float r = rsqrt_det(dot3(v, v));
+    return f3{v.x * r, v.y * r, v.z * r};
+}
+
+// __saturatef with NaN -> 0 (volumeRender_kernel.cu:140,146,268-271)
+__device__ __forceinline__ float saturate_det(float x) {
+    if (!(x > 0.0f)) return 0.0f;
+    return x > 1.0f ? 1.0f : x;
+}
+
+// tanh of the network output (volumeRender_kernel.cu:229; simpleInfer.cpp:109).  libdevice
+// tanhf goes through MUFU.EX2/RCP; this polynomial/Cody-Waite form is < 1.5 ulp and uses only
+// IEEE operations.
+__device__ __forceinline__ float tanhf_det(float x) {
+    const float ax = fabsf(x);
+    if (ax < 0.55f) {
+        const float x2 = x * x;
+        float p = -0x1.9b14e4p-8f;
+        p = fmaf(p, x2, 0x1.59370cp-6f);
+        p = fmaf(p, x2, -0x1.b9278cp-5f);
+        p = fmaf(p, x2, 0x1.110d1ep-3f);
+        p = fmaf(p, x2, -0x1.55554ap-2f);
+        return fmaf(x * x2, p, x);
+    }
+    float r;
+    if (ax > 9.125f) {
+        r = 1.0f;
+    } else {
+        const float y = ax + ax;
+        const float n = rintf(y * 0x1.715476p+0f);
+        float t = fmaf(n, -0x1.62e400p-1f, y);
+        t = fmaf(n, -0x1.7f7d1cp-20f, t);
+        float e = 0x1.a01a02p-13f;
+        e = fmaf(e, t, 0x1.6c16c2p-10f);
+        e = fmaf(e, t, 0x1.111112p-7f);
+        e = fmaf(e, t, 0x1.555556p-5f);
+        e = fmaf(e, t, 0x1.555556p-3f);
+        e = fmaf(e, t, 0.5f);
+        e = fmaf(e, t, 1.0f);
+        e = fmaf(e, t, 1.0f);
+        const float s = __uint_as_float((uint32_t)((int)n + 127) << 23);
+        e = e * s;
+        r = 1.0f - __fdiv_rn(2.0f, e + 1.0f);
+    }
+    if (ax != ax) return x + x;
+    return copysignf(r, x);
+}
+
+// sdfOpSmoothUnion (volumeRender_kernel.cu:144-149) with its double promotions.
+__device__ __forceinline__ float smooth_union(float d1, float d2, float k) {
+    const float diff = d2 - d1;
+    const double hd = __dadd_rn(__ddiv_rn(__dmul_rn((double)diff, 0.5), (double)k), 0.5);
+    const float h = saturate_det((float)hd);
+    const double omh = __dsub_rn(1.0, (double)h);
+    const float d1h = d1 * h;
+    const float mix = (float)fma(omh, (double)d2, (double)d1h);
+    const float kh = k * h;
+    return (float)fma(-omh, (double)kh, (double)mix);
+}
+
+// manySphere(p, nSDF, true) (volumeRender_kernel.cu:176-196): what sceneSDF (:217-222)
+// evaluates at the reference's HEAD.
+__device__ __forceinline__ float many_sphere_union(f3 p, float nsdf, int frame) {
+    float s = nsdf;
+    float cx = p.x;
+    float cy = (float)__dsub_rn((double)p.y, 0.6);
+    const double zoff = __dadd_rn(-0.7, __ddiv_rn(__dmul_rn((double)(frame * 2), 0.7), 360.0));
+    const float cz = (float)__dadd_rn((double)p.z, zoff);
+    const float zz = cz * cz;
+#pragma unroll 1
+    for (int i = 0; i < 9; ++i) {
+        if (i % 3 == 0) {
+            cy = (float)__dadd_rn((double)cy, 0.4);
+            cx = p.x + 0.5f;
+        }
+        const float len2 = zz + fmaf(cx, cx, cy * cy);
+        const float d = __fsqrt_rn(len2) + (-0.1f);
+        s = smooth_union(s, d, 0.01f);
+        cx = (float)__dsub_rn((double)cx, 0.4);
+    }
+    return s;
+}
+
+enum { SCENE_TANH = 0, SCENE_MANYSPHERE = 1 };
+
+// sceneSDF (volumeRender_kernel.cu:217-230): scene 1 = HEAD, scene 0 = `tanh(nSDF)` (:229).
+__device__ __forceinline__ float scene_sdf(int scene, f3 p, float nsdf, int frame) {
+    if (scene == SCENE_MANYSPHERE) return many_sphere_union(p, nsdf, frame);
+    return tanhf_det(nsdf);
+}
+
+#define NSDF_NORMAL_EPSILON 0.00001f     // volumeRender_kernel.cu:59
+#define NSDF_MARCHING_EPSILON 0.000001f  // volumeRender_kernel.cu:60
+
+// tetrahedronVerts (volumeRender_kernel.cu:38-43) as sign bits: bit i of TET_NEG_{X,Y,Z}
+// set <=> component of vertex i is -1.
+#define NSDF_TET_NEG_X 0x6u  // (+,-,-,+)
+#define NSDF_TET_NEG_Y 0x3u  // (-,-,+,+)
+#define NSDF_TET_NEG_Z 0x5u  // (-,+,-,+)
+__device__ __forceinline__ f3 tet_vertex(int i) {
+    return f3{((NSDF_TET_NEG_X >> i) & 1u) ? -1.0f : 1.0f, ((NSDF_TET_NEG_Y >> i) & 1u) ? -1.0f : 1.0f,
+              ((NSDF_TET_NEG_Z >> i) & 1u) ? -1.0f : 1.0f};
+}
+
+// float -> int/uint conversion with the semantics of cvt.rzi (NaN -> 0, saturating); this is
+// what the reference's device code gets for int(f) / uint(f) (:273, :398-399).
+__device__ __forceinline__ int f2i_rz(float f) { return __float2int_rz(f); }
+__device__ __forceinline__ uint32_t f2u_rz(float f) { return __float2uint_rz(f); }
+
+struct Camera {
+    float inv_view[12];  // c_invViewMatrix rows 0..2 (volumeRender_kernel.cu:31)
+    float normal[16];    // c_normalMatrix (:32)
+    int frame;           // c_frameNumber (:35)
+};
+
+struct RayInit { f3 o, d, p; float tfar; bool hit; };
+
+// initMarcher (volumeRender_kernel.cu:293-358) + intersectSphere (:200-215), sphere (0, 1.2).
+__device__ __forceinline__ RayInit init_ray(const Camera& c, int x, int y, int W, int H) {
+    RayInit r;
+    const float u = fmaf(__fdiv_rn((float)x, (float)W), 2.0f, -1.0f);
+    const float v = fmaf(__fdiv_rn((float)y, (float)H), 2.0f, -1.0f);
+    const float* M = c.inv_view;
+    r.o = f3{M[3] + fmaf(M[2], 0.0f, fmaf(M[0], 0.0f, M[1] * 0.0f)),
+             M[7] + fmaf(M[6], 0.0f, fmaf(M[4], 0.0f, M[5] * 0.0f)),
+             M[11] + fmaf(M[10], 0.0f, fmaf(M[8], 0.0f, M[9] * 0.0f))};
+    const float rs = rsqrt_det(fmaf(u, u, v * v) + 4.0f);
+    const f3 d0{u * rs, v * rs, rs * -2.0f};
+    r.d = f3{dot3(d0, f3{M[0], M[1], M[2]}), dot3(d0, f3{M[4], M[5], M[6]}), dot3(d0, f3{M[8], M[9], M[10]})};
+    const float a = dot3(r.d, r.d);
+    const float qd = dot3(r.o, r.d);
+    const float b = qd + qd;
+    const float cc = dot3(r.o, r.o) + (-1.4400000572204589844f);
+    const float disc = fmaf(b, b, -(cc * (a * 4.0f)));
+    r.hit = disc > 0.0f;
+    r.tfar = 0.0f;
+    r.p = r.o;
+    if (!r.hit) return r;
+    const float sq = __fsqrt_rn(disc);
+    const double two_a = __dadd_rn((double)a, (double)a);
+    float tnear = (float)__ddiv_rn((double)(-b - sq), two_a);
+    r.tfar = (float)__ddiv_rn((double)(sq - b), two_a);
+    if (tnear < 0.0f) tnear = 0.0f;
+    r.p = f3{fmaf(r.d.x, tnear, r.o.x), fmaf(r.d.y, tnear, r.o.y), fmaf(r.d.z, tnear, r.o.z)};
+    return r;
+}
+
+// rgbaFloatToInt (volumeRender_kernel.cu:266-274)
+__device__ __forceinline__ uint32_t rgba_float_to_int(float r, float g, float b, float a) {
+    r = saturate_det(r); g = saturate_det(g); b = saturate_det(b); a = saturate_det(a);
+    return (f2u_rz(a * 255.0f) << 24) | (f2u_rz(b * 255.0f) << 16) | (f2u_rz(g * 255.0f) << 8) | f2u_rz(r * 255.0f);
+}
+
+// facingColor (volumeRender_kernel.cu:380-384)
+__device__ __forceinline__ uint32_t facing_color(f3 n, f3 ray) {
+    float t = ray.x * n.x;
+    t = fmaf(-ray.y, n.y, -t);
+    t = fmaf(-ray.z, n.z, t);
+    double rd = (double)t;
+    rd = (rd > 0.0) ? rd : 0.0;
+    const float ratio = (float)rd;
+    return rgba_float_to_int(ratio, ratio, ratio, 1.0f);
+}
+
+// matCapColor (volumeRender_kernel.cu:387-413): nearest texel, truncating, texel returned as is.
+__device__ __forceinline__ uint32_t matcap_color(const Camera& c, f3 n, const uint32_t* __restrict__ matcap, int mw,
+                                                 int mh) {
+    const float* N = c.normal;
+    float e[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const float* row = N + 4 * i;
+        float t = n.y * row[1];
+        t = fmaf(n.x, row[0], t);
+        t = fmaf(n.z, row[2], t);
+        t = fmaf(row[3], 0.0f, t);
+        e[i] = t;
+    }
+    const f3 ne = normalize3(f3{e[0], e[1], e[2]});
+    const float fu = (float)fma((double)ne.x, 0.5, 0.5);
+    const float fv = (float)fma((double)ne.y, 0.5, 0.5);
+    const int ux = f2i_rz(fu * (float)(mw - 1));
+    const int uy = f2i_rz(fv * (float)(mh - 1));
+    const int index = (int)((uint32_t)uy * (uint32_t)mw + (uint32_t)ux);
+    if (index < 0 || index >= mw * mh) return 0u;  // :403-407 (the upper bound is our guard; the reference would fault)
+    return __ldg(matcap + index);
+}
+
+// surfaceNormal (volumeRender_kernel.cu:361-377): p0+p1+p2+p3 as contracted by nvcc.
+__device__ __forceinline__ f3 tet_normal(const float (&s)[4]) {
+    f3 nn;
+    const f3 t0 = tet_vertex(0), t1 = tet_vertex(1), t2 = tet_vertex(2), t3 = tet_vertex(3);
+    nn.x = fmaf(t3.x, s[3], fmaf(t2.x, s[2], fmaf(t0.x, s[0], t1.x * s[1])));
+    nn.y = fmaf(t3.y, s[3], fmaf(t2.y, s[2], fmaf(t0.y, s[0], t1.y * s[1])));
+    nn.z = fmaf(t3.z, s[3], fmaf(t2.z, s[2], fmaf(t0.z, s[0], t1.z * s[1])));
+    return normalize3(nn);
+}
+
+}  // namespace nsdf

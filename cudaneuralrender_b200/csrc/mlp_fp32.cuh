@@ -1,0 +1,231 @@
+// =====================================================================================
+// mlp_fp32.cuh -- fused all-layer SDF-MLP evaluators, fp32, reference arithmetic order.
+//
+// Replaces the nine CUTLASS SIMT GemmBatched launches of one NeuralNetwork::forward
+// (src/neuralNetwork.cpp:54-63 -> src/layers/denseLayer.cu:126-176) by ONE kernel: the
+// whole network's weights are staged once per CTA into shared memory with a TMA bulk copy
+// (cp.async.bulk + mbarrier) and activations never leave registers / shared memory.
+//
+// Arithmetic (identical to the CUTLASS 2.0 SIMT kernels the reference instantiates, so the
+// results are the reference's bit for bit): per output, one accumulator starting at 0,
+// acc = fma(W[o][k], a[k], acc) for k ascending; z = acc + bias; ReLU on hidden layers.
+//
+// Two evaluators over the same packed weights:
+//   * mlp32_eval_thread<P>  one thread = P points, weights read as warp-uniform LDS.128
+//                           (throughput form: 64 FFMA per LDS.128 at P = 2)
+//   * mlp32_eval_warp<R>    one warp = R points, lane = neuron (latency form: one layer is a
+//                           32-deep FFMA chain instead of 1024 FFMA issue slots)
+// =====================================================================================
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace nsdf {
+
+// ---- packed "fused blob" (floats) ---------------------------------------------------------
+//   [0,128)    Wt0[k][o], k < 4 (rows >= in0 are zero), o < 32
+//   [128,160)  b0[o]
+//   160 + l*1056 : hidden layer l (l < n_sq):  Wt[k][o] (1024) then b[o] (32)
+//   160 + n_sq*1056 : last layer w[k] (32), b (1), 3 pad
+constexpr int FUSED_L0_FLOATS = 160;
+constexpr int FUSED_SQ_FLOATS = 1056;
+constexpr int FUSED_LAST_FLOATS = 36;
+constexpr int FUSED_MAX_SQ = 15;
+__host__ __device__ constexpr int fused_blob_floats(int n_sq) {
+    return FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS + FUSED_LAST_FLOATS;
+}
+
+// ---- TMA bulk staging -----------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D TMA: global -> shared::cta, completion on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void tma_bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+// Stages `bytes` (multiple of 16) of the fused blob into shared memory.  Must be called by all
+// threads of the CTA; returns after the data is visible to every thread.
+__device__ __forceinline__ void stage_weights(float* s_dst, const float* __restrict__ g_blob, uint32_t bytes,
+                                              uint64_t* s_bar) {
+    if (threadIdx.x == 0) {
+        mbar_init(s_bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(s_bar, bytes);
+        // chunks of <= 32 KB keep each bulk request small enough for any smem carve-out
+        uint32_t off = 0;
+        while (off < bytes) {
+            const uint32_t n = (bytes - off) < 32768u ? (bytes - off) : 32768u;
+            tma_bulk_g2s((char*)s_dst + off, (const char*)g_blob + off, n, s_bar);
+            off += n;
+        }
+    }
+    mbar_wait(s_bar, 0);
+}
+
+__device__ __forceinline__ float relu_det(float v) { return (v > 0.0f) ? v : 0.0f; }
+
+// ---- thread-per-point evaluator ---------------------------------------------------------------
+// x[p][0..2] -> y[p].  sw = fused blob in shared memory.  All weight reads are warp-uniform
+// 16-byte loads; with -fmad=false the only FMAs are the explicit ones, in reference order.
+template <int P>
+__device__ __forceinline__ void mlp32_eval_thread(const float* __restrict__ sw, int n_sq, const float (&x)[P][3],
+                                                  float (&y)[P]) {
+    float a[P][32];
+    {
+        const float4* L0 = reinterpret_cast<const float4*>(sw);
+#pragma unroll
+        for (int oc = 0; oc < 8; ++oc) {
+            const float4 w0 = L0[oc], w1 = L0[8 + oc], w2 = L0[16 + oc], bb = L0[32 + oc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                a[p][4 * oc + 0] = relu_det(fmaf(w2.x, x[p][2], fmaf(w1.x, x[p][1], fmaf(w0.x, x[p][0], 0.0f))) + bb.x);
+                a[p][4 * oc + 1] = relu_det(fmaf(w2.y, x[p][2], fmaf(w1.y, x[p][1], fmaf(w0.y, x[p][0], 0.0f))) + bb.y);
+                a[p][4 * oc + 2] = relu_det(fmaf(w2.z, x[p][2], fmaf(w1.z, x[p][1], fmaf(w0.z, x[p][0], 0.0f))) + bb.z);
+                a[p][4 * oc + 3] = relu_det(fmaf(w2.w, x[p][2], fmaf(w1.w, x[p][1], fmaf(w0.w, x[p][0], 0.0f))) + bb.w);
+            }
+        }
+    }
+#pragma unroll 1
+    for (int l = 0; l < n_sq; ++l) {
+        const float4* Wt = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS);
+        float z[P][32];
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+#pragma unroll
+            for (int o = 0; o < 32; ++o) z[p][o] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+#pragma unroll
+            for (int oc = 0; oc < 8; ++oc) {
+                const float4 w = Wt[k * 8 + oc];
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    z[p][4 * oc + 0] = fmaf(w.x, a[p][k], z[p][4 * oc + 0]);
+                    z[p][4 * oc + 1] = fmaf(w.y, a[p][k], z[p][4 * oc + 1]);
+                    z[p][4 * oc + 2] = fmaf(w.z, a[p][k], z[p][4 * oc + 2]);
+                    z[p][4 * oc + 3] = fmaf(w.w, a[p][k], z[p][4 * oc + 3]);
+                }
+            }
+        }
+#pragma unroll
+        for (int oc = 0; oc < 8; ++oc) {
+            const float4 bb = Wt[256 + oc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                a[p][4 * oc + 0] = relu_det(z[p][4 * oc + 0] + bb.x);
+                a[p][4 * oc + 1] = relu_det(z[p][4 * oc + 1] + bb.y);
+                a[p][4 * oc + 2] = relu_det(z[p][4 * oc + 2] + bb.z);
+                a[p][4 * oc + 3] = relu_det(z[p][4 * oc + 3] + bb.w);
+            }
+        }
+    }
+    {
+        const float4* LL = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS);
+        float acc[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) acc[p] = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const float4 w = LL[kc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                acc[p] = fmaf(w.x, a[p][4 * kc + 0], acc[p]);
+                acc[p] = fmaf(w.y, a[p][4 * kc + 1], acc[p]);
+                acc[p] = fmaf(w.z, a[p][4 * kc + 2], acc[p]);
+                acc[p] = fmaf(w.w, a[p][4 * kc + 3], acc[p]);
+            }
+        }
+        const float bl = sw[FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS + 32];
+#pragma unroll
+        for (int p = 0; p < P; ++p) y[p] = acc[p] + bl;
+    }
+}
+
+// ---- warp-cooperative evaluator ------------------------------------------------------------------
+// One warp evaluates R points; lane = neuron.  x must be warp-uniform.  abuf: per-warp scratch of
+// 2*R*WARP_ACT_STRIDE floats in shared memory.  y is returned warp-uniform.  Same bits as above.
+constexpr int WARP_ACT_STRIDE = 36;  // 32 + 4 pad: rows start 4 banks apart (last-layer reads)
+template <int R>
+__device__ __forceinline__ void mlp32_eval_warp(const float* __restrict__ sw, int n_sq, float* __restrict__ abuf,
+                                                const float (&x)[R][3], float (&y)[R], int lane) {
+    float* cur = abuf;
+    float* nxt = abuf + R * WARP_ACT_STRIDE;
+    {
+        const float w0 = sw[lane], w1 = sw[32 + lane], w2 = sw[64 + lane], bb = sw[128 + lane];
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            cur[r * WARP_ACT_STRIDE + lane] =
+                relu_det(fmaf(w2, x[r][2], fmaf(w1, x[r][1], fmaf(w0, x[r][0], 0.0f))) + bb);
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int l = 0; l < n_sq; ++l) {
+        const float* Wt = sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS;
+        float z[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) z[r] = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const float wa = Wt[(4 * kc + 0) * 32 + lane], wb = Wt[(4 * kc + 1) * 32 + lane],
+                        wc = Wt[(4 * kc + 2) * 32 + lane], wd = Wt[(4 * kc + 3) * 32 + lane];
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                const float4 av = *reinterpret_cast<const float4*>(cur + r * WARP_ACT_STRIDE + 4 * kc);
+                z[r] = fmaf(wa, av.x, z[r]);
+                z[r] = fmaf(wb, av.y, z[r]);
+                z[r] = fmaf(wc, av.z, z[r]);
+                z[r] = fmaf(wd, av.w, z[r]);
+            }
+        }
+        const float bb = Wt[1024 + lane];
+#pragma unroll
+        for (int r = 0; r < R; ++r) nxt[r * WARP_ACT_STRIDE + lane] = relu_det(z[r] + bb);
+        __syncwarp();
+        float* t = cur; cur = nxt; nxt = t;
+    }
+    float out = 0.0f;
+    {
+        const float* LL = sw + FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS;
+        const int r = lane < R ? lane : 0;
+        float acc = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const float4 w = *reinterpret_cast<const float4*>(LL + 4 * kc);
+            const float4 av = *reinterpret_cast<const float4*>(cur + r * WARP_ACT_STRIDE + 4 * kc);
+            acc = fmaf(w.x, av.x, acc);
+            acc = fmaf(w.y, av.y, acc);
+            acc = fmaf(w.z, av.z, acc);
+            acc = fmaf(w.w, av.w, acc);
+        }
+        out = acc + LL[32];
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) y[r] = __shfl_sync(0xffffffffu, out, r);
+    __syncwarp();   // abuf may be rewritten by the caller's next evaluation
+}
+
+}  // namespace nsdf

@@ -1,0 +1,56 @@
+// Internal declarations shared by the translation units of libnsdf.so (not part of the ABI).
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/nsdf.h"
+
+struct nsdf_model {
+    int device = 0;
+    int n_layers = 0;
+    std::vector<int> in, out, act;
+    std::vector<float> h_params;          // packed: per layer W[out][in] then b[out]
+    std::vector<size_t> w_off, b_off;     // offsets (floats) into the packed array
+    float* d_params = nullptr;            // same layout on the device (per-layer operators)
+    bool fused = false;                   // 3 -> 32 x k -> 1, ReLU hidden, linear last
+    int n_sq = 0;                         // number of 32x32 layers
+    float* d_blob = nullptr;              // fused fp32 blob (mlp_fp32.cuh)
+    uint32_t blob_bytes = 0;
+    void* d_tc = nullptr;                 // tensor-core operand images (mlp_tc.cu), lazily built
+    size_t tc_bytes = 0;
+    // render scratch, grown on demand (the reference keeps file-scope globals,
+    // src/volumeRender_kernel.cu:578-585); one render at a time per model handle
+    unsigned int* d_counters = nullptr;   // [0] pixel counter [1] queue tail [2] queue head [3] pad
+    void* d_queue = nullptr;
+    size_t queue_capacity = 0;
+    nsdf_render_stats* d_stats_scratch = nullptr;
+    float* d_act[2] = {nullptr, nullptr}; // ping-pong activations for the per-layer path
+    size_t act_capacity = 0;              // floats per buffer
+    int sm_count = 0;
+    // device staging of the host-buffer entry points (nsdf_render_host / nsdf_mlp_forward_host), grown on demand
+    void* d_stage[3] = {nullptr, nullptr, nullptr};   // [0] frame / y, [1] matcap / x, [2] stats
+    size_t stage_bytes[3] = {0, 0, 0};
+};
+
+namespace nsdf {
+
+// fp32 rungs + per-layer operator (nsdf_mlp.cu)
+int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res,
+                 float lo, float hi, int64_t first, cudaStream_t stream);
+int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const float* d_b, int M, int K,
+                       int64_t num_batches, int activation, cudaStream_t stream);
+
+// renderer (nsdf_render.cu)
+int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                  const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                  cudaStream_t stream);
+void render_release(nsdf_model* m);
+
+// tensor-core path (mlp_tc.cu)
+int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res, float lo,
+               float hi, int64_t first, cudaStream_t stream);
+void tc_release(nsdf_model* m);
+
+}  // namespace nsdf

@@ -1,0 +1,163 @@
+// =====================================================================================
+// nsdf_mlp.cu -- dense-query kernels (fp32 rungs) and the per-layer operators.
+// Compiled with -fmad=false: the explicit fmaf() calls are the only fused operations.
+// =====================================================================================
+#include "mlp_fp32.cuh"
+#include "nsdf_internal.h"
+
+namespace nsdf {
+
+struct LatticeParams { int enabled; int res; float lo, hi; long long first; };
+
+// p = lo + (hi-lo)*(i+0.5)/res per axis, x fastest (BASELINE config 3 / SURVEY 8(d) C3).
+__device__ __forceinline__ void lattice_point(const LatticeParams& lp, long long idx, float (&x)[3]) {
+    const long long r = lp.res;
+    const int ix = (int)(idx % r), iy = (int)((idx / r) % r), iz = (int)(idx / (r * r));
+    const float s = __fdiv_rn(lp.hi - lp.lo, (float)lp.res);
+    x[0] = fmaf((float)ix + 0.5f, s, lp.lo);
+    x[1] = fmaf((float)iy + 0.5f, s, lp.lo);
+    x[2] = fmaf((float)iz + 0.5f, s, lp.lo);
+}
+
+// Thread-per-point fused MLP.  Persistent: chunks of blockDim*P points are strided over the grid.
+template <int P>
+__global__ void __launch_bounds__(256, (P >= 2) ? 1 : 2)
+mlp_fp32_thread_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_sq, const float* __restrict__ xin,
+                       float* __restrict__ yout, long long n, const LatticeParams lp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, blob, blob_bytes, &s_bar);
+    const long long chunk = (long long)blockDim.x * P;
+    for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
+        float x[P][3], y[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const long long i = base + (long long)p * blockDim.x + threadIdx.x;
+            x[p][0] = x[p][1] = x[p][2] = 0.0f;
+            if (i < n) {
+                if (lp.enabled) lattice_point(lp, lp.first + i, x[p]);
+                else { x[p][0] = __ldg(xin + 3 * i); x[p][1] = __ldg(xin + 3 * i + 1); x[p][2] = __ldg(xin + 3 * i + 2); }
+            }
+        }
+        mlp32_eval_thread<P>(s_w, n_sq, x, y);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const long long i = base + (long long)p * blockDim.x + threadIdx.x;
+            if (i < n) yout[i] = y[p];
+        }
+    }
+}
+
+// Warp-cooperative fused MLP on a dense batch (exercises the latency evaluator of the tracer).
+template <int R>
+__global__ void __launch_bounds__(512, 1)
+mlp_fp32_warp_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_sq, const float* __restrict__ xin,
+                     float* __restrict__ yout, long long n, const LatticeParams lp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, blob, blob_bytes, &s_bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    float* abuf = s_w + (blob_bytes >> 2) + warp * (2 * R * WARP_ACT_STRIDE);
+    const long long gw = (long long)blockIdx.x * wpb + warp, nw = (long long)gridDim.x * wpb;
+    for (long long base = gw * R; base < n; base += nw * R) {
+        float x[R][3], y[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const long long i = base + r;
+            x[r][0] = x[r][1] = x[r][2] = 0.0f;
+            if (i < n) {
+                if (lp.enabled) lattice_point(lp, lp.first + i, x[r]);
+                else { x[r][0] = __ldg(xin + 3 * i); x[r][1] = __ldg(xin + 3 * i + 1); x[r][2] = __ldg(xin + 3 * i + 2); }
+            }
+        }
+        mlp32_eval_warp<R>(s_w, n_sq, abuf, x, y, lane);
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+            if (lane == r && base + r < n) yout[base + r] = y[r];
+    }
+}
+
+// Generic dense layer (any M, K; N = 1 per batch): replaces denseLayerForward /
+// batchedDenseLayerForward (src/layers/denseLayer.cu:86-176) with the same arithmetic.
+__global__ void __launch_bounds__(256)
+dense_layer_kernel(const float* __restrict__ W, const float* __restrict__ A, float* __restrict__ Z,
+                   const float* __restrict__ b, int M, int K, long long num_batches, int activation) {
+    const long long total = num_batches * M;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (long long)gridDim.x * blockDim.x) {
+        const long long j = t / M;
+        const int m = (int)(t % M);
+        const float* w = W + (size_t)m * K;
+        const float* a = A + (size_t)j * K;
+        float acc = 0.0f;
+        for (int k = 0; k < K; ++k) acc = fmaf(__ldg(w + k), __ldg(a + k), acc);
+        float v = acc + __ldg(b + m);
+        if (activation == NSDF_ACT_RELU) v = relu_det(v);
+        Z[t] = v;
+    }
+}
+
+static int env_int(const char* name, int dflt) {
+    const char* s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res,
+                 float lo, float hi, int64_t first, cudaStream_t stream) {
+    if (n == 0) return NSDF_OK;
+    LatticeParams lp{lattice ? 1 : 0, res, lo, hi, (long long)first};
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    cudaError_t e;
+    if (precision == NSDF_PREC_FP32_WARP) {
+        constexpr int R = 4;
+        const int threads = 512;
+        const size_t smem = m->blob_bytes + (threads / 32) * 2 * R * WARP_ACT_STRIDE * sizeof(float);
+        static bool attr_done = false;
+        if (!attr_done) {
+            e = cudaFuncSetAttribute(mlp_fp32_warp_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            if (e != cudaSuccess) return (int)e;
+            attr_done = true;
+        }
+        long long want = (n + (long long)(threads / 32) * R - 1) / ((long long)(threads / 32) * R);
+        const int grid = (int)(want < sms ? want : sms);
+        mlp_fp32_warp_kernel<R><<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+        return (int)cudaGetLastError();
+    }
+    const int P = env_int("NSDF_FP32_P", 2);
+    const size_t smem = m->blob_bytes;
+    static bool attr1 = false, attr2 = false;
+    if (P == 1) {
+        if (!attr1) {
+            e = cudaFuncSetAttribute(mlp_fp32_thread_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+            if (e != cudaSuccess) return (int)e;
+            attr1 = true;
+        }
+        const long long chunk = 256;
+        long long want = (n + chunk - 1) / chunk;
+        const int grid = (int)(want < 2LL * sms ? want : 2LL * sms);
+        mlp_fp32_thread_kernel<1><<<grid, 256, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+    } else {
+        if (!attr2) {
+            e = cudaFuncSetAttribute(mlp_fp32_thread_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+            if (e != cudaSuccess) return (int)e;
+            attr2 = true;
+        }
+        const long long chunk = 512;
+        long long want = (n + chunk - 1) / chunk;
+        const int grid = (int)(want < sms ? want : sms);
+        mlp_fp32_thread_kernel<2><<<grid, 256, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+    }
+    return (int)cudaGetLastError();
+}
+
+int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const float* d_b, int M, int K,
+                       int64_t num_batches, int activation, cudaStream_t stream) {
+    if (num_batches == 0) return NSDF_OK;
+    const long long total = (long long)num_batches * M;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    dense_layer_kernel<<<(int)blocks, 256, 0, stream>>>(d_W, d_A, d_Z, d_b, M, K, (long long)num_batches, activation);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace nsdf

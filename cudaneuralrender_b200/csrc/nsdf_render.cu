@@ -1,0 +1,156 @@
+// =====================================================================================
+// nsdf_render.cu -- host side of the persistent sphere tracer (launches of
+// render_kernels.cuh).  Replaces render_kernel / allocateBuffers
+// (src/volumeRender_kernel.cu:587-692).  Compiled with -fmad=false.
+// =====================================================================================
+#include <cstdlib>
+#include <cstring>
+
+#include "nsdf_internal.h"
+#include "render_kernels.cuh"
+
+namespace nsdf {
+
+static int env_int(const char* name, int dflt) {
+    const char* s = getenv(name);
+    return (s && *s) ? atoi(s) : dflt;
+}
+
+constexpr int LAT_R = 4;            // ray slots per warp in the latency kernel
+constexpr int LAT_THREADS = 512;
+
+static size_t latency_smem(const nsdf_model* m) {
+    return m->blob_bytes + (LAT_THREADS / 32) * 2 * LAT_R * WARP_ACT_STRIDE * sizeof(float);
+}
+
+static int ensure_scratch(nsdf_model* m, size_t queue_entries) {
+    cudaError_t e;
+    if (!m->d_counters) {
+        e = cudaMalloc(&m->d_counters, 4 * sizeof(unsigned int));
+        if (e != cudaSuccess) return (int)e;
+    }
+    if (queue_entries > m->queue_capacity) {
+        if (m->d_queue) cudaFree(m->d_queue);
+        m->d_queue = nullptr;
+        m->queue_capacity = 0;
+        e = cudaMalloc(&m->d_queue, queue_entries * sizeof(StragglerEntry));
+        if (e != cudaSuccess) return (int)e;
+        m->queue_capacity = queue_entries;
+    }
+    return NSDF_OK;
+}
+
+void render_release(nsdf_model* m) {
+    if (m->d_counters) cudaFree(m->d_counters);
+    if (m->d_queue) cudaFree(m->d_queue);
+    if (m->d_stats_scratch) cudaFree(m->d_stats_scratch);
+    m->d_counters = nullptr;
+    m->d_queue = nullptr;
+    m->d_stats_scratch = nullptr;
+    m->queue_capacity = 0;
+}
+
+int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                  const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                  cudaStream_t stream) {
+    if (!m->fused || m->in[0] != 3) return NSDF_EUNSUPPORTED;
+    if (opts->tile_world < 1 || opts->tile_rank < 0 || opts->tile_rank >= opts->tile_world) return NSDF_EINVAL;
+    if (opts->color_type == NSDF_COLOR_MATCAP && (!d_matcap || mw <= 0 || mh <= 0)) return NSDF_EINVAL;
+
+    RenderParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    std::memcpy(rp.cam.inv_view, cam->inv_view, sizeof(rp.cam.inv_view));
+    std::memcpy(rp.cam.normal, cam->normal, sizeof(rp.cam.normal));
+    rp.cam.frame = cam->frame;
+    rp.blob = m->d_blob;
+    rp.n_sq = m->n_sq;
+    rp.blob_bytes = m->blob_bytes;
+    rp.matcap = d_matcap;
+    rp.mw = mw;
+    rp.mh = mh;
+    rp.color_type = opts->color_type;
+    rp.scene = opts->scene;
+    rp.out = d_out;
+    rp.W = W;
+    rp.H = H;
+    rp.tiles_x = (W + TILE - 1) / TILE;
+    const int tiles_y = (H + TILE - 1) / TILE;
+    rp.n_tiles = rp.tiles_x * tiles_y;
+    rp.tile_rank = opts->tile_rank;
+    rp.tile_world = opts->tile_world;
+    const int my_tiles = (rp.n_tiles - opts->tile_rank + opts->tile_world - 1) / opts->tile_world;
+    if (my_tiles <= 0) return NSDF_OK;
+    if ((long long)my_tiles * TILE_PIXELS >= (1LL << 32)) return NSDF_EINVAL;
+    rp.total_idx = (unsigned int)my_tiles * TILE_PIXELS;
+    rp.max_steps = opts->max_steps;
+    rp.evict_steps = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_EVICT_STEPS", 48);
+    rp.stats = d_stats;
+
+    const bool simple = (opts->flags & NSDF_RENDER_SIMPLE) != 0;
+    const bool straggler = !simple && !(opts->flags & NSDF_RENDER_NO_STRAGGLER);
+    size_t qcap = 0;
+    if (straggler) {
+        qcap = rp.total_idx;
+        const size_t cap_max = (size_t)env_int("NSDF_QUEUE_MAX", 4 << 20);
+        if (qcap > cap_max) qcap = cap_max;
+    }
+    int rc = ensure_scratch(m, qcap);
+    if (rc) return rc;
+    rp.pixel_counter = m->d_counters;
+    rp.queue = straggler ? reinterpret_cast<StragglerEntry*>(m->d_queue) : nullptr;
+    rp.queue_capacity = straggler ? (unsigned int)qcap : 0u;
+
+    const bool only_latency = straggler && (opts->flags & NSDF_RENDER_PHASE_LATENCY) != 0;
+    const bool only_throughput = straggler && (opts->flags & NSDF_RENDER_PHASE_THROUGHPUT) != 0;
+    cudaError_t e = cudaSuccess;
+    if (!only_latency) {
+        e = cudaMemsetAsync(m->d_counters, 0, 4 * sizeof(unsigned int), stream);
+        if (e != cudaSuccess) return (int)e;
+    }
+
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    static bool attr_done = false;
+    if (!attr_done) {
+        e = cudaFuncSetAttribute(trace_throughput_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(trace_throughput_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(trace_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(trace_latency_kernel<LAT_R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+
+    if (simple) {
+        const unsigned int blocks = (rp.total_idx + 127u) / 128u;
+        trace_simple_kernel<<<blocks, 128, m->blob_bytes, stream>>>(rp);
+        return (int)cudaGetLastError();
+    }
+
+    if (only_latency) {
+        trace_latency_kernel<LAT_R><<<sms, LAT_THREADS, latency_smem(m), stream>>>(rp);
+        return (int)cudaGetLastError();
+    }
+    // throughput kernel: persistent, grid = SMs x resident CTAs
+    const int P = env_int("NSDF_TRACE_P", 1);
+    const unsigned int per_cta = 256u * (unsigned)P;
+    unsigned int want = (rp.total_idx + per_cta - 1) / per_cta;
+    if (P == 2) {
+        const unsigned int grid = want < (unsigned)sms ? want : (unsigned)sms;
+        trace_throughput_kernel<2><<<grid, 256, m->blob_bytes, stream>>>(rp);
+    } else {
+        const unsigned int cap = 2u * (unsigned)sms;
+        const unsigned int grid = want < cap ? want : cap;
+        trace_throughput_kernel<1><<<grid, 256, m->blob_bytes, stream>>>(rp);
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return (int)e;
+    if (straggler && !only_throughput) {
+        trace_latency_kernel<LAT_R><<<sms, LAT_THREADS, latency_smem(m), stream>>>(rp);
+        e = cudaGetLastError();
+    }
+    return (int)e;
+}
+
+}  // namespace nsdf

@@ -1,0 +1,329 @@
+// =====================================================================================
+// render_kernels.cuh -- persistent sphere tracer with fused normals + matcap shading.
+//
+// Replaces the reference's host-driven wavefront loop (render_kernel,
+// src/volumeRender_kernel.cu:608-692: up to 6000 x {9 GEMM launches, singleMarch, thrust
+// scan, blocking 4-byte D2H, createBatch}) by two launches with no host round trip:
+//
+//   trace_throughput_kernel<P>  persistent; one lane = P ray slots; the MLP is evaluated
+//       in registers (mlp32_eval_thread).  Finished slots are refilled from a global pixel
+//       counter with warp-ballot compaction (replaces thrust::exclusive_scan + createBatch),
+//       so lanes stay full.  Rays that are still marching after `evict_steps` steps (and
+//       the last few rays of a draining warp) are appended to the straggler queue.
+//   trace_latency_kernel<R>     persistent; one warp = R ray slots, lane = neuron
+//       (mlp32_eval_warp): one march step costs ~1.5k cycles instead of ~15k, which bounds
+//       the serial tail of rays that need thousands of steps.
+//
+// Per ray both kernels perform exactly the per-pixel projection of the reference loop
+// (initMarcher :293-358, createBatch :504-547, singleMarch :416-477), in the same
+// arithmetic, so frames are bit-identical to the oracle whatever the schedule.
+// =====================================================================================
+#pragma once
+#include "device_math.cuh"
+#include "mlp_fp32.cuh"
+#include "../../include/nsdf.h"
+
+namespace nsdf {
+
+constexpr int TILE = 64;           // multi-GPU partition granule (pixels)
+constexpr int TILE_PIXELS = TILE * TILE;
+
+struct StragglerEntry {            // 48 bytes, 16-byte aligned
+    int pix, steps;
+    float px, py;
+    float pz, dx, dy, dz;
+    float tfar, pad0, pad1, pad2;
+};
+
+struct RenderParams {
+    Camera cam;
+    const float* blob;
+    int n_sq;
+    uint32_t blob_bytes;
+    const uint32_t* matcap;
+    int mw, mh;
+    int color_type, scene;
+    uint32_t* out;
+    int W, H;
+    int tiles_x, n_tiles;
+    int tile_rank, tile_world;
+    unsigned int total_idx;        // pixel indices this call enumerates (my tiles * 4096)
+    int max_steps, evict_steps;
+    unsigned int* pixel_counter;   // [0] next pixel index, [1] straggler tail, [2] straggler head
+    StragglerEntry* queue;
+    unsigned int queue_capacity;
+    nsdf_render_stats* stats;
+};
+
+struct RaySlot {
+    int pix;      // linear pixel id y*W+x
+    int steps;    // march steps taken
+    int mode;     // -1 idle, 0 marching, 1..4 shading: next tetrahedron vertex = mode-1
+    f3 p, d;
+    float tfar;
+    float s0, s1, s2;
+};
+
+struct LocalStats { unsigned int queries, hits, rays, evicted, unfinished, pixels; };
+
+__device__ __forceinline__ bool decode_pixel(const RenderParams& rp, unsigned int idx, int& x, int& y) {
+    const unsigned int j = idx / TILE_PIXELS, within = idx % TILE_PIXELS;
+    const int t = rp.tile_rank + (int)j * rp.tile_world;
+    const int tx = t % rp.tiles_x, ty = t / rp.tiles_x;
+    const unsigned int sb = within >> 5, l = within & 31u;        // 8x4-pixel sub-blocks: one warp's first fill
+    x = tx * TILE + (int)(sb & 7u) * 8 + (int)(l & 7u);
+    y = ty * TILE + (int)(sb >> 3) * 4 + (int)(l >> 3);
+    return x < rp.W && y < rp.H;
+}
+
+// Point the network is asked about (createBatch, volumeRender_kernel.cu:526-545).
+__device__ __forceinline__ f3 slot_query_point(const RaySlot& s) {
+    if (s.mode <= 0) return s.p;
+    const f3 t = tet_vertex(s.mode - 1);
+    return f3{fmaf(t.x, NSDF_NORMAL_EPSILON, s.p.x), fmaf(t.y, NSDF_NORMAL_EPSILON, s.p.y),
+              fmaf(t.z, NSDF_NORMAL_EPSILON, s.p.z)};
+}
+
+// singleMarch (volumeRender_kernel.cu:416-477) for one slot whose request returned `nsdf`.
+__device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const RenderParams& rp, LocalStats& st) {
+    ++st.queries;
+    if (s.mode > 0) {
+        const float sv = scene_sdf(rp.scene, q, nsdf, rp.cam.frame);
+        if (s.mode == 1) s.s0 = sv;
+        else if (s.mode == 2) s.s1 = sv;
+        else if (s.mode == 3) s.s2 = sv;
+        if (s.mode < 4) { ++s.mode; return; }
+        const float sarr[4] = {s.s0, s.s1, s.s2, sv};
+        const f3 n = tet_normal(sarr);
+        rp.out[s.pix] = (rp.color_type == NSDF_COLOR_FACING) ? facing_color(n, s.d)
+                                                             : matcap_color(rp.cam, n, rp.matcap, rp.mw, rp.mh);
+        ++st.hits;
+        s.mode = -1;
+        return;
+    }
+    const float t = scene_sdf(rp.scene, s.p, nsdf, rp.cam.frame);
+    s.tfar = s.tfar - t;
+    ++s.steps;
+    if (s.tfar <= 0.0f) {             // left the march budget: background (:463-467)
+        rp.out[s.pix] = 0u;
+        s.mode = -1;
+        return;
+    }
+    s.p = f3{fmaf(s.d.x, t, s.p.x), fmaf(s.d.y, t, s.p.y), fmaf(s.d.z, t, s.p.z)};
+    if (t < NSDF_MARCHING_EPSILON) s.mode = 1;
+    if (s.steps >= rp.max_steps) {    // loop bound of render_kernel (:652): never shaded, stays 0
+        rp.out[s.pix] = 0u;
+        ++st.unfinished;
+        s.mode = -1;
+    }
+}
+
+// Starts the ray of enumeration index idx in slot s (initMarcher).  Returns with s.mode == -1 when
+// the pixel is outside the frame or misses the bounding sphere.
+__device__ __forceinline__ void slot_start(RaySlot& s, unsigned int idx, const RenderParams& rp, LocalStats& st) {
+    int x, y;
+    s.mode = -1;
+    if (!decode_pixel(rp, idx, x, y)) return;
+    ++st.pixels;
+    const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H);
+    const int pix = y * rp.W + x;
+    if (!r.hit || rp.max_steps <= 0) { rp.out[pix] = 0u; return; }
+    ++st.rays;
+    s.pix = pix; s.steps = 0; s.mode = 0; s.p = r.p; s.d = r.d; s.tfar = r.tfar;
+}
+
+__device__ __forceinline__ void flush_stats(const LocalStats& st, nsdf_render_stats* g) {
+    if (!g) return;
+    unsigned int v[6] = {st.queries, st.hits, st.rays, st.evicted, st.unfinished, st.pixels};
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        unsigned int x = v[i];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+        v[i] = x;
+    }
+    if ((threadIdx.x & 31) == 0) {
+        unsigned long long* p = reinterpret_cast<unsigned long long*>(g);
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            if (v[i]) atomicAdd(p + i, (unsigned long long)v[i]);
+    }
+}
+
+__device__ __forceinline__ unsigned int lanemask_lt() {
+    unsigned int m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// Warp-aggregated append of marching rays to the straggler queue.
+__device__ __forceinline__ void evict_slot(RaySlot& s, bool do_evict, const RenderParams& rp, LocalStats& st) {
+    const unsigned int m = __ballot_sync(0xffffffffu, do_evict);
+    if (!m) return;
+    const int leader = __ffs(m) - 1;
+    unsigned int base = 0;
+    if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(rp.pixel_counter + 1, (unsigned int)__popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (do_evict) {
+        const unsigned int slot = base + __popc(m & lanemask_lt());
+        if (slot < rp.queue_capacity) {
+            StragglerEntry e;
+            e.pix = s.pix; e.steps = s.steps; e.px = s.p.x; e.py = s.p.y; e.pz = s.p.z;
+            e.dx = s.d.x; e.dy = s.d.y; e.dz = s.d.z; e.tfar = s.tfar; e.pad0 = e.pad1 = e.pad2 = 0.0f;
+            float4* dst = reinterpret_cast<float4*>(rp.queue + slot);
+            const float4* src = reinterpret_cast<const float4*>(&e);
+            dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+            ++st.evicted;
+            s.mode = -1;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int P>
+__global__ void __launch_bounds__(256, (P >= 2) ? 1 : 2) trace_throughput_kernel(const __grid_constant__ RenderParams rp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
+
+    const unsigned int lane = threadIdx.x & 31u;
+    RaySlot slot[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) slot[p].mode = -1;
+    LocalStats st = {0, 0, 0, 0, 0, 0};
+    bool exhausted = false;   // warp-uniform
+
+    for (;;) {
+        // ---- refill idle slots from the global pixel counter (ballot compaction)
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            while (!exhausted) {
+                const bool need = slot[p].mode < 0;
+                const unsigned int m = __ballot_sync(0xffffffffu, need);
+                if (!m) break;
+                const int leader = __ffs(m) - 1;
+                const unsigned int cnt = __popc(m);
+                unsigned int base = 0;
+                if ((int)lane == leader) base = atomicAdd(rp.pixel_counter, cnt);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (need) {
+                    const unsigned int idx = base + __popc(m & lanemask_lt());
+                    if (idx < rp.total_idx) slot_start(slot[p], idx, rp, st);
+                }
+                if (base + cnt >= rp.total_idx) exhausted = true;
+            }
+        }
+        bool any = false;
+#pragma unroll
+        for (int p = 0; p < P; ++p) any |= slot[p].mode >= 0;
+        const unsigned int act = __ballot_sync(0xffffffffu, any);
+        if (!act) break;
+
+        // ---- one network evaluation per slot
+        float x[P][3], y[P];
+        f3 q[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            q[p] = (slot[p].mode >= 0) ? slot_query_point(slot[p]) : f3{0.0f, 0.0f, 0.0f};
+            x[p][0] = q[p].x; x[p][1] = q[p].y; x[p][2] = q[p].z;
+        }
+        mlp32_eval_thread<P>(s_w, rp.n_sq, x, y);
+#pragma unroll
+        for (int p = 0; p < P; ++p)
+            if (slot[p].mode >= 0) slot_update(slot[p], y[p], q[p], rp, st);
+
+        // ---- hand long rays (and the remains of a draining warp) to the latency kernel
+        if (rp.queue) {
+            int n_act = 0;
+#pragma unroll
+            for (int p = 0; p < P; ++p) n_act += __popc(__ballot_sync(0xffffffffu, slot[p].mode >= 0));
+            const bool drain = exhausted && n_act <= 8 * P;
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+                evict_slot(slot[p], slot[p].mode == 0 && (drain || slot[p].steps >= rp.evict_steps), rp, st);
+        }
+    }
+    flush_stats(st, rp.stats);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Latency path: lane r < R owns ray slot r; every lane is a neuron.
+template <int R>
+__global__ void __launch_bounds__(512, 1) trace_latency_kernel(const __grid_constant__ RenderParams rp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* abuf = s_w + (rp.blob_bytes >> 2) + warp * (2 * R * WARP_ACT_STRIDE);
+
+    unsigned int n_queue = rp.pixel_counter[1];
+    if (n_queue > rp.queue_capacity) n_queue = rp.queue_capacity;
+    RaySlot slot;
+    slot.mode = -1;
+    LocalStats st = {0, 0, 0, 0, 0, 0};
+    bool exhausted = false;
+
+    for (;;) {
+        if (!exhausted) {
+            const bool need = lane < R && slot.mode < 0;
+            const unsigned int m = __ballot_sync(0xffffffffu, need);
+            if (m) {
+                const int leader = __ffs(m) - 1;
+                const unsigned int cnt = __popc(m);
+                unsigned int base = 0;
+                if (lane == leader) base = atomicAdd(rp.pixel_counter + 2, cnt);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (need) {
+                    const unsigned int idx = base + __popc(m & lanemask_lt());
+                    if (idx < n_queue) {
+                        const float4* src = reinterpret_cast<const float4*>(rp.queue + idx);
+                        const float4 e0 = src[0], e1 = src[1], e2 = src[2];
+                        slot.pix = __float_as_int(e0.x); slot.steps = __float_as_int(e0.y);
+                        slot.p = f3{e0.z, e0.w, e1.x}; slot.d = f3{e1.y, e1.z, e1.w};
+                        slot.tfar = e2.x; slot.mode = 0;
+                    }
+                }
+                if (base + cnt >= n_queue) exhausted = true;
+            }
+        }
+        const unsigned int act = __ballot_sync(0xffffffffu, lane < R && slot.mode >= 0);
+        if (!act) { if (exhausted) break; else continue; }
+
+        const f3 q = (lane < R && slot.mode >= 0) ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
+        float x[R][3], y[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            x[r][0] = __shfl_sync(0xffffffffu, q.x, r);
+            x[r][1] = __shfl_sync(0xffffffffu, q.y, r);
+            x[r][2] = __shfl_sync(0xffffffffu, q.z, r);
+        }
+        mlp32_eval_warp<R>(s_w, rp.n_sq, abuf, x, y, lane);
+        float mine = y[0];
+#pragma unroll
+        for (int r = 1; r < R; ++r) mine = (lane == r) ? y[r] : mine;
+        if (lane < R && slot.mode >= 0) slot_update(slot, mine, q, rp, st);
+    }
+    flush_stats(st, rp.stats);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Debug / A-B kernel: one thread per enumeration index, no refill, no eviction.
+__global__ void __launch_bounds__(128) trace_simple_kernel(const __grid_constant__ RenderParams rp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
+    const unsigned int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    RaySlot slot;
+    slot.mode = -1;
+    LocalStats st = {0, 0, 0, 0, 0, 0};
+    if (idx < rp.total_idx) slot_start(slot, idx, rp, st);
+    while (__ballot_sync(0xffffffffu, slot.mode >= 0)) {
+        const f3 q = (slot.mode >= 0) ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
+        float x[1][3] = {{q.x, q.y, q.z}}, y[1];
+        mlp32_eval_thread<1>(s_w, rp.n_sq, x, y);
+        if (slot.mode >= 0) slot_update(slot, y[0], q, rp, st);
+    }
+    flush_stats(st, rp.stats);
+}
+
+}  // namespace nsdf

@@ -1,0 +1,187 @@
+/* =====================================================================================
+ * nsdf.h -- C ABI of the B200-native neural-SDF hot path (libnsdf.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, opaque handles, int status
+ * (0 = success, otherwise a cudaError_t value or one of the NSDF_E* codes below).
+ * Nothing here depends on torch, on C++ types, or on the CPU oracle.  Every entry
+ * point names the interface of the reference (daviesthomas/cudaNeuralRender, paths
+ * relative to its root) that it replaces.  INTEGRATION.md shows the reference-side
+ * binding (the patch a maintainer would apply to src/layers/denseLayer.cu,
+ * src/neuralNetwork.cpp and src/volumeRender_kernel.cu).
+ *
+ * Conventions
+ *   - "d_" pointers are device pointers on the CURRENT device, "h_" pointers are host.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).  Calls that take a
+ *     stream are asynchronous with respect to the host unless stated otherwise.
+ *   - A model handle belongs to the device that was current when it was created.
+ * ===================================================================================== */
+#ifndef NSDF_H_
+#define NSDF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NSDF_OK 0
+#define NSDF_EINVAL 10001       /* bad argument                                           */
+#define NSDF_EUNSUPPORTED 10002 /* model shape not handled by the requested kernel        */
+#define NSDF_EIO 10003          /* file could not be read / parsed                        */
+#define NSDF_ENOMEM 10004
+
+/* Activation ids: the reference's `enum Activation { ReLU, Tanh }` (src/layers/denseLayer.hh:6-9).
+ * "Tanh" selects the LINEAR epilogue in the reference (src/layers/denseLayer.cu:93-113,150-166);
+ * the caller applies tanh itself (src/simpleInfer.cpp:109, src/volumeRender_kernel.cu:229). */
+#define NSDF_ACT_RELU 0
+#define NSDF_ACT_TANH_LINEAR 1
+
+/* Arithmetic rungs of the fused MLP kernel (DESIGN.md "Precision ladder"). */
+#define NSDF_PREC_FP32 0       /* fp32 FFMA, ascending-k single accumulator: bit-identical to the reference order */
+#define NSDF_PREC_TC_FP16 1    /* tcgen05 kind::f16, fp16 operands, fp32 accumulate (bound 4e-3 abs)              */
+#define NSDF_PREC_TC_BF16 2    /* tcgen05 kind::f16, bf16 operands, fp32 accumulate (bound 3e-2 abs)              */
+#define NSDF_PREC_TC_FP16X3 3  /* tcgen05, split-fp16 (hi+lo) operands, 3 MMAs per layer (bound 1e-4 abs)        */
+#define NSDF_PREC_FP32_WARP 4  /* fp32, warp-cooperative evaluator (lanes = neurons); same bits as NSDF_PREC_FP32 */
+
+/* Scene functions: sceneSDF, src/volumeRender_kernel.cu:217-230. */
+#define NSDF_SCENE_TANH 0       /* tanh(nSDF)  (:229, the shipped renders)                 */
+#define NSDF_SCENE_MANYSPHERE 1 /* manySphere(p, nSDF, true)  (:221, what HEAD evaluates)  */
+
+/* c_coloringType, src/volumeRender_kernel.cu:33 */
+#define NSDF_COLOR_FACING 0
+#define NSDF_COLOR_MATCAP 1
+
+typedef struct nsdf_model nsdf_model;
+
+/* ---- library --------------------------------------------------------------------------- */
+const char* nsdf_version(void);
+/* Human-readable text for a status returned by this library. */
+const char* nsdf_error_string(int status);
+/* Number of SMs of the current device (0 if there is no usable device). */
+int nsdf_device_sm_count(void);
+
+/* ---- model: replaces NeuralNetwork::load / addLayer and the DenseLayer constructor ------
+ * (src/neuralNetwork.cpp:50-52,85-151; src/layers/denseLayer.cu:180-227).
+ * W[l] is HOST memory, [out][in] row-major, exactly DenseLayer::W after initializeWeights
+ * (W[y*in + x] = weights[x][y], denseLayer.cu:220); b[l] is host, [out].  Weights are copied to
+ * the device and re-packed for the fused kernels; the caller keeps ownership of its buffers. */
+int nsdf_model_create(const float* const* W, const float* const* b, const int* in_dim, const int* out_dim,
+                      const int* activation, int n_layers, nsdf_model** out);
+/* Same, from one packed host array: per layer W[out][in] then b[out]; dims has n_layers+1 entries.
+ * Activations follow src/neuralNetwork.cpp:136-139 (last layer "Tanh", the others ReLU). */
+int nsdf_model_create_packed(const float* params, const int* dims, int n_layers, nsdf_model** out);
+/* Keras `save_weights` .h5 file, walked like NeuralNetwork::load (name-sorted groups,
+ * /L/L/{bias:0,kernel:0}; src/neuralNetwork.cpp:85-151) by the library's own HDF5 reader. */
+int nsdf_model_load_h5(const char* path, nsdf_model** out);
+/* Host-only part of the same walk (no device needed): returns the layer count, dims (n_layers+1
+ * ints, capacity dims_capacity) and the packed parameters in the layout of nsdf_model_create_packed.
+ * Any output pointer may be NULL; n_params_out always receives the float count. */
+int nsdf_h5_read_keras(const char* path, int* n_layers_out, int* dims_out, int dims_capacity, float* params_out,
+                       size_t params_capacity, size_t* n_params_out);
+void nsdf_model_destroy(nsdf_model* m);
+int nsdf_model_num_layers(const nsdf_model* m);
+/* dims_out receives n_layers+1 ints. */
+int nsdf_model_dims(const nsdf_model* m, int* dims_out);
+/* 1 if the fused kernels apply (3|4 -> 32 x k -> 1, ReLU hidden, linear last), else 0. */
+int nsdf_model_is_fused(const nsdf_model* m);
+/* Copies the packed host parameters (layout of nsdf_model_create_packed) into params_out
+ * (capacity in floats); returns the number of floats through n_out. */
+int nsdf_model_params(const nsdf_model* m, float* params_out, size_t capacity, size_t* n_out);
+
+/* ---- MLP: replaces NeuralNetwork::forward (src/neuralNetwork.cpp:54-63) -------------------
+ * d_x: n points, element [b*in0 + c] -- the layout of Matrix(Shape(3, B)) (src/simpleInfer.cpp:116);
+ * d_y: n values, pre-tanh, the layout of the returned Matrix(1, B).  Any n >= 0 (the reference
+ * fails when n is a multiple of 65536). */
+int nsdf_mlp_forward(const nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, void* stream);
+/* Host-buffer variant (what a plugin caller with host Matrix data uses): H2D, kernel, D2H,
+ * synchronous.  h_x / h_y may be pageable or pinned. */
+int nsdf_mlp_forward_host(const nsdf_model* m, const float* h_x, float* h_y, int64_t n, int precision);
+/* Dense lattice sweep (BASELINE config 3): evaluates the res^3 lattice p = lo + (hi-lo)*(i+0.5)/res,
+ * x fastest, for linear indices [first, first+count); points are generated in-kernel. */
+int nsdf_mlp_forward_lattice(const nsdf_model* m, float* d_y, int res, float lo, float hi, int64_t first,
+                             int64_t count, int precision, void* stream);
+
+/* ---- per-layer operators: replace the free functions of src/layers/denseLayer.cu ----------
+ * denseLayerForward (:86-124) and batchedDenseLayerForward (:126-176): Z[:,j] = act(W A[:,j] + b)
+ * for j < num_batches; W is [M][K] row-major, A has column stride K, Z column stride M
+ * (N must be 1, as in every call the reference makes).  All device pointers, caller-owned. */
+int nsdf_dense_layer_forward(const float* d_W, const float* d_A, float* d_Z, const float* d_b, int M, int N, int K,
+                             int64_t num_batches, int activation, void* stream);
+
+/* ---- renderer: replaces render_kernel / copyViewMatrices / copyStaticSettings ---------------
+ * (src/volumeRender_kernel.cu:608-706) and the kernels it drives (initMarcher :293,
+ * createBatch :504, singleMarch :416, thrust scan :553). */
+typedef struct nsdf_camera {
+    float inv_view[12]; /* c_invViewMatrix: rows 0..2 of modelView (src/main.cpp:218-221)            */
+    float normal[16];   /* c_normalMatrix: inverse(modelView), row-major 4x4 (src/main.cpp:214-217) */
+    int frame;          /* c_frameNumber                                                           */
+} nsdf_camera;
+
+typedef struct nsdf_render_opts {
+    int color_type;   /* NSDF_COLOR_*                                                      */
+    int scene;        /* NSDF_SCENE_*                                                      */
+    int max_steps;    /* MAX_STEPS of the reference = 6000 (volumeRender_kernel.cu:61)     */
+    int tile_rank;    /* this call renders the 64x64 tiles t with t % tile_world == tile_rank */
+    int tile_world;   /* 1 = whole frame                                                   */
+    int evict_steps;  /* rays still marching after this many steps move to the latency path; 0 = library default */
+    int flags;        /* NSDF_RENDER_* bits                                                */
+} nsdf_render_opts;
+
+#define NSDF_RENDER_SIMPLE 1u      /* one-thread-per-pixel kernel without refill (debug / A-B testing) */
+#define NSDF_RENDER_NO_STRAGGLER 2u /* keep every ray in the throughput kernel                          */
+#define NSDF_RENDER_PHASE_THROUGHPUT 4u /* launch only the throughput kernel (stragglers stay queued)       */
+#define NSDF_RENDER_PHASE_LATENCY 8u    /* launch only the latency kernel on the queue a PHASE_THROUGHPUT call
+                                           of the same model handle left behind (per-kernel timing)            */
+
+typedef struct nsdf_render_stats {
+    unsigned long long queries;    /* MLP evaluations = sum over rays (march steps + 4 per shaded hit) */
+    unsigned long long hit_pixels; /* shaded pixels                                                     */
+    unsigned long long rays;       /* rays that entered the bounding sphere                             */
+    unsigned long long evicted;    /* rays handed to the latency path                                   */
+    unsigned long long unfinished; /* rays stopped by max_steps                                         */
+    unsigned long long pixels;     /* pixels this call covered                                          */
+} nsdf_render_stats;
+
+/* Fills opts with the reference's compile-time settings (tanh scene, 6000 steps, whole frame). */
+void nsdf_render_opts_default(nsdf_render_opts* opts);
+
+/* updateViewMatrices (src/main.cpp:207-222): modelView from viewRotation (degrees) and
+ * viewTranslation, without Eigen.  Host-side helper. */
+void nsdf_camera_from_view(float rx_deg, float ry_deg, float tx, float ty, float tz, int frame, nsdf_camera* cam);
+
+/* One frame into d_out (W*H packed a<<24|b<<16|g<<8|r, volumeRender_kernel.cu:273).  Every pixel
+ * of the selected tiles is written (0 where the reference leaves the caller's memset).
+ * d_matcap: mw*mh texels packed like Image::loadPNG (src/neuralUtils/image.cu:58); may be NULL
+ * when color_type == NSDF_COLOR_FACING.  d_stats (device, may be NULL) is ACCUMULATED into.
+ * d_out may be a peer-mapped pointer (tile partitioning across GPUs). */
+int nsdf_render(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                void* stream);
+/* Host-buffer variant: uploads the matcap, renders, copies the frame back; synchronous.
+ * h_stats may be NULL. */
+int nsdf_render_host(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* h_matcap, int mw, int mh,
+                     const nsdf_render_opts* opts, uint32_t* h_out, int W, int H, nsdf_render_stats* h_stats);
+
+/* ---- multi-GPU frame gather over NVLink (one process per GPU) --------------------------------
+ * The presenting rank exports its frame buffer; the other ranks open it and pass the mapped
+ * pointer as d_out of nsdf_render, so finished tiles are stored straight into the root's HBM. */
+#define NSDF_IPC_HANDLE_BYTES 64
+int nsdf_ipc_export(void* d_ptr, unsigned char handle_out[NSDF_IPC_HANDLE_BYTES]);
+int nsdf_ipc_open(const unsigned char handle[NSDF_IPC_HANDLE_BYTES], void** d_ptr_out);
+int nsdf_ipc_close(void* d_ptr);
+
+/* ---- image I/O used by the drop-in executables (src/neuralUtils/image.cu:36-110,
+ * src/common/helper_image.h:252-329) ------------------------------------------------------------ */
+/* Decodes an 8-bit RGB/RGBA/grey non-interlaced PNG into packed texels (a<<24|b<<16|g<<8|r).
+ * Call with texels == NULL to query w/h. */
+int nsdf_png_load(const char* path, uint32_t* texels, size_t capacity, int* w, int* h);
+/* Image::savePNG: flip != 0 reverses the texel stream (the reference's default 180-degree turn). */
+int nsdf_png_save(const char* path, const uint32_t* texels, int w, int h, int flip);
+/* sdkSavePPM4ub / __savePPM: "P6\n<W>\n<H>\n255\n" + RGB. */
+int nsdf_ppm_save(const char* path, const uint32_t* texels, int w, int h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NSDF_H_ */

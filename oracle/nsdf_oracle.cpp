@@ -509,14 +509,15 @@ int oracle_init_rays(const float* inv_view12, int W, int H, float* rays10, uint8
     return 0;
 }
 
-// render_kernel (src/volumeRender_kernel.cu:608-692) for one frame.
+// render_kernel (src/volumeRender_kernel.cu:608-692) for one frame, or for the rows
+// y = y0, y0+ystride, ... < y1 of it (bounded CPU-baseline samples; other rows are not touched).
 //   color_type: 0 facing ratio, 1 matcap (c_coloringType :33);  scene: 0 tanh, 1 manySphere (HEAD)
 //   out: W*H packed ABGR uint32 (:273);  steps_out/hit_out optional;  queries_out = Q_frame.
-int oracle_render(const float* params, const int* dims, int n_layers, const float* inv_view12, const float* normal16,
-                  int frame, const uint32_t* matcap, int mw, int mh, int color_type, int scene, int W, int H,
-                  int max_steps, uint32_t* out, int32_t* steps_out, uint8_t* hit_out, int64_t* queries_out,
-                  int nthreads) {
-    if (n_layers <= 0 || W <= 0 || H <= 0) return 1;
+int oracle_render_rows(const float* params, const int* dims, int n_layers, const float* inv_view12,
+                       const float* normal16, int frame, const uint32_t* matcap, int mw, int mh, int color_type,
+                       int scene, int W, int H, int max_steps, int y0, int y1, int ystride, uint32_t* out,
+                       int32_t* steps_out, uint8_t* hit_out, int64_t* queries_out, int nthreads) {
+    if (n_layers <= 0 || W <= 0 || H <= 0 || ystride <= 0 || y0 < 0 || y1 > H) return 1;
     if (color_type != 0 && (!matcap || mw <= 0 || mh <= 0)) return 2;
     const Model m = make_model(params, dims, n_layers);
     if (m.in[0] != 3 || m.out[n_layers - 1] != 1) return 3;
@@ -524,7 +525,8 @@ int oracle_render(const float* params, const int* dims, int n_layers, const floa
     std::memcpy(cam.inv_view, inv_view12, sizeof(cam.inv_view));
     std::memcpy(cam.normal, normal16, sizeof(cam.normal));
     cam.frame = frame;
-    const int64_t N = (int64_t)W * H;
+    const int64_t nrows = y1 > y0 ? (y1 - y0 + ystride - 1) / ystride : 0;
+    const int64_t N = nrows * W;
     const int64_t nblocks = (N + LANES - 1) / LANES;
     std::atomic<int64_t> total_q(0);
     parallel_for(nblocks, nthreads, [&](int64_t b0, int64_t b1, int) {
@@ -534,7 +536,10 @@ int oracle_render(const float* params, const int* dims, int n_layers, const floa
         for (int64_t blk = b0; blk < b1; ++blk) {
             const int64_t base = blk * LANES;
             const int cnt = (int)std::min<int64_t>(LANES, N - base);
-            for (int j = 0; j < cnt; ++j) { px[j] = (int)((base + j) % W); py[j] = (int)((base + j) / W); }
+            for (int j = 0; j < cnt; ++j) {
+                px[j] = (int)((base + j) % W);
+                py[j] = y0 + (int)((base + j) / W) * ystride;
+            }
             render_block<LANES>(m, cam, matcap, mw, mh, color_type, scene, W, H, max_steps, px, py, cnt, out,
                                 steps_out, hit_out, q, scratch.data());
         }
@@ -542,6 +547,14 @@ int oracle_render(const float* params, const int* dims, int n_layers, const floa
     });
     if (queries_out) *queries_out = total_q.load();
     return 0;
+}
+
+int oracle_render(const float* params, const int* dims, int n_layers, const float* inv_view12, const float* normal16,
+                  int frame, const uint32_t* matcap, int mw, int mh, int color_type, int scene, int W, int H,
+                  int max_steps, uint32_t* out, int32_t* steps_out, uint8_t* hit_out, int64_t* queries_out,
+                  int nthreads) {
+    return oracle_render_rows(params, dims, n_layers, inv_view12, normal16, frame, matcap, mw, mh, color_type, scene, W,
+                              H, max_steps, 0, H, 1, out, steps_out, hit_out, queries_out, nthreads);
 }
 
 }  // extern "C"

@@ -52,6 +52,11 @@ def lib():
         L.oracle_render.argtypes = [fp, ip, C.c_int, fp, fp, C.c_int, C.POINTER(C.c_uint32), C.c_int, C.c_int,
                                     C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_uint32),
                                     C.POINTER(C.c_int32), C.POINTER(C.c_uint8), C.POINTER(C.c_int64), C.c_int]
+        L.oracle_render_rows.restype = C.c_int
+        L.oracle_render_rows.argtypes = [fp, ip, C.c_int, fp, fp, C.c_int, C.POINTER(C.c_uint32), C.c_int, C.c_int,
+                                         C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                         C.POINTER(C.c_uint32), C.POINTER(C.c_int32), C.POINTER(C.c_uint8),
+                                         C.POINTER(C.c_int64), C.c_int]
         _lib = L
     return _lib
 
@@ -136,8 +141,9 @@ def init_rays(inv_view: np.ndarray, W: int, H: int):
 
 def render(model: Model, inv_view, normal, W: int, H: int, matcap: Optional[np.ndarray] = None,
            color_type: Optional[int] = None, scene: int = SCENE_TANH, frame: int = 0, max_steps: int = 6000,
-           nthreads: int = 0, want_stats: bool = True):
-    """Returns dict(image uint32[H,W], steps int32[H,W], hit uint8[H,W], queries int)."""
+           nthreads: int = 0, want_stats: bool = True, rows=None):
+    """Returns dict(image uint32[H,W], steps int32[H,W], hit uint8[H,W], queries int).
+    rows=(y0, y1, stride) renders only those rows (the others stay 0)."""
     iv = np.ascontiguousarray(inv_view, dtype=np.float32)
     nm = np.ascontiguousarray(normal, dtype=np.float32)
     if color_type is None:
@@ -153,8 +159,9 @@ def render(model: Model, inv_view, normal, W: int, H: int, matcap: Optional[np.n
     steps = np.zeros((H, W), dtype=np.int32) if want_stats else None
     hit = np.zeros((H, W), dtype=np.uint8) if want_stats else None
     q = C.c_int64(0)
-    rc = lib().oracle_render(_fp(model.params), model.dims.ctypes.data_as(C.POINTER(C.c_int)), model.n_layers,
-                             _fp(iv), _fp(nm), frame, mptr, mw, mh, color_type, scene, W, H, max_steps,
+    y0, y1, ys = rows if rows is not None else (0, H, 1)
+    rc = lib().oracle_render_rows(_fp(model.params), model.dims.ctypes.data_as(C.POINTER(C.c_int)), model.n_layers,
+                             _fp(iv), _fp(nm), frame, mptr, mw, mh, color_type, scene, W, H, max_steps, y0, y1, ys,
                              out.ctypes.data_as(C.POINTER(C.c_uint32)),
                              steps.ctypes.data_as(C.POINTER(C.c_int32)) if want_stats else None,
                              hit.ctypes.data_as(C.POINTER(C.c_uint8)) if want_stats else None,

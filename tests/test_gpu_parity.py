@@ -1,0 +1,276 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle.
+
+Bars: fp32 rungs and the renderer are BIT-EXACT against the oracle (integer comparison of the
+float bit patterns / packed RGBA); tensor-core rungs within their stated bounds."""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, MATCAPS, MODELS, model_path
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def env(gpu):
+    import torch
+    from cudaneuralrender_b200 import host
+    from oracle import oracle
+    return {"torch": torch, "host": host, "oracle": oracle}
+
+
+def _load(env, name):
+    nn = env["host"].NeuralNetwork()
+    assert nn.load(model_path(name))
+    return nn, env["oracle"].Model.from_h5(model_path(name))
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def test_native_library_is_loaded(env):
+    from cudaneuralrender_b200 import _capi
+    assert os.path.exists(_capi.LIB_PATH)
+    assert _capi.lib().nsdf_device_sm_count() >= 100
+    maps = open("/proc/self/maps").read()
+    assert "libnsdf.so" in maps
+
+
+def test_known_answers_on_gpu(env):
+    """SURVEY App. B bit patterns through nsdf_mlp_forward (both fp32 evaluators)."""
+    torch, host = env["torch"], env["host"]
+    rows = json.load(open(os.path.join(GOLDEN, "kat_sdf.json")))["rows"]
+    for name in MODELS:
+        nn, _ = _load(env, name)
+        mine = [r for r in rows if r["model"] == name]
+        x = torch.tensor([r["point"] for r in mine], dtype=torch.float32, device="cuda")
+        for prec in (host.PREC_FP32, host.PREC_FP32_WARP):
+            y = nn.forward_tensor(x.contiguous(), prec).cpu().numpy()
+            assert [int(b) for b in _bits(y)] == [int(r["bits"], 16) for r in mine], (name, prec)
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 255, 256, 257, 65536, 2 ** 20, 1000003])
+def test_fp32_mlp_bit_exact(env, n):
+    """Random points, ragged sizes, and the multiples of 65 536 on which the reference's
+    GemmBatched grid.z bug fails."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "car_1")
+    x = np.random.default_rng(n).uniform(-1, 1, (n, 3)).astype(np.float32)
+    ref = oracle.mlp_forward(om, x).ravel()
+    xd = torch.from_numpy(x).cuda().contiguous()
+    for prec in (host.PREC_FP32, host.PREC_FP32_WARP):
+        if prec == host.PREC_FP32_WARP and n > 2 ** 20:
+            continue
+        y = nn.forward_tensor(xd, prec).cpu().numpy()
+        assert np.array_equal(_bits(y), _bits(ref)), prec
+    if n:
+        assert np.array_equal(_bits(nn.forward_host(x)), _bits(ref))
+
+
+def test_fp32_all_models_and_special_values(env):
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    rng = np.random.default_rng(5)
+    x = rng.uniform(-1.5, 1.5, (40000, 3)).astype(np.float32)
+    x[:8] = [[0, 0, 0], [-0.0, 0.0, -0.0], [1e-30, -1e-30, 1e-38], [1e4, -1e4, 1e4], [np.inf, 0, 0], [np.nan, 0, 0],
+             [1, 1, 1], [-1, -1, -1]]
+    for name in MODELS:
+        nn, om = _load(env, name)
+        y = nn.forward_tensor(torch.from_numpy(x).cuda().contiguous()).cpu().numpy()
+        ref = oracle.mlp_forward(om, x).ravel()
+        finite = np.isfinite(ref)
+        assert np.array_equal(_bits(y[finite]), _bits(ref[finite])), name
+        assert np.array_equal(np.isnan(y), np.isnan(ref))
+
+
+def test_equal_inputs_equal_outputs_like_simpleInfer(env):
+    """src/simpleInfer.cpp:112-147: 1 000 000 zero points, all outputs identical."""
+    torch, host = env["torch"], env["host"]
+    nn, _ = _load(env, "car_1")
+    X = host.Matrix(host.Shape(3, 1000000))
+    X.allocateMemory()
+    X.copyHostToDevice()
+    Y = nn.forward(X)
+    assert (Y.shape.x, Y.shape.y) == (1, 1000000)
+    Y.copyDeviceToHost()
+    assert np.all(Y.hostData[:1000000] == Y[0])
+    assert _bits(Y.hostData[:1])[0] == 0xBDF2F39C
+
+
+def test_layered_operators_match_fused(env):
+    """DenseLayer::forward chain (nsdf_dense_layer_forward) == fused kernel == oracle."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "plane_2")
+    n = 5000
+    x = np.random.default_rng(2).uniform(-1, 1, (n, 3)).astype(np.float32)
+    X = host.Matrix(host.Shape(3, n))
+    X.allocateMemory()
+    X.hostData[:] = x.ravel()
+    X.copyHostToDevice()
+    Z = nn.forward_layered(X)
+    Z.copyDeviceToHost()
+    ref = oracle.mlp_forward(om, x).ravel()
+    assert np.array_equal(_bits(Z.hostData[:n]), _bits(ref))
+    assert nn.layers[0].getXDim() == 3 and nn.layers[0].getYDim() == 32 and nn.getNumWeightParams() == 7296
+
+
+def test_non_fused_shapes_fall_to_layer_kernels(env):
+    """Arbitrary widths/depths go through the per-layer CUDA operator (still no CPU path)."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    for dims in ([3, 16, 8, 1], [5, 64, 64, 2], [3, 32, 1], [3, 32, 32, 32, 1]):
+        om = oracle.Model.random(dims, seed=len(dims))
+        nn = host.NeuralNetwork()
+        for i, (W, b) in enumerate(om.layers()):
+            nn.addLayer(host.DenseLayer(f"dense_{i}", W.T, b, host.Tanh if i == len(dims) - 2 else host.ReLU))
+        x = np.random.default_rng(0).uniform(-1, 1, (3001, dims[0])).astype(np.float32)
+        y = nn.forward_tensor(torch.from_numpy(x).cuda().contiguous()).cpu().numpy()
+        assert np.array_equal(_bits(y), _bits(oracle.mlp_forward(om, x).ravel())), dims
+
+
+def test_lattice_matches_explicit_points(env):
+    """BASELINE config 3 at reduced resolution: in-kernel lattice == explicit points == oracle."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "car_1")
+    res = 48
+    y = nn.forward_lattice(res).cpu().numpy()
+    i = np.arange(res, dtype=np.float32)
+    s = np.float32(2.0) / np.float32(res)
+    c = ((i + np.float32(0.5)).astype(np.float64) * np.float64(s) + np.float64(-1.0)).astype(np.float32)  # fmaf
+    zz, yy, xx = np.meshgrid(c, c, c, indexing="ij")
+    pts = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], axis=1).astype(np.float32)
+    ref = oracle.mlp_forward(om, pts).ravel()
+    assert np.array_equal(_bits(y), _bits(ref))
+    part = nn.forward_lattice(res, first=1000, count=777).cpu().numpy()
+    assert np.array_equal(_bits(part), _bits(ref[1000:1777]))
+
+
+def _render_both(env, name, W, H, matcap_name=None, scene=0, max_steps=6000, rx=0.0, ry=0.0, flags=0, frame=0,
+                 evict_steps=0):
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, name)
+    matcap = oracle.load_matcap_png(os.path.join(MATCAPS, matcap_name)) if matcap_name else None
+    iv, nm = oracle.view_matrices(rx, ry)
+    host.copyStaticSettings(host.COLOR_MATCAP if matcap is not None else host.COLOR_FACING, 3)
+    host.copyViewMatrices(iv, nm, frame, 3)
+    host.setSceneOptions(scene, max_steps, flags, evict_steps)
+    img, stats = host.render_host(nn, W, H, matcap)
+    host.setSceneOptions()
+    ref = oracle.render(om, iv, nm, W, H, matcap=matcap, scene=scene, max_steps=max_steps, frame=frame)
+    return img, stats, ref
+
+
+@pytest.mark.parametrize("name,W,H,matcap", [("car_1", 128, 128, "blue.png"), ("plane_1", 160, 90, "red.png"),
+                                              ("plane_3", 97, 61, None), ("car_1", 64, 64, "ball-298x300.png"),
+                                              ("3a3d4a90a2db90b4203936772104a82d.obj", 130, 70, "Normal.png")])
+def test_frames_bit_exact(env, name, W, H, matcap):
+    img, stats, ref = _render_both(env, name, W, H, matcap)
+    hit = ref["hit"] != 0
+    assert np.array_equal(img != 0, (ref["image"] != 0)), "hit masks differ"
+    assert np.array_equal(img, ref["image"]), "RGBA differs"
+    assert stats["queries"] == ref["queries"]
+    assert stats["hit_pixels"] == int(hit.sum())
+    assert stats["pixels"] == W * H
+
+
+def test_frame_schedules_agree(env):
+    """Simple kernel, refill kernel without stragglers, and refill + latency kernel with an
+    aggressive eviction threshold produce the same bytes (schedule independence)."""
+    host = env["host"]
+    outs = []
+    for flags, ev in [(host.capi.RENDER_SIMPLE, 0), (host.capi.RENDER_NO_STRAGGLER, 0), (0, 4), (0, 0)]:
+        img, stats, ref = _render_both(env, "car_1", 96, 96, "blue.png", flags=flags, evict_steps=ev)
+        assert np.array_equal(img, ref["image"]), (flags, ev)
+        assert stats["queries"] == ref["queries"]
+        outs.append(stats)
+    assert outs[2]["evicted"] > 0 and outs[0]["evicted"] == 0
+
+
+def test_frame_rotated_camera_and_head_scene(env):
+    img, stats, ref = _render_both(env, "car_1", 100, 80, "blue.png", rx=20.0, ry=135.0)
+    assert np.array_equal(img, ref["image"])
+    img, stats, ref = _render_both(env, "car_1", 80, 80, "blue.png", scene=1, frame=40)   # HEAD manySphere scene
+    assert np.array_equal(img, ref["image"])
+    assert stats["queries"] == ref["queries"]
+
+
+def test_frame_step_cap(env):
+    for cap in (1, 7, 64):
+        img, stats, ref = _render_both(env, "plane_1", 96, 64, None, max_steps=cap)
+        assert np.array_equal(img, ref["image"]), cap
+        assert stats["queries"] == ref["queries"]
+
+
+def test_frame_determinism_and_tiles(env):
+    """Same frame twice -> identical bytes; rendering the 64x64 tiles of ranks 0..G-1 into one
+    buffer equals the single-rank frame (the multi-GPU partition, on one device)."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "car_1")
+    W, H = 200, 136
+    iv, nm = oracle.view_matrices(0, 30)
+    host.copyStaticSettings(host.COLOR_FACING, 3)
+    host.copyViewMatrices(iv, nm, 0, 3)
+    a = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    b = torch.zeros_like(a)
+    host.render_kernel(a, W, H, nn)
+    host.render_kernel(b, W, H, nn)
+    assert torch.equal(a, b)
+    for G in (2, 3, 8):
+        c = torch.full_like(a, 0x55)
+        st = torch.zeros(6, dtype=torch.int64, device="cuda")
+        for r in range(G):
+            host.render_kernel(c, W, H, nn, stats=st, tile_rank=r, tile_world=G)
+        assert torch.equal(a, c), G
+        assert int(st[5]) == W * H
+    ref = oracle.render(om, iv, nm, W, H)
+    assert np.array_equal(a.cpu().numpy().view(np.uint32).reshape(H, W), ref["image"])
+
+
+def test_full_size_frame_properties(env):
+    """BASELINE config 2 size (1920x1080 plane_1): size-independent checks -- determinism across
+    schedules, query accounting, and a 64-row band compared with the oracle."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "plane_1")
+    W, H = 1920, 1080
+    matcap_np = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    mc = host.Image(host.Shape(matcap_np.shape[1], matcap_np.shape[0]))
+    mc.allocateMemory()
+    mc.hostData[:] = matcap_np.ravel()
+    mc.copyHostToDevice()
+    iv, nm = oracle.view_matrices()
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.copyViewMatrices(iv, nm, 0, 3)
+    outs = []
+    for flags in (0, host.capi.RENDER_NO_STRAGGLER):
+        host.setSceneOptions(host.SCENE_TANH, 6000, flags)
+        out = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+        st = torch.zeros(6, dtype=torch.int64, device="cuda")
+        host.render_kernel(out, W, H, nn, mc, stats=st)
+        torch.cuda.synchronize()
+        outs.append((out, st.cpu().numpy()))
+    host.setSceneOptions()
+    assert torch.equal(outs[0][0], outs[1][0])
+    assert outs[0][1][0] == outs[1][1][0]
+    q, hits, rays = int(outs[0][1][0]), int(outs[0][1][1]), int(outs[0][1][2])
+    assert rays == W * H and abs(q - 25034278) / 25034278 < 5e-3 and abs(hits - 70375) < 300
+    img = outs[0][0].cpu().numpy().view(np.uint32).reshape(H, W)
+    assert int((img != 0).sum()) == hits
+
+
+def test_error_behaviour(env):
+    torch, host = env["torch"], env["host"]
+    from cudaneuralrender_b200 import _capi
+    L = _capi.lib()
+    h = C.c_void_p(None)
+    assert L.nsdf_model_load_h5(b"/nonexistent/model.h5", C.byref(h)) == 10003
+    with pytest.raises(FileNotFoundError):
+        host.NeuralNetwork().load("/nonexistent/model.h5")
+    nn, _ = _load(env, "car_1")
+    assert L.nsdf_mlp_forward(nn.handle(), None, None, 5, 0, None) == 10001
+    assert L.nsdf_mlp_forward(nn.handle(), None, None, 0, 0, None) == 0
+    x = torch.zeros(30, device="cuda")
+    y = torch.zeros(10, device="cuda")
+    assert L.nsdf_mlp_forward(nn.handle(), x.data_ptr(), y.data_ptr(), 10, 99, None) == 10001
+    assert L.nsdf_dense_layer_forward(x.data_ptr(), x.data_ptr(), y.data_ptr(), y.data_ptr(), 1, 2, 3, 1, 0, None) == 10002

@@ -1,0 +1,230 @@
+"""CPU tests (no GPU): the oracle against the golden vectors, the HDF5 readers against each other,
+image I/O, and that libnsdf.so loads and exports every symbol include/nsdf.h declares."""
+import ctypes as C
+import json
+import os
+import re
+import struct
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, MATCAPS, MODELS, ROOT, model_path
+
+from oracle import h5mini, oracle
+
+
+@pytest.fixture(scope="module")
+def kat():
+    with open(os.path.join(GOLDEN, "kat_sdf.json")) as f:
+        return json.load(f)["rows"]
+
+
+def test_oracle_known_answers(built, kat):
+    """25 SDF values with bit patterns (CUTLASS SIMT order)."""
+    models = {}
+    for row in kat:
+        m = models.setdefault(row["model"], oracle.Model.from_h5(model_path(row["model"])))
+        y = oracle.mlp_forward(m, np.asarray([row["point"]], dtype=np.float32))[0, 0]
+        bits = struct.unpack("<I", struct.pack("<f", float(y)))[0]
+        assert bits == int(row["bits"], 16), (row, float(y))
+        t = oracle.tanhf(np.asarray([y], dtype=np.float32))[0]
+        assert abs(float(t) - row["tanh"]) <= 2e-7 * max(1.0, abs(row["tanh"])) + 6e-8
+
+
+def test_oracle_matches_float64_numpy(built):
+    """fp32 ascending-k evaluation stays within 1e-6 of an fp64 evaluation."""
+    rng = np.random.default_rng(0)
+    x = rng.uniform(-1, 1, (20000, 3)).astype(np.float32)
+    for name in MODELS[:2]:
+        m = oracle.Model.from_h5(model_path(name))
+        a = x.astype(np.float64)
+        layers = m.layers()
+        for i, (W, b) in enumerate(layers):
+            a = a @ W.astype(np.float64).T + b.astype(np.float64)
+            if i < len(layers) - 1:
+                a = np.maximum(a, 0)
+        y = oracle.mlp_forward(m, x)
+        assert np.max(np.abs(y - a)) < 1e-6
+
+
+def test_oracle_equal_inputs_equal_outputs(built):
+    """The only check the reference ships (src/simpleInfer.cpp:134-146)."""
+    m = oracle.Model.from_h5(model_path("car_1"))
+    y = oracle.mlp_forward(m, np.zeros((10000, 3), dtype=np.float32))
+    assert np.all(y == y[0])
+    assert y[0, 0].view(np.uint32) == 0xBDF2F39C
+
+
+def test_oracle_threads_agree(built):
+    m = oracle.Model.from_h5(model_path("plane_1"))
+    x = np.random.default_rng(1).uniform(-1, 1, (5003, 3)).astype(np.float32)
+    assert np.array_equal(oracle.mlp_forward(m, x, nthreads=1), oracle.mlp_forward(m, x, nthreads=4))
+
+
+def test_oracle_tanh_accuracy(built):
+    x = np.concatenate([np.linspace(-12, 12, 200001), np.random.default_rng(0).normal(0, 0.3, 100000)]).astype(np.float32)
+    t = oracle.tanhf(x)
+    ref = np.tanh(x.astype(np.float64))
+    ulp = np.spacing(np.abs(ref).astype(np.float32)).astype(np.float64)
+    assert np.max(np.abs(t - ref) / ulp) < 1.6
+    assert np.all(oracle.tanhf(np.float32([0.0, -0.0])) == 0)
+    assert oracle.tanhf(np.float32([np.inf]))[0] == 1 and oracle.tanhf(np.float32([-np.inf]))[0] == -1
+    assert np.isnan(oracle.tanhf(np.float32([np.nan]))[0])
+    small = np.float32([1e-6, -3e-7, 1e-4])
+    assert np.array_equal(oracle.tanhf(small), small)   # tanh(x) == x near the surface
+
+
+def test_h5_layout_golden(built):
+    """raw-data offsets and dims, identical in all five files; both readers agree."""
+    with open(os.path.join(GOLDEN, "h5_layout.json")) as f:
+        gold = json.load(f)
+    for name in MODELS:
+        path = model_path(name)
+        assert os.path.getsize(path) == gold["file_bytes"]
+        f5 = h5mini.H5File(path)
+        names = f5.root.list_object_names()
+        assert names == [l["layer"] for l in gold["layers"]]
+        raw = open(path, "rb").read()
+        for l in gold["layers"]:
+            inner = f5.root.children[l["layer"]].children[l["layer"]]
+            k, b = inner.children["kernel:0"], inner.children["bias:0"]
+            assert list(k.dims) == l["kernel_dims"] and k.data_offset == l["kernel_offset"]
+            assert list(b.dims) == l["bias_dims"] and b.data_offset == l["bias_offset"]
+            assert np.array_equal(k.data.ravel(), np.frombuffer(raw, "<f4", k.data.size, l["kernel_offset"]))
+
+
+def _capi():
+    from cudaneuralrender_b200 import _capi
+    return _capi
+
+
+def test_library_exports_every_declared_symbol(built):
+    capi = _capi()
+    L = capi.lib()
+    hdr = open(os.path.join(ROOT, "include", "nsdf.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(nsdf_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 25
+    for name in declared:
+        assert hasattr(L, name), f"libnsdf.so does not export {name}"
+    assert declared == set(capi.PROTOTYPES), declared ^ set(capi.PROTOTYPES)
+    assert b"sm_100a" in L.nsdf_version()
+    assert L.nsdf_error_string(10002).startswith(b"nsdf:")
+
+
+def test_product_h5_reader_matches_independent_reader(built):
+    """libnsdf's C++ reader (include/nsdf_h5.hpp) vs oracle/h5mini.py, host only."""
+    L = _capi().lib()
+    for name in MODELS:
+        n, cnt = C.c_int(0), C.c_size_t(0)
+        dims = (C.c_int * 16)()
+        assert L.nsdf_h5_read_keras(model_path(name).encode(), C.byref(n), dims, 16, None, 0, C.byref(cnt)) == 0
+        assert n.value == 9 and list(dims[:10]) == [3] + [32] * 8 + [1] and cnt.value == 7553
+        params = np.empty(cnt.value, dtype=np.float32)
+        assert L.nsdf_h5_read_keras(model_path(name).encode(), None, None, 0,
+                                    params.ctypes.data_as(C.POINTER(C.c_float)), params.size, None) == 0
+        ref_params, ref_dims = h5mini.pack_model(h5mini.load_keras_mlp(model_path(name)))
+        assert np.array_equal(params, ref_params) and list(ref_dims) == list(dims[:10])
+
+
+def test_product_h5_reader_rejects_garbage(built, tmp_path):
+    L = _capi().lib()
+    p = tmp_path / "bad.h5"
+    p.write_bytes(b"not an hdf5 file" * 100)
+    assert L.nsdf_h5_read_keras(str(p).encode(), None, None, 0, None, 0, None) == 10003
+    assert L.nsdf_h5_read_keras(str(tmp_path / "missing.h5").encode(), None, None, 0, None, 0, None) == 10003
+    raw = bytearray(open(model_path("car_1"), "rb").read())
+    q = tmp_path / "trunc.h5"
+    q.write_bytes(bytes(raw[:20000]))   # cuts into the kernels
+    assert L.nsdf_h5_read_keras(str(q).encode(), None, None, 0, None, 0, None) == 10003
+
+
+def test_png_decoder_matches_pil(built):
+    L = _capi().lib()
+    for fn in sorted(os.listdir(MATCAPS)):
+        if not fn.endswith(".png"):
+            continue
+        path = os.path.join(MATCAPS, fn)
+        w, h = C.c_int(0), C.c_int(0)
+        assert L.nsdf_png_load(path.encode(), None, 0, C.byref(w), C.byref(h)) == 0
+        tex = np.empty(w.value * h.value, dtype=np.uint32)
+        assert L.nsdf_png_load(path.encode(), tex.ctypes.data, tex.size, C.byref(w), C.byref(h)) == 0
+        ref = oracle.load_matcap_png(path)
+        assert ref.shape == (h.value, w.value)
+        assert np.array_equal(tex.reshape(ref.shape), ref), fn
+
+
+def test_png_ppm_writers(built, tmp_path):
+    from PIL import Image as PILImage
+    L = _capi().lib()
+    rng = np.random.default_rng(3)
+    w, h = 37, 21
+    tex = rng.integers(0, 2 ** 32, size=(h, w), dtype=np.uint64).astype(np.uint32)
+    p = str(tmp_path / "a.png")
+    assert L.nsdf_png_save(p.encode(), tex.ctypes.data, w, h, 0) == 0
+    im = np.asarray(PILImage.open(p).convert("RGBA"), dtype=np.uint32)
+    back = (im[..., 3] << 24) | (im[..., 2] << 16) | (im[..., 1] << 8) | im[..., 0]
+    assert np.array_equal(back, tex)
+    # Image::savePNG default: the texel stream reversed (180-degree turn), image.cu:84-98
+    assert L.nsdf_png_save(p.encode(), tex.ctypes.data, w, h, 1) == 0
+    im = np.asarray(PILImage.open(p).convert("RGBA"), dtype=np.uint32)
+    back = (im[..., 3] << 24) | (im[..., 2] << 16) | (im[..., 1] << 8) | im[..., 0]
+    assert np.array_equal(back, tex[::-1, ::-1])
+    # own decoder reads own encoder
+    out = np.empty(w * h, dtype=np.uint32)
+    ww, hh = C.c_int(0), C.c_int(0)
+    assert L.nsdf_png_load(p.encode(), out.ctypes.data, out.size, C.byref(ww), C.byref(hh)) == 0
+    assert np.array_equal(out.reshape(h, w), tex[::-1, ::-1])
+    q = str(tmp_path / "a.ppm")
+    assert L.nsdf_ppm_save(q.encode(), tex.ctypes.data, w, h) == 0
+    raw = open(q, "rb").read()
+    hdr = f"P6\n{w}\n{h}\n255\n".encode()   # helper_image.h:265-274
+    assert raw.startswith(hdr) and len(raw) == len(hdr) + 3 * w * h
+    rgb = np.frombuffer(raw[len(hdr):], dtype=np.uint8).reshape(h, w, 3)
+    assert np.array_equal(rgb[..., 0], tex & 0xFF) and np.array_equal(rgb[..., 2], (tex >> 16) & 0xFF)
+
+
+def test_camera_helper_matches_oracle(built):
+    capi = _capi()
+    L = capi.lib()
+    for rx, ry, t in [(0, 0, (0, 0, -2)), (30, 45, (0, 0, -2)), (-10, 200, (0.1, -0.2, -3)), (0, 5.625, (0, 0, -2))]:
+        cam = capi.Camera()
+        L.nsdf_camera_from_view(rx, ry, t[0], t[1], t[2], 7, C.byref(cam))
+        iv, nm = oracle.view_matrices(rx, ry, t)
+        assert cam.frame == 7
+        assert np.array_equal(np.array(cam.inv_view[:], dtype=np.float32), iv)   # same formulae -> same bits
+        np.testing.assert_allclose(np.array(cam.normal[:], dtype=np.float32), nm, atol=2e-6)
+    cam = capi.Camera()
+    L.nsdf_camera_from_view(0, 0, 0, 0, -2, 0, C.byref(cam))
+    assert list(cam.inv_view[:]) == [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 2]
+    assert list(cam.normal[:]) == [1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, -2, 0, 0, 0, 1]
+
+
+def test_oracle_render_small_frame(built):
+    """Renderer restatement: determinism, thread invariance, query accounting, max_steps rule."""
+    m = oracle.Model.from_h5(model_path("car_1"))
+    iv, nm = oracle.view_matrices()
+    a = oracle.render(m, iv, nm, 64, 64, nthreads=1)
+    b = oracle.render(m, iv, nm, 64, 64, nthreads=4)
+    assert np.array_equal(a["image"], b["image"]) and a["queries"] == b["queries"]
+    hits = int(a["hit"].sum())
+    assert 200 < hits < 2000
+    assert a["queries"] == int(a["steps"].sum()) + 4 * hits
+    assert np.all((a["image"] != 0) <= (a["hit"] != 0))
+    assert np.all((a["image"][a["hit"] != 0] >> 24) == 255)   # facing colour has alpha 255
+    c = oracle.render(m, iv, nm, 64, 64, max_steps=8)
+    assert int(c["steps"].max()) <= 8 and int(c["hit"].sum()) < hits
+    # HEAD scene (manySphere union) shows more surface than the tanh scene
+    d = oracle.render(m, iv, nm, 64, 64, scene=oracle.SCENE_MANYSPHERE)
+    assert int(d["hit"].sum()) > hits
+
+
+def test_oracle_workload_characterisation(built):
+    """SURVEY App. C planning numbers for car_1 512x512 (independent numpy probe):
+    2 416 iterations, 3 126 923 queries, 37 897 hit pixels -- allow the probe's tanh/rsqrt slack."""
+    m = oracle.Model.from_h5(model_path("car_1"))
+    iv, nm = oracle.view_matrices()
+    r = oracle.render(m, iv, nm, 512, 512)
+    assert abs(int(r["hit"].sum()) - 37897) <= 40
+    assert abs(r["queries"] - 3126923) / 3126923 < 2e-3
