@@ -24,9 +24,10 @@ constexpr uint32_t B_LBO = 512;            // k-chunk (8 elements) stride
 constexpr uint32_t B_SBO = 128;            // 8-row group stride
 constexpr uint32_t B_MMA_BYTES = 1024;     // one K = 16 slice (two k-chunks)
 
-// byte offset of element (n, k) inside one layer's B image
-__host__ __device__ constexpr uint32_t b_elem_offset(int n, int k) {
-    return (uint32_t)(k >> 3) * B_LBO + (uint32_t)(n >> 3) * B_SBO + (uint32_t)(n & 7) * 16u + (uint32_t)(k & 7) * 2u;
+// byte offset of element (n, k) inside a B image of `rows` rows (k-chunk stride = rows * 16 bytes)
+__host__ __device__ constexpr uint32_t b_elem_offset(int n, int k, int rows = 32) {
+    return (uint32_t)(k >> 3) * (uint32_t)(rows * 16) + (uint32_t)(n >> 3) * B_SBO + (uint32_t)(n & 7) * 16u +
+           (uint32_t)(k & 7) * 2u;
 }
 
 // tcgen05 instruction descriptor, kind::f16, fp32 accumulate, A and B K-major.
@@ -38,8 +39,8 @@ __host__ __device__ constexpr uint32_t make_idesc(int fmt, int M, int N) {
 
 // shared-memory matrix descriptor (no swizzle, K-major): start>>4 [0,14), LBO>>4 [16,30),
 // SBO>>4 [32,46), version = 1 at [46,48).
-__device__ __forceinline__ uint64_t make_bdesc(uint32_t smem_addr) {
-    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(B_LBO >> 4) << 16) | ((uint64_t)(B_SBO >> 4) << 32) |
+__device__ __forceinline__ uint64_t make_bdesc(uint32_t smem_addr, uint32_t lbo = B_LBO) {
+    return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(B_SBO >> 4) << 32) |
            (1ull << 46);
 }
 
@@ -128,6 +129,12 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8])
                  : "memory");
 }
 
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
+    uint32_t r;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr) : "memory");
+    return r;
+}
+
 // relu + round-to-nearest pack: low half = lo, high half = hi.
 __device__ __forceinline__ uint32_t pack_relu_f16(float lo, float hi) {
     uint32_t d;
@@ -142,6 +149,17 @@ __device__ __forceinline__ uint32_t pack_relu_bf16(float lo, float hi) {
 __device__ __forceinline__ uint32_t pack_f16(float lo, float hi) {
     uint32_t d;
     asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    uint32_t d;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+// relu + round-toward-zero pack: for v > 0 the packed value never exceeds v, so v - packed >= 0
+__device__ __forceinline__ uint32_t pack_relu_rz_f16(float lo, float hi) {
+    uint32_t d;
+    asm("cvt.rz.relu.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
     return d;
 }
 __device__ __forceinline__ float f16lo_to_f32(uint32_t p) {
