@@ -43,22 +43,26 @@ struct TcParams {
     float* y;
     long long n;
     LatticeParams lp;
-    int dbg;
+    long long* trace;   // development: clock64 stamps of CTA 0 (threads 0 and 96), 2 x 512 entries, or null
 };
 
-template <int MODE>
-__global__ void __launch_bounds__(128) mlp_tc_kernel(const __grid_constant__ TcParams p) {
+constexpr int TC_THREADS = 128;   // thread t = query row t of the tile = TMEM lane t; thread 0 also issues the MMAs
+
+template <int MODE, int HALVES>
+__global__ void __launch_bounds__(TC_THREADS, 512 / tc::Cols<MODE>::TOTAL) mlp_tc_kernel(const __grid_constant__ TcParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ uint64_t s_bar_w, s_bar_mma;
+    __shared__ uint64_t s_bar_w, s_bar_d;
     __shared__ uint32_t s_tmem;
+    __shared__ __align__(16) uint64_t s_desc[(FUSED_MAX_SQ + 2) * 8];
     constexpr uint32_t TMEM_COLS = tc::Cols<MODE>::TOTAL;
 
     const int tid = threadIdx.x, warp = tid >> 5;
     if (tid == 0) {
         mbar_init(&s_bar_w, 1);
-        mbar_init(&s_bar_mma, 1);
+        mbar_init(&s_bar_d, 1);
         mbar_fence_init();
     }
+    tc::tile_build_desc<MODE>(s_desc, smem_u32(smem), p.n_sq, tid, TC_THREADS);
     __syncthreads();
     if (tid == 0) {
         mbar_arrive_expect_tx(&s_bar_w, p.image_bytes);
@@ -78,13 +82,21 @@ __global__ void __launch_bounds__(128) mlp_tc_kernel(const __grid_constant__ TcP
     tc::TileCtx c;
     c.tmem = s_tmem;
     c.t_row = c.tmem + ((uint32_t)(warp * 32) << 16);
-    c.img = smem_u32(smem);
-    c.bar = &s_bar_mma;
+    c.desc = s_desc;
+    c.bar_d = &s_bar_d;
+    c.bar_a = nullptr;
     c.phase = 0;
     c.n_sq = p.n_sq;
-    c.dbg = p.dbg;
     tc::tile_init_ones<MODE>(c);
     tc::mbar_wait_guard(&s_bar_w, 0);
+
+#ifdef NSDF_TC_TRACE
+    long long* trace = (p.trace && blockIdx.x == 0 && (tid == 0 || tid == 96)) ? p.trace + (tid ? 512 : 0) : nullptr;
+    int ti = 0;
+#define TC_STAMP() do { if (trace && ti < 500) trace[ti++] = clock64(); } while (0)
+#else
+#define TC_STAMP() do { } while (0)
+#endif
 
     const long long n_tiles = (p.n + 127) >> 7;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -94,21 +106,27 @@ __global__ void __launch_bounds__(128) mlp_tc_kernel(const __grid_constant__ TcP
             if (p.lp.enabled) lattice_point(p.lp, p.lp.first + row, x);
             else { x[0] = __ldg(p.x + 3 * row); x[1] = __ldg(p.x + 3 * row + 1); x[2] = __ldg(p.x + 3 * row + 2); }
         }
+        TC_STAMP();
         tc::tile_store_query<MODE>(c, x);
 #pragma unroll 1
-        for (int layer = -1; layer <= p.n_sq; ++layer) {
+        for (int step = 0; step <= p.n_sq + 1; ++step) {
+            TC_STAMP();
             tc::fence_before_sync();
             __syncthreads();
-            if (tid == 0) tc::tile_issue_layer<MODE>(c, layer);
-            tc::mbar_wait_guard(c.bar, c.phase);
+            TC_STAMP();
+            if (tid == 0) tc::tile_issue_step<MODE>(c, step);
+            TC_STAMP();
+            tc::mbar_wait_guard(c.bar_d, c.phase);
             c.phase ^= 1u;
             tc::fence_after_sync();
-            if (layer < p.n_sq) tc::tile_epilogue<MODE>(c);
+            TC_STAMP();
+            if (step <= p.n_sq) tc::tile_epilogue<MODE, HALVES>(c);
         }
         const float y = __uint_as_float(tc::tmem_ld1(c.t_row + tc::Cols<MODE>::D));
         tc::wait_ld();
         if (row < p.n) p.y[row] = y;
     }
+#undef TC_STAMP
 
     tc::fence_before_sync();
     __syncthreads();

@@ -110,7 +110,9 @@ int ensure_images(nsdf_model* m) {
     return NSDF_OK;
 }
 
-template <int MODE>
+long long* g_tc_trace = nullptr;   // set by nsdf_debug_tc_trace (development)
+
+template <int MODE, int HALVES>
 int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
            cudaStream_t stream) {
     TcParams p;
@@ -121,10 +123,10 @@ int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y,
     p.y = d_y;
     p.n = n;
     p.lp = lp;
-    p.dbg = env_int("NSDF_TC_DBG", 0);
+    p.trace = g_tc_trace;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<MODE, HALVES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_done = true;
     }
@@ -142,11 +144,13 @@ int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y,
     const long long n_tiles = (n + 127) / 128;
     const long long cap = (long long)sms * per_sm;
     const int grid = (int)(n_tiles < cap ? n_tiles : cap);
-    mlp_tc_kernel<MODE><<<grid, 128, smem, stream>>>(p);
+    mlp_tc_kernel<MODE, HALVES><<<grid, TC_THREADS, smem, stream>>>(p);
     return (int)cudaGetLastError();
 }
 
 }  // namespace
+
+void tc_set_trace(long long* d_buf) { g_tc_trace = d_buf; }
 
 const uint8_t* tc_image(nsdf_model* m, int mode, uint32_t* bytes) {
     if (ensure_images(m) != NSDF_OK) return nullptr;
@@ -163,10 +167,14 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
     if (rc) return rc;
     const TcDeviceImages* t = static_cast<const TcDeviceImages*>(m->d_tc);
     LatticeParams lp{lattice ? 1 : 0, res, lo, hi, (long long)first};
+    const int halves = env_int("NSDF_TC_EPI_HALVES", 1);
     switch (precision) {
-        case NSDF_PREC_TC_FP16: return launch<MODE_FP16>(m, t, d_x, d_y, n, lp, stream);
-        case NSDF_PREC_TC_BF16: return launch<MODE_BF16>(m, t, d_x, d_y, n, lp, stream);
-        case NSDF_PREC_TC_FP16X3: return launch<MODE_FP16X3>(m, t, d_x, d_y, n, lp, stream);
+        case NSDF_PREC_TC_FP16:
+            return halves == 2 ? launch<MODE_FP16, 2>(m, t, d_x, d_y, n, lp, stream) : launch<MODE_FP16, 1>(m, t, d_x, d_y, n, lp, stream);
+        case NSDF_PREC_TC_BF16:
+            return halves == 2 ? launch<MODE_BF16, 2>(m, t, d_x, d_y, n, lp, stream) : launch<MODE_BF16, 1>(m, t, d_x, d_y, n, lp, stream);
+        case NSDF_PREC_TC_FP16X3:
+            return halves == 2 ? launch<MODE_FP16X3, 2>(m, t, d_x, d_y, n, lp, stream) : launch<MODE_FP16X3, 1>(m, t, d_x, d_y, n, lp, stream);
         default: return NSDF_EINVAL;
     }
 }

@@ -144,6 +144,9 @@ int forward_dispatch(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int
 
 extern "C" {
 
+/* development hook (not in include/nsdf.h): clock64 trace buffer of the dense TC kernel, 1024 int64 */
+void nsdf_debug_tc_trace(long long* d_buf) { nsdf::tc_set_trace(d_buf); }
+
 const char* nsdf_version(void) { return "nsdf-b200 0.1 (sm_100a)"; }
 
 const char* nsdf_error_string(int status) {

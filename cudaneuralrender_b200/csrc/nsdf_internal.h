@@ -52,6 +52,7 @@ void render_release(nsdf_model* m);
 int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res, float lo,
                float hi, int64_t first, cudaStream_t stream);
 void tc_release(nsdf_model* m);
+void tc_set_trace(long long* d_buf);
 // device pointer + size of the tensor-core weight image of one rung (tc_mlp.cuh MODE_*), built lazily
 const uint8_t* tc_image(nsdf_model* m, int mode, uint32_t* bytes);
 

@@ -79,15 +79,15 @@ template <int MODE> __device__ __forceinline__ float unpack_hi(uint32_t p) {
 }
 template <int MODE> __device__ __forceinline__ uint32_t ones_word() { return MODE == MODE_BF16 ? 0x3F803F80u : 0x3C003C00u; }
 
-// Per-CTA-slot state of the evaluator.  All 128 threads of the slot hold the same values except t_row.
+// Per-CTA-slot state of the evaluator.  All threads of the slot hold the same values except t_row.
 struct TileCtx {
     uint32_t tmem;        // TMEM base of this slot (lane 0)
     uint32_t t_row;       // tmem + (lane quadrant of this warp << 16)
-    uint32_t img;         // shared-memory address of the weight image
-    uint64_t* bar;        // MMA-complete mbarrier of this slot
-    uint32_t phase;       // its running parity
+    const uint64_t* desc; // shared-memory table of B descriptors: [step][8], step = layer + 1
+    uint64_t* bar_d;      // "accumulator ready" mbarrier (tcgen05.commit arrives)
+    uint64_t* bar_a;      // "A operand ready" mbarrier (one arrival per epilogue warp)
+    uint32_t phase;       // running parity of the barrier this role waits on
     int n_sq;
-    int dbg;              // development knobs (NSDF_TC_DBG): 1 no LDTM, 2 no STTM, 4 no MMA, 8 one MMA per layer
 };
 
 // Writes the constant ones block of this thread's row.  Call once after TMEM allocation.
@@ -98,45 +98,64 @@ __device__ __forceinline__ void tile_init_ones(const TileCtx& c) {
     wait_st();
 }
 
-// Issues the MMAs of one layer and commits them to the slot barrier.  ONE thread.
-//   layer: -1 = layer 0, 0..n_sq-1 = hidden, n_sq = last.
+// MMAs of one step: count, and for MMA j the A operand column and the B descriptor.
+//   step 0 = layer 0 (1 MMA), steps 1..n_sq = hidden, step n_sq+1 = last.
+template <int MODE> __host__ __device__ constexpr int mmas_in_step(int step) {
+    return step == 0 ? 1 : (MODE == MODE_FP16X3 ? 7 : 3);
+}
+template <int MODE> __host__ __device__ constexpr uint32_t mma_a_col(int j) {
+    // hi k0-15, hi k16-31, ones | lo k0-15, lo k16-31 (x W_hi) | hi k0-15, hi k16-31 (x W_lo)
+    return j == 0 ? Cols<MODE>::A_HI : j == 1 ? Cols<MODE>::A_HI + 8 : j == 2 ? Cols<MODE>::ONES
+         : j == 3 ? Cols<MODE>::A_LO : j == 4 ? Cols<MODE>::A_LO + 8 : j == 5 ? Cols<MODE>::A_HI : Cols<MODE>::A_HI + 8;
+}
+// Fills the descriptor table (any number of threads; entry e = step * 8 + j).
 template <int MODE>
-__device__ __forceinline__ void tile_issue_layer(const TileCtx& c, int layer) {
+__device__ __forceinline__ void tile_build_desc(uint64_t* table, uint32_t img, int n_sq, int tid, int nthreads) {
+    const ImageLayout L = image_layout(n_sq, MODE);
+    for (int e = tid; e < (n_sq + 2) * 8; e += nthreads) {
+        const int step = e >> 3, j = e & 7;
+        uint64_t d = 0;
+        if (j < mmas_in_step<MODE>(step)) {
+            if (step == 0) {
+                d = make_bdesc(img + L.b0);
+            } else if (step <= n_sq) {
+                const uint32_t bh = img + L.hid_hi + (uint32_t)(step - 1) * IMG_HID_HI_BYTES;
+                const uint32_t bl = img + L.hid_lo + (uint32_t)(step - 1) * IMG_HID_LO_BYTES;
+                const uint32_t a = j < 3 ? bh + 1024u * j : j < 5 ? bh + 1024u * (j - 3) : bl + 1024u * (j - 5);
+                d = make_bdesc(a);
+            } else {
+                const uint32_t bh = img + L.last_hi, bl = img + L.last_lo;
+                const uint32_t a = j < 3 ? bh + 512u * j : j < 5 ? bh + 512u * (j - 3) : bl + 512u * (j - 5);
+                d = make_bdesc(a, LAST_LBO);
+            }
+        }
+        table[e] = d;
+    }
+}
+
+// Issues the MMAs of one step and commits them to bar_d.  ONE thread (the MMA warp's lane 0).
+template <int MODE>
+__device__ __forceinline__ void tile_issue_step(const TileCtx& c, int step) {
     constexpr uint32_t ID32 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 32);
     constexpr uint32_t ID16 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 16);
-    const ImageLayout L = image_layout(c.n_sq, MODE);
-    const uint32_t tD = c.tmem + Cols<MODE>::D, tA = c.tmem + Cols<MODE>::A_HI, tL = c.tmem + Cols<MODE>::A_LO;
+    const uint32_t idesc = step > c.n_sq ? ID16 : ID32;
+    const uint64_t* d = c.desc + step * 8;
+    const uint32_t tD = c.tmem + Cols<MODE>::D;
     fence_after_sync();
-    if (c.dbg & 4) { mma_commit(c.bar); return; }
-    if (layer < 0) {
-        mma_ts(tD, tA, make_bdesc(c.img + L.b0), ID32, 0u);
-    } else if (layer < c.n_sq) {
-        const uint32_t bh = c.img + L.hid_hi + (uint32_t)layer * IMG_HID_HI_BYTES;
-        mma_ts(tD, tA, make_bdesc(bh), ID32, 0u);
-        if (c.dbg & 8) { mma_commit(c.bar); return; }
-        mma_ts(tD, tA + 8, make_bdesc(bh + 1024), ID32, 1u);
-        mma_ts(tD, tA + 16, make_bdesc(bh + 2048), ID32, 1u);           // ones block x bias rows
-        if (MODE == MODE_FP16X3) {
-            const uint32_t bl = c.img + L.hid_lo + (uint32_t)layer * IMG_HID_LO_BYTES;
-            mma_ts(tD, tL, make_bdesc(bh), ID32, 1u);
-            mma_ts(tD, tL + 8, make_bdesc(bh + 1024), ID32, 1u);
-            mma_ts(tD, tA, make_bdesc(bl), ID32, 1u);
-            mma_ts(tD, tA + 8, make_bdesc(bl + 1024), ID32, 1u);
-        }
-    } else {
-        const uint32_t bh = c.img + L.last_hi;
-        mma_ts(tD, tA, make_bdesc(bh, LAST_LBO), ID16, 0u);
-        mma_ts(tD, tA + 8, make_bdesc(bh + 512, LAST_LBO), ID16, 1u);
-        mma_ts(tD, tA + 16, make_bdesc(bh + 1024, LAST_LBO), ID16, 1u);
-        if (MODE == MODE_FP16X3) {
-            const uint32_t bl = c.img + L.last_lo;
-            mma_ts(tD, tL, make_bdesc(bh, LAST_LBO), ID16, 1u);
-            mma_ts(tD, tL + 8, make_bdesc(bh + 512, LAST_LBO), ID16, 1u);
-            mma_ts(tD, tA, make_bdesc(bl, LAST_LBO), ID16, 1u);
-            mma_ts(tD, tA + 8, make_bdesc(bl + 512, LAST_LBO), ID16, 1u);
-        }
+    mma_ts(tD, c.tmem + mma_a_col<MODE>(0), d[0], idesc, 0u);
+    if (step > 0) {
+#pragma unroll
+        for (int j = 1; j < mmas_in_step<MODE>(1); ++j) mma_ts(tD, c.tmem + mma_a_col<MODE>(j), d[j], idesc, 1u);
     }
-    mma_commit(c.bar);
+    mma_commit(c.bar_d);
+}
+
+// One elected arrival per epilogue warp on bar_a, after the warp's tcgen05.st have completed.
+__device__ __forceinline__ void tile_signal_a(const TileCtx& c) {
+    fence_before_sync();
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0)
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(c.bar_a)) : "memory");
 }
 
 // This thread's query -> the layer-0 A operand (8 packed columns).
@@ -160,32 +179,34 @@ __device__ __forceinline__ void tile_store_query(const TileCtx& c, const float (
 }
 
 // Epilogue of layer 0 / a hidden layer: D -> relu -> 16-bit A operand of the next layer.
-template <int MODE>
+// HALVES = 2 processes 16 accumulator columns at a time (smaller live register set).
+template <int MODE, int HALVES = 1>
 __device__ __forceinline__ void tile_epilogue(const TileCtx& c) {
-    uint32_t v[32];
-    if (c.dbg & 1) {
+    constexpr int NC = 32 / HALVES;          // accumulator columns per pass
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = c.phase + j;
-    } else {
-        tmem_ld32(c.t_row + Cols<MODE>::D, v);
+    for (int half = 0; half < HALVES; ++half) {
+        uint32_t v[NC];
+        if (HALVES == 1) tmem_ld32(c.t_row + Cols<MODE>::D, reinterpret_cast<uint32_t(&)[32]>(v));
+        else tmem_ld16(c.t_row + Cols<MODE>::D + 16 * half, reinterpret_cast<uint32_t(&)[16]>(v));
         wait_ld();
-    }
-    uint32_t ahi[16];
-    if (MODE != MODE_FP16X3) {
+        uint32_t ahi[NC / 2], alo[NC / 2];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) ahi[j] = pack2_relu<MODE>(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
-        if (!(c.dbg & 2)) tmem_st16(c.t_row + Cols<MODE>::A_HI, ahi);
-        else if (ahi[0] == 0x12345u && ahi[7] == 0x777u && ahi[15] == 3u) __trap();
-    } else {
-        uint32_t alo[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
+        for (int j = 0; j < NC / 2; ++j) {
             const float h0 = __uint_as_float(v[2 * j]), h1 = __uint_as_float(v[2 * j + 1]);
-            ahi[j] = pack_relu_rz_f16(h0, h1);                 // hi <= h for h > 0, hi = 0 for h <= 0
-            alo[j] = pack_relu_f16(h0 - f16lo_to_f32(ahi[j]), h1 - f16hi_to_f32(ahi[j]));   // >= 0 where h > 0
+            if (MODE != MODE_FP16X3) {
+                ahi[j] = pack2_relu<MODE>(h0, h1);
+            } else {
+                ahi[j] = pack_relu_rz_f16(h0, h1);                 // hi <= h for h > 0, hi = 0 for h <= 0
+                alo[j] = pack_relu_f16(h0 - f16lo_to_f32(ahi[j]), h1 - f16hi_to_f32(ahi[j]));   // >= 0 where h > 0
+            }
         }
-        tmem_st16(c.t_row + Cols<MODE>::A_HI, ahi);
-        tmem_st16(c.t_row + Cols<MODE>::A_LO, alo);
+        if (HALVES == 1) {
+            tmem_st16(c.t_row + Cols<MODE>::A_HI, reinterpret_cast<uint32_t(&)[16]>(ahi));
+            if (MODE == MODE_FP16X3) tmem_st16(c.t_row + Cols<MODE>::A_LO, reinterpret_cast<uint32_t(&)[16]>(alo));
+        } else {
+            tmem_st8(c.t_row + Cols<MODE>::A_HI + 8 * half, reinterpret_cast<uint32_t(&)[8]>(ahi));
+            if (MODE == MODE_FP16X3) tmem_st8(c.t_row + Cols<MODE>::A_LO + 8 * half, reinterpret_cast<uint32_t(&)[8]>(alo));
+        }
     }
     wait_st();
 }

@@ -147,6 +147,56 @@ def test_lattice_matches_explicit_points(env):
     assert np.array_equal(_bits(part), _bits(ref[1000:1777]))
 
 
+# Stated bounds of the tensor-core rungs (absolute SDF error against the oracle; include/nsdf.h):
+# FP16X3 meets the north star's fp32 bound of 1e-4, the single-pass rungs carry the looser ones.
+TC_BOUNDS = {"PREC_TC_FP16X3": 1e-4, "PREC_TC_FP16": 4e-3, "PREC_TC_BF16": 5e-2}
+
+
+@pytest.mark.parametrize("name", MODELS)
+def test_tc_rungs_within_stated_bounds(env, name):
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, name)
+    x = np.random.default_rng(7).uniform(-1, 1, (200_000, 3)).astype(np.float32)
+    x[:8] = [[0, 0, 0], [1, 1, 1], [-1, -1, -1], [1, -1, 1], [0.5, 0, 0], [0, -0.5, 0], [0, 0, 0.25], [1e-6, -1e-6, 1e-3]]
+    ref = oracle.mlp_forward(om, x).ravel().astype(np.float64)
+    xd = torch.from_numpy(x).cuda().contiguous()
+    for pname, bound in TC_BOUNDS.items():
+        y = nn.forward_tensor(xd, getattr(host, pname)).cpu().numpy().astype(np.float64)
+        err = np.abs(y - ref)
+        assert np.isfinite(y).all(), pname
+        assert err.max() <= bound, (name, pname, err.max())
+
+
+@pytest.mark.parametrize("n", [1, 127, 128, 129, 4097, 1000003])
+def test_tc_ragged_sizes(env, n):
+    """Tile tails: rows past n are computed on zeros and never stored."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "car_1")
+    x = np.random.default_rng(n).uniform(-1, 1, (n, 3)).astype(np.float32)
+    ref = oracle.mlp_forward(om, x).ravel()
+    xd = torch.from_numpy(x).cuda().contiguous()
+    guard = torch.full((n + 256,), 12345.0, dtype=torch.float32, device="cuda")
+    nn.forward_tensor(xd, host.PREC_TC_FP16X3, out=guard)
+    g = guard.cpu().numpy()
+    assert np.abs(g[:n].astype(np.float64) - ref).max() <= 1e-4
+    assert (g[n:] == 12345.0).all()
+
+
+def test_tc_lattice_matches_explicit_points(env):
+    torch, host = env["torch"], env["host"]
+    nn, _ = _load(env, "plane_1")
+    res = 48
+    idx = np.arange(res ** 3)
+    c = (-1.0 + 2.0 * (np.stack([idx % res, (idx // res) % res, idx // (res * res)], 1) + 0.5) / res).astype(np.float32)
+    # lattice points are generated with one fma in-kernel and may differ from numpy's by an ulp; a
+    # single-pass rung rounds activations to 16 bits, so an ulp of input can move the output by a
+    # rounding quantum: the tolerance is the rung's own bound there
+    for prec, tol in ((host.PREC_TC_FP16, 4e-3), (host.PREC_TC_FP16X3, 1e-5)):
+        a = nn.forward_lattice(res, precision=prec).cpu().numpy()
+        b = nn.forward_tensor(torch.from_numpy(c).cuda().contiguous(), prec).cpu().numpy()
+        assert np.abs(a - b).max() <= tol, prec
+
+
 def _render_both(env, name, W, H, matcap_name=None, scene=0, max_steps=6000, rx=0.0, ry=0.0, flags=0, frame=0,
                  evict_steps=0):
     torch, host, oracle = env["torch"], env["host"], env["oracle"]

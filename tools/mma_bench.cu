@@ -1,0 +1,68 @@
+// Development microbenchmark: issue rate of tcgen05.mma.kind::f16 (A from TMEM, B from smem) for small N.
+// nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o mma_bench mma_bench.cu ; ./mma_bench
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../cudaneuralrender_b200/csrc/mlp_fp32.cuh"
+#include "../cudaneuralrender_b200/csrc/tc_common.cuh"
+using namespace nsdf;
+
+// ctas_per_sm CTAs of 128 threads; each allocates 64 TMEM columns and issues `iters` batches of `per` MMAs + commit + wait.
+__global__ void __launch_bounds__(128) bench(int N, int per, int iters, int lbo, long long* out) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t s_tmem;
+    for (int i = threadIdx.x; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    __syncthreads();
+    if (threadIdx.x < 32) tc::tmem_alloc(&s_tmem, 64);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = s_tmem;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    long long t0 = 0, t1 = 0;
+    if (threadIdx.x == 0) {
+        const uint32_t idesc = tc::make_idesc(0, 128, N);
+        const uint64_t d = tc::make_bdesc(smem_u32(smem), lbo);
+        uint32_t phase = 0;
+        t0 = clock64();
+        for (int it = 0; it < iters; ++it) {
+            for (int j = 0; j < per; ++j) tc::mma_ts(tmem, tmem + 32 + 8 * (j & 1), d, idesc, j ? 1u : 0u);
+            tc::mma_commit(&bar);
+            tc::mbar_wait_guard(&bar, phase);
+            phase ^= 1;
+        }
+        t1 = clock64();
+        out[blockIdx.x] = t1 - t0;
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 64);
+}
+
+int main() {
+    long long* d_out;
+    cudaMalloc(&d_out, 148 * 8 * 8);
+    cudaFuncSetAttribute(bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    const int Ns[] = {16, 32, 64, 128, 256};
+    for (int ctas = 1; ctas <= 4; ctas *= 2)
+        for (int N : Ns) {
+            if (N > 32 && false) continue;
+            for (int per : {1, 3, 16, 64}) {
+                const int iters = 256 / per > 8 ? 256 / per : 8;
+                const int smem = 48 * 1024;   // <= 4 CTAs/SM
+                bench<<<148 * ctas, 128, smem>>>(N, per, iters, N * 16, d_out);
+                cudaError_t e = cudaDeviceSynchronize();
+                if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
+                long long h[148 * 4];
+                cudaMemcpy(h, d_out, sizeof(long long) * 148 * ctas, cudaMemcpyDeviceToHost);
+                double avg = 0;
+                for (int i = 0; i < 148 * ctas; ++i) avg += h[i];
+                avg /= 148 * ctas;
+                printf("ctas/SM %d N %3d per-batch %2d : %.1f cycles/batch  %.1f cycles/MMA (SM-level %.1f cycles/MMA)\n", ctas, N, per,
+                       avg / iters, avg / iters / per, avg / iters / per / ctas);
+            }
+        }
+    return 0;
+}
