@@ -172,18 +172,13 @@ def run_native(args):
 
     for _ in range(Wm):
         step()
-    # ---- untimed accounting pass: Q_frame, hits, and the share of the throughput kernel
+    # ---- untimed accounting pass: Q_frame, hits, rays handed to the latency warps
     stats.zero_()
-    host._state.flags = capi.RENDER_PHASE_THROUGHPUT
-    host.render_kernel(frame, W, H, nn, matcap, stats=stats)
-    torch.cuda.synchronize()
-    sA = stats.cpu().numpy().copy()
-    host._state.flags = capi.RENDER_PHASE_LATENCY
+    host._state.flags = 0
     host.render_kernel(frame, W, H, nn, matcap, stats=stats)
     torch.cuda.synchronize()
     sAB = stats.cpu().numpy().copy()
-    q_frame, hits, q_A = int(sAB[0]), int(sAB[1]), int(sA[0])
-    evicted = int(sA[3])
+    q_frame, hits, evicted = int(sAB[0]), int(sAB[1]), int(sAB[3])
 
     # ---- timed region: K steps, device time per step, L2 flushed between steps
     sampler = ClockSampler(local)
@@ -207,19 +202,16 @@ def run_native(args):
     fps = world * K / (total_ms * 1e-3)
     q_total = sum_over_ranks(float(q_frame))
 
-    # ---- per-kernel timing (same launches, split by phase flags so events can sit between them)
-    evp = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
-    for i in range(K):
+    # ---- A/B: the earlier two-launch schedule (throughput kernel, then latency kernel), same frame
+    evp = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(min(K, 5))]
+    for e in evp:
         flush.zero_()
-        evp[i][0].record()
-        step(capi.RENDER_PHASE_THROUGHPUT)
-        evp[i][1].record()
-        step(capi.RENDER_PHASE_LATENCY)
-        evp[i][2].record()
+        e[0].record()
+        step(capi.RENDER_TWO_KERNELS)
+        e[1].record()
     torch.cuda.synchronize()
     host._state.flags = 0
-    tA = sum(e[0].elapsed_time(e[1]) for e in evp) / K
-    tB = sum(e[1].elapsed_time(e[2]) for e in evp) / K
+    t_two = sum(e[0].elapsed_time(e[1]) for e in evp) / len(evp)
 
     # ---- end to end through the C ABI with host buffers (pinned): matcap H2D + frame D2H every step
     mc_host = torch.from_numpy(matcap.hostData.view(np.int32)).pin_memory()
@@ -278,7 +270,7 @@ def run_native(args):
         return
 
     pk = peaks()
-    achieved = q_A * FLOP_PER_QUERY / (tA * 1e-3) / 1e12
+    achieved = q_frame * FLOP_PER_QUERY / (ms_per_step * 1e-3) / 1e12
     hbm_bytes = 4 * W * H + 4 * hits + nn.getNumWeightParams() * 4 + nn.getNumBiasParams() * 4
     line = {
         "metric": "1080p frames/sec (plane_1, FD normals + matcap)", "value": fps, "unit": "frames/s", "n_gpus": world,
@@ -292,9 +284,10 @@ def run_native(args):
         "queries_per_s": q_total * K / (total_ms * 1e-3), "queries_per_frame": q_frame, "hit_pixels": hits,
         "evicted_rays": evicted,
         "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": 2 * K,
-        "kernels": {"trace_throughput_kernel": {"ms": tA, "queries": q_A}, "trace_latency_kernel": {"ms": tB, "queries": q_frame - q_A}},
-        "roofline": {"kernel": "trace_throughput_kernel", "bound": "tensor", "achieved": achieved,
+        "gpu_launches": K,
+        "kernels": {"trace_coop_kernel": {"ms": ms_per_step, "queries": q_frame},
+                    "two_launch_schedule_ms": t_two},
+        "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved,
                      "peak": pk["tflops_burst"], "unit": "TFLOP/s", "frac": achieved / pk["tflops_burst"],
                      "traffic": None, "peak_source": pk["source"],
                      "note": "algorithmic FLOP = queries x 14592; fp32 ALU rung, its own ceiling is ~74 TFLOP/s",

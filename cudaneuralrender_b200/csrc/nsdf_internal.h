@@ -25,6 +25,7 @@ struct nsdf_model {
     unsigned int* d_counters = nullptr;   // [0] pixel counter [1] queue tail [2] queue head [3] pad
     void* d_queue = nullptr;
     size_t queue_capacity = 0;
+    unsigned int frame_seq = 0;           // publication stamp of the fused tracer's queue entries
     nsdf_render_stats* d_stats_scratch = nullptr;
     float* d_act[2] = {nullptr, nullptr}; // ping-pong activations for the per-layer path
     size_t act_capacity = 0;              // floats per buffer

@@ -39,7 +39,7 @@ mlp_fp32_thread_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int 
 
 // Warp-cooperative fused MLP on a dense batch (exercises the latency evaluator of the tracer).
 template <int R>
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(1024, 1)
 mlp_fp32_warp_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_sq, const float* __restrict__ xin,
                      float* __restrict__ yout, long long n, const LatticeParams lp) {
     extern __shared__ __align__(16) float s_w[];
@@ -98,19 +98,22 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
     const int sms = m->sm_count > 0 ? m->sm_count : 148;
     cudaError_t e;
     if (precision == NSDF_PREC_FP32_WARP) {
-        constexpr int R = 4;
-        const int threads = 512;
-        const size_t smem = m->blob_bytes + (threads / 32) * 2 * R * WARP_ACT_STRIDE * sizeof(float);
-        static bool attr_done = false;
-        if (!attr_done) {
-            e = cudaFuncSetAttribute(mlp_fp32_warp_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-            if (e != cudaSuccess) return (int)e;
-            attr_done = true;
-        }
-        long long want = (n + (long long)(threads / 32) * R - 1) / ((long long)(threads / 32) * R);
-        const int grid = (int)(want < sms ? want : sms);
-        mlp_fp32_warp_kernel<R><<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
-        return (int)cudaGetLastError();
+        const int R = env_int("NSDF_FP32_WARP_R", 4);
+        const int threads = env_int("NSDF_FP32_WARP_THREADS", 512);
+        const int ctas = env_int("NSDF_FP32_WARP_CTAS", 1);
+        auto go = [&](auto kern, int r) -> int {
+            const size_t smem = m->blob_bytes + (threads / 32) * 2 * r * WARP_ACT_STRIDE * sizeof(float);
+            cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e2 != cudaSuccess) return (int)e2;
+            long long want = (n + (long long)(threads / 32) * r - 1) / ((long long)(threads / 32) * r);
+            const long long cap = (long long)sms * ctas;
+            const int grid = (int)(want < cap ? want : cap);
+            kern<<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+            return (int)cudaGetLastError();
+        };
+        if (R == 8) return go(mlp_fp32_warp_kernel<8>, 8);
+        if (R == 2) return go(mlp_fp32_warp_kernel<2>, 2);
+        return go(mlp_fp32_warp_kernel<4>, 4);
     }
     const int P = env_int("NSDF_FP32_P", 2);
     const size_t smem = m->blob_bytes;

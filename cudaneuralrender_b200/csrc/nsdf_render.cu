@@ -8,6 +8,8 @@
 
 #include "nsdf_internal.h"
 #include "render_kernels.cuh"
+#include "trace_coop.cuh"
+#include "trace_fused.cuh"
 
 namespace nsdf {
 
@@ -23,6 +25,14 @@ static size_t latency_smem(const nsdf_model* m) {
     return m->blob_bytes + (LAT_THREADS / 32) * 2 * LAT_R * WARP_ACT_STRIDE * sizeof(float);
 }
 
+static size_t fused_smem(const nsdf_model* m) {
+    return m->blob_bytes + (FUSED_THREADS / 32) * 2 * FUSED_R * WARP_ACT_STRIDE * sizeof(float);
+}
+
+static size_t coop_smem(const nsdf_model* m) {
+    return m->blob_bytes + (COOP_THREADS / 32) * 2 * COOP_R * WARP_ACT_STRIDE * sizeof(float);
+}
+
 static int ensure_scratch(nsdf_model* m, size_t queue_entries) {
     cudaError_t e;
     if (!m->d_counters) {
@@ -34,6 +44,8 @@ static int ensure_scratch(nsdf_model* m, size_t queue_entries) {
         m->d_queue = nullptr;
         m->queue_capacity = 0;
         e = cudaMalloc(&m->d_queue, queue_entries * sizeof(StragglerEntry));
+        if (e != cudaSuccess) return (int)e;
+        e = cudaMemset(m->d_queue, 0, queue_entries * sizeof(StragglerEntry));   // no entry carries a live frame stamp
         if (e != cudaSuccess) return (int)e;
         m->queue_capacity = queue_entries;
     }
@@ -83,16 +95,26 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     if ((long long)my_tiles * TILE_PIXELS >= (1LL << 32)) return NSDF_EINVAL;
     rp.total_idx = (unsigned int)my_tiles * TILE_PIXELS;
     rp.max_steps = opts->max_steps;
-    rp.evict_steps = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_EVICT_STEPS", 48);
     rp.stats = d_stats;
 
     const bool simple = (opts->flags & NSDF_RENDER_SIMPLE) != 0;
-    const bool straggler = !simple && !(opts->flags & NSDF_RENDER_NO_STRAGGLER);
+    const bool coop = !simple && !(opts->flags & (NSDF_RENDER_NO_STRAGGLER | NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
+                                                   NSDF_RENDER_TWO_KERNELS | NSDF_RENDER_QUEUE));
+    const bool coop_queue = coop && !(opts->flags & NSDF_RENDER_NO_QUIET_SMS) && env_int("NSDF_COOP_QUEUE", 1) != 0;
+    const bool straggler = !simple && (coop ? coop_queue : !(opts->flags & NSDF_RENDER_NO_STRAGGLER));
+    const bool two_kernel = straggler && (opts->flags & (NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
+                                                         NSDF_RENDER_TWO_KERNELS)) != 0;
+    // fused kernel: only the long tail leaves the throughput lanes early; two-kernel path: its old default
+    rp.evict_steps = opts->evict_steps > 0 ? opts->evict_steps
+                                           : (two_kernel ? env_int("NSDF_EVICT_STEPS", 48) : env_int("NSDF_FUSED_EVICT_STEPS", 32));
+    rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_FUSED_EVICT_HI", 256);
     size_t qcap = 0;
     if (straggler) {
-        qcap = rp.total_idx;
-        const size_t cap_max = (size_t)env_int("NSDF_QUEUE_MAX", 4 << 20);
-        if (qcap > cap_max) qcap = cap_max;
+        qcap = rp.total_idx;   // every ray is queued at most once
+        if (two_kernel) {
+            const size_t cap_max = (size_t)env_int("NSDF_QUEUE_MAX", 4 << 20);
+            if (qcap > cap_max) qcap = cap_max;
+        }
     }
     int rc = ensure_scratch(m, qcap);
     if (rc) return rc;
@@ -119,12 +141,55 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         if (e != cudaSuccess) return (int)e;
         e = cudaFuncSetAttribute(trace_latency_kernel<LAT_R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(trace_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(trace_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
         attr_done = true;
     }
 
     if (simple) {
         const unsigned int blocks = (rp.total_idx + 127u) / 128u;
         trace_simple_kernel<<<blocks, 128, m->blob_bytes, stream>>>(rp);
+        return (int)cudaGetLastError();
+    }
+
+    if (coop) {
+        // ---- default: one persistent launch, every warp marches COOP_R rays cooperatively (trace_coop.cuh)
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
+        if (e != cudaSuccess) return (int)e;
+        if (occ < 1) return NSDF_EUNSUPPORTED;
+        const unsigned int per_cta = (COOP_THREADS / 32) * COOP_R;
+        const unsigned int cap = (unsigned int)(sms * occ);
+        const unsigned int want = (rp.total_idx + per_cta - 1) / per_cta;
+        m->frame_seq = m->frame_seq + 1u ? m->frame_seq + 1u : 1u;
+        rp.frame_seq = m->frame_seq;
+        rp.consumer_period = (unsigned int)env_int("NSDF_COOP_QUIET_PERIOD", 16);
+        rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_COOP_EVICT", 256);
+        trace_coop_kernel<<<want < cap ? want : cap, COOP_THREADS, coop_smem(m), stream>>>(rp);
+        return (int)cudaGetLastError();
+    }
+
+    if (!two_kernel) {
+        // ---- A/B: producer lanes + consumer warps through a queue (trace_fused.cuh); grid = co-resident CTAs
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_fused_kernel, FUSED_THREADS, fused_smem(m));
+        if (e != cudaSuccess) return (int)e;
+        if (occ < 1) return NSDF_EUNSUPPORTED;
+        const unsigned int cap = (unsigned int)(sms * occ);
+        const unsigned int want = (rp.total_idx + FUSED_THREADS - 1) / FUSED_THREADS;
+        const unsigned int grid = want < cap ? want : cap;
+        m->frame_seq = m->frame_seq + 1u ? m->frame_seq + 1u : 1u;
+        rp.frame_seq = m->frame_seq;
+        const unsigned int total_warps = grid * (FUSED_THREADS / 32);
+        unsigned int period = (unsigned int)env_int("NSDF_FUSED_CONSUMER_PERIOD", 16);
+        if (period > total_warps) period = total_warps;   // at least one consumer from the start
+        if (period < 2) period = total_warps >= 2 ? 2 : 0; // a lone warp produces first, then consumes
+        rp.consumer_period = straggler ? period : 0u;
+        const unsigned int consumers0 = period ? total_warps / period : 0u;
+        rp.queue_room = (unsigned int)env_int("NSDF_FUSED_ROOM", (int)(2u * FUSED_R * (consumers0 ? consumers0 : 1u)));
+        trace_fused_kernel<<<grid, FUSED_THREADS, fused_smem(m), stream>>>(rp);
         return (int)cudaGetLastError();
     }
 

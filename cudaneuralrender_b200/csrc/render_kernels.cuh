@@ -32,7 +32,8 @@ struct StragglerEntry {            // 48 bytes, 16-byte aligned
     int pix, steps;
     float px, py;
     float pz, dx, dy, dz;
-    float tfar, pad0, pad1, pad2;
+    float tfar, pad0, pad1;
+    unsigned int ready;         // == RenderParams::frame_seq once the entry is complete (fused kernel)
 };
 
 struct RenderParams {
@@ -49,7 +50,13 @@ struct RenderParams {
     int tile_rank, tile_world;
     unsigned int total_idx;        // pixel indices this call enumerates (my tiles * 4096)
     int max_steps, evict_steps;
-    unsigned int* pixel_counter;   // [0] next pixel index, [1] straggler tail, [2] straggler head
+    int evict_steps_hi;            // fused kernel: unconditional hand-over (evict_steps applies while the backlog is short)
+    unsigned int queue_room;       // fused kernel: backlog (tail - head) below which evict_steps applies
+    unsigned int* pixel_counter;   // [0] next pixel index, [1] straggler tail, [2] straggler head,
+                                   // [3] producer warps finished (fused kernel)
+    unsigned int frame_seq;        // publication stamp of straggler entries (fused kernel), never 0
+    unsigned int consumer_period;  // fused kernel: global warp w is a consumer from the start when
+                                   // w % consumer_period == consumer_period - 1 (0 = none)
     StragglerEntry* queue;
     unsigned int queue_capacity;
     nsdf_render_stats* stats;
@@ -169,7 +176,7 @@ __device__ __forceinline__ void evict_slot(RaySlot& s, bool do_evict, const Rend
         if (slot < rp.queue_capacity) {
             StragglerEntry e;
             e.pix = s.pix; e.steps = s.steps; e.px = s.p.x; e.py = s.p.y; e.pz = s.p.z;
-            e.dx = s.d.x; e.dy = s.d.y; e.dz = s.d.z; e.tfar = s.tfar; e.pad0 = e.pad1 = e.pad2 = 0.0f;
+            e.dx = s.d.x; e.dy = s.d.y; e.dz = s.d.z; e.tfar = s.tfar; e.pad0 = e.pad1 = 0.0f; e.ready = 0u;
             float4* dst = reinterpret_cast<float4*>(rp.queue + slot);
             const float4* src = reinterpret_cast<const float4*>(&e);
             dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];

@@ -1,0 +1,149 @@
+// =====================================================================================
+// trace_coop.cuh -- the default tracer: ONE persistent launch, every warp marches up to
+// COOP_R rays with the warp-cooperative evaluator (lane = neuron, mlp32_eval_warp).
+//
+// Replaces the host loop of render_kernel (src/volumeRender_kernel.cu:608-692) and its
+// per-iteration thrust::exclusive_scan + createBatch (:504-563): a warp's idle ray slots are
+// refilled from the global pixel counter by ballot compaction, so there is no batch to build.
+//
+// Why lane = neuron rather than lane = ray: one march step of a ray is a chain of nine dependent
+// layers.  With a ray per lane a step costs the whole warp ~9k instructions (~18 us on a busy SM),
+// which turns the few rays that need thousands of steps into tens of milliseconds;
+// with a neuron per lane a layer is a 32-deep FFMA chain and a step is ~1-2.5 us, at ~80 % of the
+// ray-per-lane instruction efficiency once COOP_R rays share every weight load.  All rays take the
+// same path, so nothing is queued or handed over, and the serial tail overlaps the bulk.
+// As rays finish and the pixels run out, the warp drops to the 4-, 2- and 1-ray evaluators.
+//
+// Per ray the arithmetic is that of render_kernels.cuh (slot_start / slot_update): frames are
+// bit-identical to the oracle.
+// =====================================================================================
+#pragma once
+#include "render_kernels.cuh"
+#include "trace_fused.cuh"   // fused_push / fused_pop (the straggler queue)
+
+namespace nsdf {
+
+constexpr int COOP_THREADS = 256;
+constexpr int COOP_R = 8;   // ray slots per warp (lanes 0..COOP_R-1 own them)
+
+// Evaluates the K lowest-ranked active rays of the warp.  src[j] = lane of the j-th active ray.
+template <int K>
+__device__ __forceinline__ float coop_eval(const float* s_w, int n_sq, float* abuf, const f3& q, const int (&src)[COOP_R],
+                                           int rank, int lane) {
+    float x[K][3], y[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+        x[j][0] = __shfl_sync(0xffffffffu, q.x, src[j]);
+        x[j][1] = __shfl_sync(0xffffffffu, q.y, src[j]);
+        x[j][2] = __shfl_sync(0xffffffffu, q.z, src[j]);
+    }
+    mlp32_eval_warp<K>(s_w, n_sq, abuf, x, y, lane);
+    float mine = y[0];
+#pragma unroll
+    for (int j = 1; j < K; ++j) mine = (rank == j) ? y[j] : mine;
+    return mine;
+}
+
+__device__ __forceinline__ unsigned int sm_id() {
+    unsigned int v;
+    asm("mov.u32 %0, %%smid;" : "=r"(v));
+    return v;
+}
+
+// rp.queue != nullptr enables the "quiet SM" scheme for the serial tail: rays that have marched
+// rp.evict_steps_hi steps are pushed to the straggler queue and continued by the warps of every
+// rp.consumer_period-th SM, which take no pixels of their own -- a lone long ray there is not slowed
+// by busy neighbours.  Warps that run out of pixels join the consumers.  Termination: every warp has
+// stopped producing (pixel_counter[3] == all warps) and the queue is empty.
+__global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __grid_constant__ RenderParams rp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* abuf = s_w + (rp.blob_bytes >> 2) + warp * (2 * COOP_R * WARP_ACT_STRIDE);
+    const unsigned int total_warps = gridDim.x * (COOP_THREADS / 32);
+    const bool use_queue = rp.queue != nullptr;
+
+    RaySlot slot;
+    slot.mode = -1;
+    LocalStats st = {0, 0, 0, 0, 0, 0};
+    // warp-uniform role state
+    bool producing = !(use_queue && rp.consumer_period && (sm_id() % rp.consumer_period) == rp.consumer_period - 1);
+    bool exhausted = !producing;
+    if (use_queue && !producing && lane == 0) atomicAdd(rp.pixel_counter + 3, 1u);
+    int poll = 0;
+    unsigned int idle = 0;
+
+    for (;;) {
+        // ---- refill idle ray slots (ballot compaction over the slot lanes)
+        while (!exhausted) {
+            const bool need = lane < COOP_R && slot.mode < 0;
+            const unsigned int m = __ballot_sync(0xffffffffu, need);
+            if (!m) break;
+            const int leader = __ffs(m) - 1;
+            const unsigned int cnt = __popc(m);
+            unsigned int base = 0;
+            if (lane == leader) base = atomicAdd(rp.pixel_counter, cnt);
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (need) {
+                const unsigned int idx = base + __popc(m & lanemask_lt());
+                if (idx < rp.total_idx) slot_start(slot, idx, rp, st);
+            }
+            if (base + cnt >= rp.total_idx) exhausted = true;
+        }
+        unsigned int act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
+        if (use_queue && exhausted) {
+            if (producing && !act) {          // out of pixels and rays: from now on a consumer
+                producing = false;
+                if (lane == 0) { __threadfence(); atomicAdd(rp.pixel_counter + 3, 1u); }
+            }
+            if (!producing && (!act || --poll <= 0)) {
+                fused_pop(slot, lane < COOP_R && slot.mode < 0, rp);
+                poll = 8;
+                act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
+            }
+            if (!act) {
+                unsigned int done = 0;
+                if (lane == 0) {
+                    const unsigned int fin = ld_volatile_u32(rp.pixel_counter + 3);
+                    const unsigned int tail = ld_volatile_u32(rp.pixel_counter + 1);
+                    const unsigned int head = ld_volatile_u32(rp.pixel_counter + 2);
+                    done = (fin >= total_warps && head >= tail) ? 1u : 0u;
+                }
+                if (__shfl_sync(0xffffffffu, done, 0)) break;
+                __nanosleep(200);
+                if (++idle > 50000000u) __trap();     // > 10 s without work: never hang the device
+                continue;
+            }
+            idle = 0;
+        } else if (!act) {
+            break;
+        }
+        const bool active = lane < COOP_R && slot.mode >= 0;
+        const int na = __popc(act);
+        const int rank = __popc(act & lanemask_lt());
+        int src[COOP_R];
+        {
+            unsigned int mm = act;
+#pragma unroll
+            for (int j = 0; j < COOP_R; ++j) {
+                src[j] = mm ? (__ffs(mm) - 1) : 0;
+                mm &= mm - 1u;
+            }
+        }
+        const f3 q = active ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
+        float mine;
+        if (na > 4) mine = coop_eval<8>(s_w, rp.n_sq, abuf, q, src, rank, lane);
+        else if (na > 2) mine = coop_eval<4>(s_w, rp.n_sq, abuf, q, src, rank, lane);
+        else if (na == 2) mine = coop_eval<2>(s_w, rp.n_sq, abuf, q, src, rank, lane);
+        else mine = coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane);
+        if (active) slot_update(slot, mine, q, rp, st);
+        // ---- long rays leave for the quiet SMs
+        if (use_queue && producing)
+            fused_push(slot, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.evict_steps_hi, rp, st);
+    }
+    flush_stats(st, rp.stats);
+}
+
+}  // namespace nsdf

@@ -129,8 +129,11 @@ typedef struct nsdf_render_opts {
 } nsdf_render_opts;
 
 #define NSDF_RENDER_SIMPLE 1u      /* one-thread-per-pixel kernel without refill (debug / A-B testing) */
-#define NSDF_RENDER_NO_STRAGGLER 2u /* keep every ray in the throughput kernel                          */
+#define NSDF_RENDER_NO_STRAGGLER 2u /* ray-per-lane kernel with refill, nothing handed to cooperative warps (A/B) */
 #define NSDF_RENDER_PHASE_THROUGHPUT 4u /* launch only the throughput kernel (stragglers stay queued)       */
+#define NSDF_RENDER_NO_QUIET_SMS 64u    /* default kernel without the quiet-SM queue for long rays (A/B)            */
+#define NSDF_RENDER_QUEUE 32u           /* ray-per-lane producers + cooperative consumers through a queue, one launch (A/B) */
+#define NSDF_RENDER_TWO_KERNELS 16u     /* throughput kernel then latency kernel instead of the fused launch (A/B) */
 #define NSDF_RENDER_PHASE_LATENCY 8u    /* launch only the latency kernel on the queue a PHASE_THROUGHPUT call
                                            of the same model handle left behind (per-kernel timing)            */
 

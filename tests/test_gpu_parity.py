@@ -226,16 +226,19 @@ def test_frames_bit_exact(env, name, W, H, matcap):
 
 
 def test_frame_schedules_agree(env):
-    """Simple kernel, refill kernel without stragglers, and refill + latency kernel with an
-    aggressive eviction threshold produce the same bytes (schedule independence)."""
+    """Simple kernel, ray-per-lane kernel, the default cooperative kernel, the two-launch schedule and the
+    producer -> queue -> consumer kernel with aggressive hand-over thresholds (every ray crosses the queue)
+    all produce the same bytes (schedule independence)."""
     host = env["host"]
     outs = []
-    for flags, ev in [(host.capi.RENDER_SIMPLE, 0), (host.capi.RENDER_NO_STRAGGLER, 0), (0, 4), (0, 0)]:
+    for flags, ev in [(host.capi.RENDER_SIMPLE, 0), (host.capi.RENDER_NO_STRAGGLER, 0), (0, 4), (0, 0),
+                      (host.capi.RENDER_TWO_KERNELS, 4), (host.capi.RENDER_TWO_KERNELS, 0), (host.capi.RENDER_QUEUE, 1),
+                      (host.capi.RENDER_QUEUE, 37), (host.capi.RENDER_QUEUE, 0)]:
         img, stats, ref = _render_both(env, "car_1", 96, 96, "blue.png", flags=flags, evict_steps=ev)
         assert np.array_equal(img, ref["image"]), (flags, ev)
         assert stats["queries"] == ref["queries"]
         outs.append(stats)
-    assert outs[2]["evicted"] > 0 and outs[0]["evicted"] == 0
+    assert outs[4]["evicted"] > 0 and outs[6]["evicted"] > 0 and outs[0]["evicted"] == 0
 
 
 def test_frame_rotated_camera_and_head_scene(env):
