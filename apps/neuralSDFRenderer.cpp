@@ -1,0 +1,131 @@
+// neuralSDFRenderer -- headless drop-in for the reference's renderer executable (src/main.cpp).
+//
+// Same flags as src/main.cpp:536-631 (-i -o -H -W -M -rx -ry -rz -z --single --spin --animation -h) and the
+// same stdout line on the first frame (:434-438).  There is no window: without --spin one frame is rendered
+// (the reference's --single path, generateSingleImage :404-468); --spin renders 360 frames with
+// viewRotation.y = i and frameNumber = i (doABarrelRoll :470-478).  Output: <prefix><basename>.png with the
+// reference's 180-degree turn (Image::savePNG), and the same frame as PPM with --ppm.
+// Extra flags: --ppm, --scene tanh|manysphere, --max-steps N, --precision N (NSDF_PREC_*), --views N
+// (turntable of N views instead of 360), --gpu K (device ordinal), --stats.
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include "volumeRender.hh"
+
+static char* getCmdOption(char** begin, char** end, const std::string& option) {
+    for (char** it = begin; it != end; ++it)
+        if (option == *it && it + 1 != end) return *(it + 1);
+    return nullptr;
+}
+static bool cmdOptionExists(char** begin, char** end, const std::string& option) {
+    for (char** it = begin; it != end; ++it)
+        if (option == *it) return true;
+    return false;
+}
+static void usage() {
+    std::cout << "Usage: neuralSDFRenderer [OPTION]... -i SOURCE.h5 [-o DEST_PREFIX]\n"
+                 "Options\n"
+                 "\t-i input neuralGeometry path (string) REQUIRED\n"
+                 "\t-o output image prefix (string) default: {inputPath}; <basename>.png is appended\n"
+                 "\t-H imageH (int)  -W imageW (int)   default 512\n"
+                 "\t-M matcap file path (string); without it pixels are shaded by the facing ratio\n"
+                 "\t-rx -ry -rz rotation in degrees, -z zoom (camera distance, default 2)\n"
+                 "\t--single one frame (default here: there is no interactive mode)\n"
+                 "\t--spin 360 frames (or --views N) rotating about y\n"
+                 "\t--animation 4-input (xyzt) networks\n"
+                 "\t--ppm also write <name>.ppm   --scene tanh|manysphere   --max-steps N   --precision N\n"
+                 "\t--gpu K   --stats   -h (--help)\n";
+}
+static int countDigit(int n) {
+    int c = 0;
+    do { ++c; n /= 10; } while (n);
+    return c;
+}
+
+int main(int argc, char** argv) {
+    char** end = argv + argc;
+    if (cmdOptionExists(argv, end, "-h") || cmdOptionExists(argv, end, "--help")) { usage(); return 0; }
+    if (!cmdOptionExists(argv, end, "-i") || !getCmdOption(argv, end, "-i")) {
+        std::cerr << "You must give path to neuralGeometry\n";
+        return 0;
+    }
+    const std::string path = getCmdOption(argv, end, "-i");
+    const std::string prefix = getCmdOption(argv, end, "-o") ? getCmdOption(argv, end, "-o") : path;
+    const int height = getCmdOption(argv, end, "-H") ? atoi(getCmdOption(argv, end, "-H")) : 512;
+    const int width = getCmdOption(argv, end, "-W") ? atoi(getCmdOption(argv, end, "-W")) : 512;
+    const float rx = getCmdOption(argv, end, "-rx") ? (float)atof(getCmdOption(argv, end, "-rx")) : 0.0f;
+    const float ry = getCmdOption(argv, end, "-ry") ? (float)atof(getCmdOption(argv, end, "-ry")) : 0.0f;
+    const float zoom = getCmdOption(argv, end, "-z") ? -(float)atof(getCmdOption(argv, end, "-z")) : -2.0f;
+    const bool doSpin = cmdOptionExists(argv, end, "--spin") || cmdOptionExists(argv, end, "--views");
+    const int views = getCmdOption(argv, end, "--views") ? atoi(getCmdOption(argv, end, "--views")) : 360;
+    const int numInputs = cmdOptionExists(argv, end, "--animation") ? 4 : 3;
+    const bool ppm = cmdOptionExists(argv, end, "--ppm");
+    const int maxSteps = getCmdOption(argv, end, "--max-steps") ? atoi(getCmdOption(argv, end, "--max-steps")) : 6000;
+    const char* sceneName = getCmdOption(argv, end, "--scene");
+    const int scene = (sceneName && std::strcmp(sceneName, "manysphere") == 0) ? NSDF_SCENE_MANYSPHERE : NSDF_SCENE_TANH;
+    if (getCmdOption(argv, end, "--gpu")) nsdfCheck(nsdf_set_device(atoi(getCmdOption(argv, end, "--gpu"))));
+    if (width <= 0 || height <= 0) { std::cerr << "bad image size\n"; return 1; }
+
+    NeuralNetwork nn;
+    bool ok = false;
+    try {
+        ok = nn.load(path);
+    } catch (const std::exception& e) {
+        std::cerr << e.what() << std::endl;
+    }
+    if (!ok) { std::cerr << "Failed to load model at " << path << std::endl; return 1; }
+    if (getCmdOption(argv, end, "--precision")) nn.setPrecision(atoi(getCmdOption(argv, end, "--precision")));
+
+    Image matcap;
+    int colorType = NSDF_COLOR_FACING;          // src/main.cpp:655-662: no -M means facing-ratio shading
+    if (getCmdOption(argv, end, "-M")) {
+        if (!matcap.loadPNG(getCmdOption(argv, end, "-M"))) return 1;
+        colorType = NSDF_COLOR_MATCAP;
+    }
+    copyStaticSettings(colorType, numInputs);
+    setRenderOptions(scene, maxSteps, 0);
+
+    uint* d_output = nullptr;
+    nsdfCheck(nsdf_dev_malloc(reinterpret_cast<void**>(&d_output), (size_t)width * height * sizeof(uint)));
+    Image out(width, height, true);
+    out.allocateMemory();
+    const dim3 blockSize(8, 8), gridSize((width + 7) / 8, (height + 7) / 8);
+    const std::string base = path.substr(path.find_last_of("/\\") + 1);
+
+    const int frames = doSpin ? views : 1;
+    for (int i = 0; i < frames; ++i) {
+        const float yaw = doSpin ? ry + 360.0f * i / views : ry;
+        nsdfCheck(nsdf_dev_memset(d_output, 0, (size_t)width * height * sizeof(uint)));
+        updateViewMatrices(rx, yaw, 0.0f, 0.0f, zoom, doSpin ? i : 0);
+        nsdfCheck(nsdf_device_synchronize());
+        const auto t0 = std::chrono::steady_clock::now();
+        render_kernel(gridSize, blockSize, d_output, (uint)width, (uint)height, (uint)numInputs, nn, matcap);
+        nsdfCheck(nsdf_device_synchronize());
+        const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (i == 0)
+            std::printf("volumeRender, Throughput = %.4f MTexels/s, Time = %.5f s, Size = %u Texels, NumDevsUsed = %u, Workgroup = %u\n",
+                        (1.0e-6 * width * height) / dt, dt, (unsigned)(width * height), 1u, blockSize.x * blockSize.y);
+        if (cmdOptionExists(argv, end, "--stats")) {
+            nsdf_render_stats st;
+            getLastRenderStats(&st);
+            std::printf("frame %d: %.3f ms, %llu MLP queries (%.2f Gq/s), %llu hit pixels, %llu rays, %llu unfinished\n", i, dt * 1e3,
+                        st.queries, st.queries / dt * 1e-9, st.hit_pixels, st.rays, st.unfinished);
+        }
+        nsdfCheck(nsdf_memcpy_d2h(out.hostData.get(), d_output, (size_t)width * height * sizeof(uint)));
+        std::string name;
+        if (doSpin) {
+            if (countDigit(i) < 2) name = "00";
+            else if (countDigit(i) == 2) name = "0";
+            name += std::to_string(i);
+        } else {
+            name = base;
+        }
+        std::cout << "saving frame: " << prefix + name + ".png" << std::endl;
+        if (!out.savePNG(prefix + name + ".png")) return 1;
+        if (ppm && !out.savePPM(prefix + name + ".ppm")) return 1;
+    }
+    nsdf_dev_free(d_output);
+    return 0;
+}

@@ -38,6 +38,14 @@ PROTOTYPES = {
     "nsdf_version": (C.c_char_p, []),
     "nsdf_error_string": (C.c_char_p, [_i]),
     "nsdf_device_sm_count": (_i, []),
+    "nsdf_dev_malloc": (_i, [C.POINTER(_vp), _sz]),
+    "nsdf_dev_free": (_i, [_vp]),
+    "nsdf_dev_memset": (_i, [_vp, _i, _sz]),
+    "nsdf_memcpy_h2d": (_i, [_vp, _vp, _sz]),
+    "nsdf_memcpy_d2h": (_i, [_vp, _vp, _sz]),
+    "nsdf_device_synchronize": (_i, []),
+    "nsdf_set_device": (_i, [_i]),
+    "nsdf_device_count": (_i, []),
     "nsdf_model_create": (_i, [C.POINTER(_fp), C.POINTER(_fp), _ip, _ip, _ip, _i, C.POINTER(_vp)]),
     "nsdf_model_create_packed": (_i, [_fp, _ip, _i, C.POINTER(_vp)]),
     "nsdf_model_load_h5": (_i, [C.c_char_p, C.POINTER(_vp)]),

@@ -167,6 +167,22 @@ int nsdf_device_sm_count(void) {
     return sms;
 }
 
+int nsdf_dev_malloc(void** p, size_t bytes) {
+    if (!p) return NSDF_EINVAL;
+    *p = nullptr;
+    return bytes ? (int)cudaMalloc(p, bytes) : NSDF_OK;
+}
+int nsdf_dev_free(void* p) { return p ? (int)cudaFree(p) : NSDF_OK; }
+int nsdf_dev_memset(void* p, int v, size_t bytes) { return bytes ? (int)cudaMemset(p, v, bytes) : NSDF_OK; }
+int nsdf_memcpy_h2d(void* d, const void* h, size_t bytes) { return bytes ? (int)cudaMemcpy(d, h, bytes, cudaMemcpyHostToDevice) : NSDF_OK; }
+int nsdf_memcpy_d2h(void* h, const void* d, size_t bytes) { return bytes ? (int)cudaMemcpy(h, d, bytes, cudaMemcpyDeviceToHost) : NSDF_OK; }
+int nsdf_device_synchronize(void) { return (int)cudaDeviceSynchronize(); }
+int nsdf_set_device(int ordinal) { return (int)cudaSetDevice(ordinal); }
+int nsdf_device_count(void) {
+    int n = 0;
+    return cudaGetDeviceCount(&n) == cudaSuccess ? n : 0;
+}
+
 int nsdf_model_create(const float* const* W, const float* const* b, const int* in_dim, const int* out_dim,
                       const int* activation, int n_layers, nsdf_model** out) {
     if (!W || !b || !in_dim || !out_dim || !activation || n_layers <= 0 || !out) return NSDF_EINVAL;

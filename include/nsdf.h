@@ -61,6 +61,18 @@ const char* nsdf_error_string(int status);
 /* Number of SMs of the current device (0 if there is no usable device). */
 int nsdf_device_sm_count(void);
 
+/* ---- device buffers: what Matrix / Image (src/neuralUtils/matrix.cu:12-72, image.cu:12-35,112-140)
+ * do with cudaMalloc / cudaMemcpy / cudaFree, so that the C++ host layer needs no CUDA toolchain.
+ * Synchronous; pointers are plain device pointers on the current device. */
+int nsdf_dev_malloc(void** d_ptr_out, size_t bytes);
+int nsdf_dev_free(void* d_ptr);
+int nsdf_dev_memset(void* d_ptr, int value, size_t bytes);
+int nsdf_memcpy_h2d(void* d_dst, const void* h_src, size_t bytes);
+int nsdf_memcpy_d2h(void* h_dst, const void* d_src, size_t bytes);
+int nsdf_device_synchronize(void);
+int nsdf_set_device(int ordinal);
+int nsdf_device_count(void);
+
 /* ---- model: replaces NeuralNetwork::load / addLayer and the DenseLayer constructor ------
  * (src/neuralNetwork.cpp:50-52,85-151; src/layers/denseLayer.cu:180-227).
  * W[l] is HOST memory, [out][in] row-major, exactly DenseLayer::W after initializeWeights

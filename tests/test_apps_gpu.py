@@ -1,0 +1,53 @@
+"""GPU tests of the drop-in executables (apps/): the reference's simpleInfer self-check and a --single frame
+of neuralSDFRenderer, compared with the CPU oracle."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import MATCAPS, ROOT, model_path
+
+pytestmark = pytest.mark.gpu
+
+
+def test_simple_infer_app(gpu):
+    out = subprocess.run([os.path.join(ROOT, "apps", "simpleInfer"), model_path("car_1"), "65536"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    # 65 536 equal inputs (a batch size on which the reference's GemmBatched launch fails)
+    m = re.search(r"All 65536 outputs equal: raw (\S+), tanh (\S+)", out.stdout)
+    assert m, out.stdout
+    assert np.float32(m.group(1)) == np.float32(-1.186287105e-01)      # SURVEY App. B, car_1 at the origin
+    assert abs(float(m.group(2)) - (-1.180753484e-01)) < 1e-6
+    m = re.search(r"sdf\(0.1, 0.2, 0.3\) = (\S+) \(raw (\S+)\)", out.stdout)
+    assert m and np.float32(m.group(2)) == np.float32(-1.369275451e-01)
+
+
+@pytest.mark.parametrize("matcap", ["blue.png", None])
+def test_renderer_app_single_frame(gpu, tmp_path, matcap):
+    from PIL import Image
+    from oracle import oracle
+    W, H = 112, 80
+    prefix = str(tmp_path) + "/"
+    cmd = [os.path.join(ROOT, "apps", "neuralSDFRenderer"), "-i", model_path("car_1"), "-o", prefix, "-W", str(W), "-H", str(H),
+           "-ry", "30", "--single", "--ppm", "--stats"]
+    if matcap:
+        cmd += ["-M", os.path.join(MATCAPS, matcap)]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert re.search(r"volumeRender, Throughput = \S+ MTexels/s, Time = \S+ s, Size = %d Texels, NumDevsUsed = 1, Workgroup = 64" % (W * H),
+                     out.stdout), out.stdout
+    om = oracle.Model.from_h5(model_path("car_1"))
+    iv, nm = oracle.view_matrices(0.0, 30.0)
+    mc = oracle.load_matcap_png(os.path.join(MATCAPS, matcap)) if matcap else None
+    ref = oracle.render(om, iv, nm, W, H, matcap=mc)
+    q = int(re.search(r"(\d+) MLP queries", out.stdout).group(1))
+    assert q == ref["queries"]
+    img = ref["image"].reshape(H, W)
+    rgba = np.stack([img & 255, (img >> 8) & 255, (img >> 16) & 255, (img >> 24) & 255], -1).astype(np.uint8)
+    png = np.asarray(Image.open(prefix + "car_1.h5.png").convert("RGBA"))
+    assert np.array_equal(png, rgba[::-1, ::-1, :])          # Image::savePNG turns the frame by 180 degrees
+    ppm = open(prefix + "car_1.h5.ppm", "rb").read()
+    head = f"P6\n{W}\n{H}\n255\n".encode()
+    assert ppm.startswith(head) and ppm[len(head):] == rgba[:, :, :3].tobytes()
