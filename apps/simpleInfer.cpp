@@ -6,6 +6,7 @@
 // reports a warm second run too (the reference's std::clock figure includes first-call allocations).
 #include <chrono>
 #include <cmath>
+#include <iomanip>
 #include <iostream>
 #include "neuralNetwork.hh"
 
@@ -57,6 +58,7 @@ int main(int argc, char** argv) {
     }
     if (!ok) { std::cerr << "Failed to load model at " << path << std::endl; return 1; }
     if (argc > 3) nn.setPrecision(atoi(argv[3]));
+    std::cout << std::setprecision(9);
     singleTest(nn);
     return batchTest(nn, batch, true) ? 0 : 1;
 }
