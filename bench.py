@@ -307,6 +307,127 @@ def run_native(args):
         dist.destroy_process_group()
 
 
+def run_tiles(args):
+    """BASELINE config 4: one 3840x2160 frame of 3a3d4a90....obj.h5, 64x64 tiles round-robin over the ranks,
+    every rank's tracer storing its tiles straight into rank 0's frame buffer over NVLink (peer-mapped d_out).
+    Strong scaling: value = frames/s of the whole job."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from cudaneuralrender_b200 import host, multigpu
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(x, op):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    model, Wt, Ht = "3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160
+    nn = host.NeuralNetwork()
+    assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"))
+    matcap = host.Image()
+    assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.updateViewMatrices((0.0, 0.0, 0.0), (0.0, 0.0, -2.0), 0)
+    host.setSceneOptions(host.SCENE_TANH, args.max_steps, 0, 0)
+    frame = multigpu.PeerFrame(Wt, Ht, rank, world, root=0)
+    stats = torch.zeros(6, dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    K, Wm = args.steps, args.warmup
+
+    for _ in range(Wm):
+        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
+    stats.zero_()
+    multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame, stats=stats)
+    barrier()
+    my_q = float(stats[0].item())
+    q_frame = reduce(my_q, dist.ReduceOp.SUM if world > 1 else None)
+    q_max = reduce(my_q, dist.ReduceOp.MAX if world > 1 else None)
+    hits = reduce(float(stats[1].item()), dist.ReduceOp.SUM if world > 1 else None)
+
+    # parity of the partition: the gathered frame must equal a single-GPU render of the same frame, bytewise
+    equal = None
+    if rank == 0:
+        gathered = frame.to_numpy()
+        single = torch.zeros(Wt * Ht, dtype=torch.int32, device="cuda")
+        host.render_kernel(single, Wt, Ht, nn, matcap)
+        torch.cuda.synchronize()
+        equal = bool(np.array_equal(gathered.ravel(), single.cpu().numpy().view(np.uint32)))
+
+    sampler = ClockSampler(local)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    for i in range(K):
+        flush.zero_()
+        ev[i][0].record()
+        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
+        ev[i][1].record()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    my_ms = sum(a.elapsed_time(b) for a, b in ev)
+    total_ms = reduce(my_ms, dist.ReduceOp.MAX if world > 1 else None)   # a frame is done when its slowest rank is
+    min_ms = reduce(my_ms, dist.ReduceOp.MIN if world > 1 else None)
+
+    # end to end: frame on the HOST of rank 0 every step (render -> barrier -> D2H on the root)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
+        barrier()
+        if rank == 0:
+            frame.to_numpy()
+    barrier()
+    e2e_s = reduce(time.perf_counter() - t0, dist.ReduceOp.MAX if world > 1 else None)
+
+    if rank == 0:
+        pk = peaks()
+        ms = total_ms / K
+        achieved = q_frame * FLOP_PER_QUERY / (ms * 1e-3) / 1e12
+        line = {"metric": "4K frames/sec (3a3d4a90.obj, FD normals + matcap), tile-partitioned", "value": K / (total_ms * 1e-3),
+                "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": ms, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"{model}.h5 {Wt}x{Ht} sphere-traced frame, FD normals + matcap {MATCAP}, scene=tanh, "
+                                       f"max_steps={args.max_steps}",
+                           "parallelism": f"tiles{world}: 64x64 tiles round-robin, peer stores into GPU 0 over NVLink",
+                           "l2": "256 MiB memset between timed steps (outside the per-step events)",
+                           "precision": "fp32 FFMA rung (bit-exact vs oracle)"},
+                "queries_per_frame": q_frame, "queries_per_s": q_frame * K / (total_ms * 1e-3), "hit_pixels": hits,
+                "tile_balance_queries": q_frame / world / q_max if q_max else None,
+                "rank_time_min_over_max": min_ms / total_ms if total_ms else None,
+                "tiles_equal_single_gpu": equal,
+                "e2e": {"value": K / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": Wt * Ht * 4},
+                "gpu_launches": K * world,
+                "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved,
+                             "peak": pk["tflops_burst"] * world, "unit": "TFLOP/s",
+                             "frac": achieved / (pk["tflops_burst"] * world), "traffic": None, "peak_source": pk["source"],
+                             "note": "whole job; peak = N x one GPU's measured bf16 peak; fp32 ALU rung (own ceiling 74 TFLOP/s per GPU)"},
+                "clocks": clocks, "wall_s": wall}
+        print(json.dumps(line), flush=True)
+    frame.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -316,11 +437,17 @@ def main():
     ap.add_argument("--max-steps", type=int, default=6000, dest="max_steps")
     ap.add_argument("--no-dense", action="store_false", dest="dense")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--workload", default="frame1080", choices=["frame1080", "frame4k_tiles"],
+                    help="frame1080: BASELINE config 2 (default; N>1 = one view per GPU, weak scaling).  "
+                         "frame4k_tiles: BASELINE config 4, ONE 3840x2160 frame tile-partitioned over the N GPUs, "
+                         "gathered on GPU 0 over NVLink (strong scaling)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     args.dense_tc = (("tc_fp16", 1), ("tc_bf16", 2), ("tc_fp16x3", 3))
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "frame4k_tiles":
+        run_tiles(args)
     else:
         run_native(args)
 

@@ -1,0 +1,171 @@
+"""Multi-GPU partitioning of the neural-SDF hot path: one process per GPU (torch.distributed).
+
+The reference is single-GPU.  Every pixel and every query is independent
+(singleMarch touches only index `id`, src/volumeRender_kernel.cu:416-477), so the path shards
+without a data-path collective:
+
+  * frames   : 64x64-pixel tiles, tile t -> rank t % world (round-robin: balance 0.97-1.00 measured,
+               contiguous bands 0.46 at 8 GPUs).  Each rank's tracer stores its finished
+               tiles STRAIGHT into the presenting rank's frame buffer through an NVLink peer mapping
+               (cudaIpc handle; the stores are ordinary st.global on a mapped peer pointer inside
+               trace_coop_kernel), so the gather is fused into the kernel; the only synchronisation is
+               one barrier.  Fallback when peer mapping is unavailable (and for the gloo CPU tests):
+               pack own tiles -> gather -> scatter on the root.
+  * views    : whole views per rank, view v -> rank v % world.
+  * queries  : contiguous 1/world slabs.
+
+torch.distributed is plumbing only (handle exchange, barrier, timing reductions).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+TILE = 64  # must equal nsdf::TILE (csrc/render_kernels.cuh)
+
+
+# ---- pure host logic (CPU-testable) -------------------------------------------------------------
+def tile_grid(W: int, H: int) -> Tuple[int, int]:
+    return (W + TILE - 1) // TILE, (H + TILE - 1) // TILE
+
+
+def tiles_of_rank(W: int, H: int, rank: int, world: int) -> List[int]:
+    """Tile ids rendered by `rank`: t = rank, rank + world, ...  (nsdf_render_opts.tile_rank/tile_world)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError("bad rank/world")
+    tx, ty = tile_grid(W, H)
+    return list(range(rank, tx * ty, world))
+
+
+def tile_rect(W: int, H: int, t: int) -> Tuple[int, int, int, int]:
+    """(x0, y0, x1, y1) of tile t, clipped to the frame."""
+    tx, _ = tile_grid(W, H)
+    x0, y0 = (t % tx) * TILE, (t // tx) * TILE
+    return x0, y0, min(x0 + TILE, W), min(y0 + TILE, H)
+
+
+def tile_pixel_indices(W: int, H: int, tiles: Sequence[int]) -> np.ndarray:
+    """Linear pixel ids (y*W + x) of the given tiles, tile by tile, row-major inside a tile."""
+    out = []
+    for t in tiles:
+        x0, y0, x1, y1 = tile_rect(W, H, t)
+        ys, xs = np.mgrid[y0:y1, x0:x1]
+        out.append((ys * W + xs).ravel())
+    return np.concatenate(out).astype(np.int64) if out else np.zeros(0, np.int64)
+
+
+def views_of_rank(n_views: int, rank: int, world: int) -> List[int]:
+    """view v -> rank v % world."""
+    return list(range(rank, n_views, world))
+
+
+def slab_of_rank(n: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous [first, first+count) slab of n queries for `rank`; sizes differ by at most one."""
+    base, rem = divmod(n, world)
+    first = rank * base + min(rank, rem)
+    return first, base + (1 if rank < rem else 0)
+
+
+def tile_balance(counts: Sequence[float]) -> float:
+    """mean/max of per-rank work: 1.0 = perfect."""
+    c = np.asarray(counts, dtype=np.float64)
+    return float(c.mean() / c.max()) if c.size and c.max() > 0 else 1.0
+
+
+# ---- gather fallback: works on any backend (gloo on CPU, nccl on GPU) -----------------------------
+def gather_tiles(frame, W: int, H: int, rank: int, world: int, root: int = 0):
+    """Every rank holds a full-size frame tensor (W*H, any int dtype) in which only ITS tiles are valid.
+    After the call `frame` on `root` holds the whole image.  Collective: one gather of packed tiles."""
+    import torch
+    import torch.distributed as dist
+
+    if world == 1:
+        return frame
+    flat = frame.view(-1)
+    idx = [torch.from_numpy(tile_pixel_indices(W, H, tiles_of_rank(W, H, r, world))).to(flat.device) for r in range(world)]
+    mine = flat[idx[rank]].contiguous()
+    n_max = max(int(i.numel()) for i in idx)
+    send = torch.zeros(n_max, dtype=flat.dtype, device=flat.device)
+    send[: mine.numel()] = mine
+    if rank == root:
+        recv = [torch.empty(n_max, dtype=flat.dtype, device=flat.device) for _ in range(world)]
+        dist.gather(send, recv, dst=root)
+        for r in range(world):
+            if r != root:
+                flat[idx[r]] = recv[r][: idx[r].numel()]
+    else:
+        dist.gather(send, None, dst=root)
+    return frame
+
+
+# ---- NVLink peer-store path (GPU only) ---------------------------------------------------------------
+class PeerFrame:
+    """A W*H uint32 frame owned by `root`, mapped into every other rank through a CUDA IPC handle.
+
+    root:   allocates the buffer (cudaMalloc through nsdf_dev_malloc), exports the handle (nsdf_ipc_export)
+    others: nsdf_ipc_open -> a device pointer that is valid as d_out of nsdf_render
+    `ptr` is what each rank passes to host.render_kernel(d_output_ptr=...)."""
+
+    def __init__(self, W: int, H: int, rank: int, world: int, root: int = 0):
+        import ctypes as C
+
+        import torch.distributed as dist
+
+        from . import _capi as capi
+
+        self.W, self.H, self.rank, self.world, self.root = W, H, rank, world, root
+        self._capi, self._C = capi, C
+        self._mapped = None
+        self._owned = None
+        handle = [None]
+        if rank == root:
+            # plain cudaMalloc (not the torch caching allocator): an IPC handle names a whole allocation,
+            # and the importer gets its BASE address
+            p = C.c_void_p()
+            capi.check(capi.lib().nsdf_dev_malloc(C.byref(p), W * H * 4), "nsdf_dev_malloc")
+            capi.check(capi.lib().nsdf_dev_memset(p, 0, W * H * 4), "nsdf_dev_memset")
+            self._owned = p
+            buf = C.create_string_buffer(capi.IPC_HANDLE_BYTES)
+            capi.check(capi.lib().nsdf_ipc_export(p, buf), "nsdf_ipc_export")
+            handle[0] = bytes(buf.raw)
+        if world > 1:
+            dist.broadcast_object_list(handle, src=root)
+        if rank == root:
+            self.ptr = self._owned.value
+        else:
+            p = C.c_void_p()
+            capi.check(capi.lib().nsdf_ipc_open(handle[0], C.byref(p)), "nsdf_ipc_open")
+            self._mapped = p
+            self.ptr = p.value
+
+    def to_numpy(self) -> np.ndarray:
+        """Root only: the gathered frame as uint32[H, W] (synchronous D2H)."""
+        assert self._owned is not None, "only the root holds the frame"
+        out = np.empty((self.H, self.W), dtype=np.uint32)
+        self._capi.check(self._capi.lib().nsdf_memcpy_d2h(out.ctypes.data, self._owned, out.nbytes), "nsdf_memcpy_d2h")
+        return out
+
+    def close(self):
+        if self._mapped is not None:
+            self._capi.check(self._capi.lib().nsdf_ipc_close(self._mapped), "nsdf_ipc_close")
+            self._mapped = None
+        if self._owned is not None:
+            self._capi.lib().nsdf_dev_free(self._owned)
+            self._owned = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def render_frame_tiled(nn, matcap, W: int, H: int, frame: PeerFrame, stats=None):
+    """One frame partitioned by tiles over the ranks of the default process group; finished tiles land
+    in the root's buffer over NVLink.  Asynchronous on the current stream: the caller synchronises and
+    barriers (that barrier is the completion flag)."""
+    from . import host
+
+    host.render_kernel(None, W, H, nn, matcap, stats=stats, tile_rank=frame.rank, tile_world=frame.world,
+                       d_output_ptr=frame.ptr)
