@@ -19,6 +19,8 @@
 #include "lattice.cuh"
 #include "nsdf_internal.h"
 #include "tc_mlp.cuh"
+#include "tc_mlp3.cuh"
+#include "tc_mlp4.cuh"
 
 namespace nsdf {
 
@@ -114,7 +116,10 @@ __global__ void __launch_bounds__(TC_THREADS, 512 / tc::Cols<MODE>::TOTAL) mlp_t
             tc::fence_before_sync();
             __syncthreads();
             TC_STAMP();
-            if (tid == 0) tc::tile_issue_step<MODE>(c, step);
+            if (warp == 0) {
+                if (tc::elect_one()) tc::tile_issue_step<MODE>(c, step);
+                __syncwarp();
+            }
             TC_STAMP();
             tc::mbar_wait_guard(c.bar_d, c.phase);
             c.phase ^= 1u;

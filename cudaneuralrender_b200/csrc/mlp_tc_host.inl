@@ -148,6 +148,98 @@ int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y,
     return (int)cudaGetLastError();
 }
 
+// ---- v3: warp-specialised persistent kernel (tc_mlp3.cuh) ------------------------------------------------
+template <int MODE, int GW, int T, int NM>
+int launch3(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
+            cudaStream_t stream) {
+    tc::Tc3Params p;
+    p.image = t->d[MODE];
+    p.image_bytes = t->bytes[MODE];
+    p.n_sq = m->n_sq;
+    p.x = d_x;
+    p.y = d_y;
+    p.n = n;
+    p.lp = lp;
+    p.trace = g_tc_trace;
+    const size_t smem = 120 * 1024;   // > half of the SM's shared memory: exactly one CTA (and its 512 TMEM columns) per SM
+    if (p.image_bytes > smem) return NSDF_EUNSUPPORTED;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc3_kernel<MODE, GW, T, NM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    const long long n_tiles = (n + 127) / 128;
+    const long long want = (n_tiles + GW * T - 1) / (GW * T);
+    const int grid = (int)(want < sms ? want : sms);
+    tc::mlp_tc3_kernel<MODE, GW, T, NM><<<grid, (GW * 4 + NM) * 32, smem, stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <int MODE>
+int launch3_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
+                cudaStream_t stream) {
+    constexpr bool X3 = MODE == MODE_FP16X3;   // 64-column slots: at most 7 tiles in flight
+    switch (cfg) {
+        case 0: return launch3<MODE, 7, 1, 1>(m, t, d_x, d_y, n, lp, stream);
+        case 1: return launch3<MODE, X3 ? 3 : 4, 2, 1>(m, t, d_x, d_y, n, lp, stream);
+        case 2: return launch3<MODE, 3, X3 ? 2 : 3, 1>(m, t, d_x, d_y, n, lp, stream);
+        case 3: return launch3<MODE, X3 ? 3 : 5, 2, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 4: return launch3<MODE, X3 ? 3 : 4, 2, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 5: return launch3<MODE, 7, 1, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 6: return launch3<MODE, X3 ? 3 : 5, 2, 1>(m, t, d_x, d_y, n, lp, stream);
+        case 7: return launch3<MODE, 7, 1, 4>(m, t, d_x, d_y, n, lp, stream);
+        default: return NSDF_EINVAL;
+    }
+}
+
+// ---- v4: grouped CTAs, bias pre-loaded into the accumulator, UMMAs issued in parallel (tc_mlp4.cuh) ---------
+template <int MODE, int G, int CPS>
+int launch4(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
+            cudaStream_t stream) {
+    tc::Tc4Params p;
+    p.image = t->d[MODE];
+    p.image_bytes = t->bytes[MODE];
+    p.blob = m->d_blob;
+    p.n_sq = m->n_sq;
+    p.x = d_x;
+    p.y = d_y;
+    p.n = n;
+    p.lp = lp;
+    size_t smem = p.image_bytes;
+    const size_t min_smem = (size_t)(227 * 1024) / (size_t)(CPS + 1) + 1;   // never more than CPS CTAs (and their TMEM) per SM
+    if (smem < min_smem) smem = min_smem;
+    if (smem > 200 * 1024) return NSDF_EUNSUPPORTED;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc4_kernel<MODE, G, CPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    const long long n_tiles = (n + 127) / 128;
+    const long long want = (n_tiles + G - 1) / G;
+    const long long cap = (long long)sms * CPS;
+    const int grid = (int)(want < cap ? want : cap);
+    tc::mlp_tc4_kernel<MODE, G, CPS><<<grid, G * 128, smem, stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <int MODE>
+int launch4_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
+                cudaStream_t stream) {
+    constexpr bool X3 = MODE == MODE_FP16X3;   // 64-column slots
+    switch (cfg) {
+        case 0: return launch4<MODE, X3 ? 4 : 5, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 1: return launch4<MODE, 7, 1>(m, t, d_x, d_y, n, lp, stream);
+        case 2: return launch4<MODE, 4, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 3: return launch4<MODE, 2, 4>(m, t, d_x, d_y, n, lp, stream);
+        case 4: return launch4<MODE, 3, 2>(m, t, d_x, d_y, n, lp, stream);
+        default: return NSDF_EINVAL;
+    }
+}
+
 }  // namespace
 
 void tc_set_trace(long long* d_buf) { g_tc_trace = d_buf; }
@@ -167,6 +259,27 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
     if (rc) return rc;
     const TcDeviceImages* t = static_cast<const TcDeviceImages*>(m->d_tc);
     LatticeParams lp{lattice ? 1 : 0, res, lo, hi, (long long)first};
+    // Defaults from the measurements in profiles/r01_tc_schedule_notes.md: the fp16/bf16 rungs sit on the TMEM-read
+    // ceiling with the v2 schedule; the fp16x3 rung (6 UMMAs per layer) is fastest on v4 with 7 groups in one CTA per SM.
+    const int kernel = env_int("NSDF_TC_KERNEL", precision == NSDF_PREC_TC_FP16X3 ? 4 : 2);
+    if (kernel == 4) {
+        const int cfg = env_int("NSDF_TC4_CFG", 1);
+        switch (precision) {
+            case NSDF_PREC_TC_FP16: return launch4_cfg<MODE_FP16>(cfg, m, t, d_x, d_y, n, lp, stream);
+            case NSDF_PREC_TC_BF16: return launch4_cfg<MODE_BF16>(cfg, m, t, d_x, d_y, n, lp, stream);
+            case NSDF_PREC_TC_FP16X3: return launch4_cfg<MODE_FP16X3>(cfg, m, t, d_x, d_y, n, lp, stream);
+            default: return NSDF_EINVAL;
+        }
+    }
+    if (kernel == 3) {
+        const int cfg = env_int("NSDF_TC3_CFG", 0);
+        switch (precision) {
+            case NSDF_PREC_TC_FP16: return launch3_cfg<MODE_FP16>(cfg, m, t, d_x, d_y, n, lp, stream);
+            case NSDF_PREC_TC_BF16: return launch3_cfg<MODE_BF16>(cfg, m, t, d_x, d_y, n, lp, stream);
+            case NSDF_PREC_TC_FP16X3: return launch3_cfg<MODE_FP16X3>(cfg, m, t, d_x, d_y, n, lp, stream);
+            default: return NSDF_EINVAL;
+        }
+    }
     const int halves = env_int("NSDF_TC_EPI_HALVES", 1);
     switch (precision) {
         case NSDF_PREC_TC_FP16:

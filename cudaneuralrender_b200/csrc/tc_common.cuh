@@ -59,6 +59,15 @@ __device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence
 __device__ __forceinline__ void wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
+// One lane of a CONVERGED warp.  Issuing tcgen05.mma under `if (elect_one())` lets ptxas keep the operands on the
+// uniform datapath and emit back-to-back UTCHMMA; under `if (threadIdx.x == 0)` it wraps every MMA in an
+// ELECT / BRA.U.ANY loop that costs ~50 cycles per instruction (measured with tools/mma_bench.cu).
+__device__ __forceinline__ uint32_t elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred;
+}
+
 // D[tmem_d] (+)= A[tmem_a] * B[desc]   (one elected thread)
 __device__ __forceinline__ void mma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(

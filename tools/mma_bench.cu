@@ -8,11 +8,19 @@
 using namespace nsdf;
 
 // ctas_per_sm CTAs of 128 threads; each allocates 64 TMEM columns and issues `iters` batches of `per` MMAs + commit + wait.
-__global__ void __launch_bounds__(128) bench(int N, int per, int iters, int lbo, long long* out) {
+__device__ __forceinline__ void wait_poll(uint64_t* bar, uint32_t parity) {
+    const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
+    uint32_t done;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    } while (!done);
+}
+__global__ void __launch_bounds__(128) bench(int N, int per, int iters, int lbo, long long* out, int poll) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t bar;
     __shared__ uint32_t s_tmem;
-    for (int i = threadIdx.x; i < 16384 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    for (int i = threadIdx.x; i < 8192 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
     if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
     __syncthreads();
     if (threadIdx.x < 32) tc::tmem_alloc(&s_tmem, 64);
@@ -31,7 +39,7 @@ __global__ void __launch_bounds__(128) bench(int N, int per, int iters, int lbo,
         for (int it = 0; it < iters; ++it) {
             for (int j = 0; j < per; ++j) tc::mma_ts(tmem, tmem + 32 + 8 * (j & 1), d, idesc, j ? 1u : 0u);
             tc::mma_commit(&bar);
-            tc::mbar_wait_guard(&bar, phase);
+            if (poll) wait_poll(&bar, phase); else tc::mbar_wait_guard(&bar, phase);
             phase ^= 1;
         }
         t1 = clock64();
@@ -45,22 +53,23 @@ int main() {
     long long* d_out;
     cudaMalloc(&d_out, 148 * 8 * 8);
     cudaFuncSetAttribute(bench, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-    const int Ns[] = {16, 32, 64, 128, 256};
-    for (int ctas = 1; ctas <= 4; ctas *= 2)
+    const int Ns[] = {32};
+    for (int poll = 0; poll < 1; ++poll)
+    for (int ctas = 1; ctas <= 8; ctas *= 2)
         for (int N : Ns) {
             if (N > 32 && false) continue;
-            for (int per : {1, 3, 16, 64}) {
+            for (int per : {1, 2, 3, 4, 8, 16}) {
                 const int iters = 256 / per > 8 ? 256 / per : 8;
-                const int smem = 48 * 1024;   // <= 4 CTAs/SM
-                bench<<<148 * ctas, 128, smem>>>(N, per, iters, N * 16, d_out);
+                const int smem = 24 * 1024;   // <= 8 CTAs/SM (TMEM: 8 x 64 columns)
+                bench<<<148 * ctas, 128, smem>>>(N, per, iters, N * 16, d_out, poll);
                 cudaError_t e = cudaDeviceSynchronize();
                 if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
-                long long h[148 * 4];
+                long long h[148 * 8];
                 cudaMemcpy(h, d_out, sizeof(long long) * 148 * ctas, cudaMemcpyDeviceToHost);
                 double avg = 0;
                 for (int i = 0; i < 148 * ctas; ++i) avg += h[i];
                 avg /= 148 * ctas;
-                printf("ctas/SM %d N %3d per-batch %2d : %.1f cycles/batch  %.1f cycles/MMA (SM-level %.1f cycles/MMA)\n", ctas, N, per,
+                printf("poll %d ctas/SM %d N %3d per-batch %2d : %.1f cycles/batch  %.1f cycles/MMA (SM-level %.1f cycles/MMA)\n", poll, ctas, N, per,
                        avg / iters, avg / iters / per, avg / iters / per / ctas);
             }
         }
