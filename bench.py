@@ -443,7 +443,7 @@ def main():
                          "gathered on GPU 0 over NVLink (strong scaling)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
-    args.dense_tc = (("tc_fp16", 1), ("tc_bf16", 2), ("tc_fp16x3", 3))
+    args.dense_tc = (("tc_fp16", 1), ("tc_bf16", 2), ("tc_fp16x3", 3), ("tc_fp16_acc16", 5))
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "frame4k_tiles":

@@ -50,7 +50,7 @@ struct TcParams {
 
 constexpr int TC_THREADS = 128;   // thread t = query row t of the tile = TMEM lane t; thread 0 also issues the MMAs
 
-template <int MODE, int HALVES>
+template <int MODE, int HALVES, bool ACC16 = false>
 __global__ void __launch_bounds__(TC_THREADS, 512 / tc::Cols<MODE>::TOTAL) mlp_tc_kernel(const __grid_constant__ TcParams p) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t s_bar_w, s_bar_d;
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(TC_THREADS, 512 / tc::Cols<MODE>::TOTAL) mlp_t
         const long long row = (tile << 7) + tid;
         float x[3] = {0.0f, 0.0f, 0.0f};
         if (row < p.n) {
-            if (p.lp.enabled) lattice_point(p.lp, p.lp.first + row, x);
+            if (p.lp.enabled) tc::lattice_point_fast(p.lp, p.lp.first + row, x);
             else { x[0] = __ldg(p.x + 3 * row); x[1] = __ldg(p.x + 3 * row + 1); x[2] = __ldg(p.x + 3 * row + 2); }
         }
         TC_STAMP();
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(TC_THREADS, 512 / tc::Cols<MODE>::TOTAL) mlp_t
             __syncthreads();
             TC_STAMP();
             if (warp == 0) {
-                if (tc::elect_one()) tc::tile_issue_step<MODE>(c, step);
+                if (tc::elect_one()) tc::tile_issue_step<MODE, ACC16>(c, step);
                 __syncwarp();
             }
             TC_STAMP();
@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(TC_THREADS, 512 / tc::Cols<MODE>::TOTAL) mlp_t
             c.phase ^= 1u;
             tc::fence_after_sync();
             TC_STAMP();
-            if (step <= p.n_sq) tc::tile_epilogue<MODE, HALVES>(c);
+            if (step <= p.n_sq) tc::tile_epilogue<MODE, HALVES, ACC16>(c);
         }
         const float y = __uint_as_float(tc::tmem_ld1(c.t_row + tc::Cols<MODE>::D));
         tc::wait_ld();

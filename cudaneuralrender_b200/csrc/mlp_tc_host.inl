@@ -112,7 +112,7 @@ int ensure_images(nsdf_model* m) {
 
 long long* g_tc_trace = nullptr;   // set by nsdf_debug_tc_trace (development)
 
-template <int MODE, int HALVES>
+template <int MODE, int HALVES, bool ACC16 = false>
 int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
            cudaStream_t stream) {
     TcParams p;
@@ -126,7 +126,7 @@ int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y,
     p.trace = g_tc_trace;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<MODE, HALVES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<MODE, HALVES, ACC16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_done = true;
     }
@@ -144,7 +144,7 @@ int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y,
     const long long n_tiles = (n + 127) / 128;
     const long long cap = (long long)sms * per_sm;
     const int grid = (int)(n_tiles < cap ? n_tiles : cap);
-    mlp_tc_kernel<MODE, HALVES><<<grid, TC_THREADS, smem, stream>>>(p);
+    mlp_tc_kernel<MODE, HALVES, ACC16><<<grid, TC_THREADS, smem, stream>>>(p);
     return (int)cudaGetLastError();
 }
 
@@ -259,6 +259,7 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
     if (rc) return rc;
     const TcDeviceImages* t = static_cast<const TcDeviceImages*>(m->d_tc);
     LatticeParams lp{lattice ? 1 : 0, res, lo, hi, (long long)first};
+    if (precision == NSDF_PREC_TC_FP16_ACC16) return launch<MODE_FP16, 1, true>(m, t, d_x, d_y, n, lp, stream);
     // Defaults from the measurements in profiles/r01_tc_schedule_notes.md: the fp16/bf16 rungs sit on the TMEM-read
     // ceiling with the v2 schedule; the fp16x3 rung (6 UMMAs per layer) is fastest on v4 with 7 groups in one CTA per SM.
     const int kernel = env_int("NSDF_TC_KERNEL", precision == NSDF_PREC_TC_FP16X3 ? 4 : 2);

@@ -133,6 +133,7 @@ int forward_dispatch(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int
         case NSDF_PREC_TC_FP16:
         case NSDF_PREC_TC_BF16:
         case NSDF_PREC_TC_FP16X3:
+        case NSDF_PREC_TC_FP16_ACC16:
             if (!m->fused || m->in[0] != 3) return NSDF_EUNSUPPORTED;
             return nsdf::tc_forward(m, d_x, d_y, n, precision, lattice, res, lo, hi, first, stream);
         default:

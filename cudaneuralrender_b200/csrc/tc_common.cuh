@@ -32,8 +32,9 @@ __host__ __device__ constexpr uint32_t b_elem_offset(int n, int k, int rows = 32
 
 // tcgen05 instruction descriptor, kind::f16, fp32 accumulate, A and B K-major.
 // fmt: 0 = fp16, 1 = bf16 (bits [7,10) and [10,13)); N>>3 at [17,23); M>>4 at [24,29).
-__host__ __device__ constexpr uint32_t make_idesc(int fmt, int M, int N) {
-    return (1u << 4) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(N >> 3) << 17) |
+// d_f32: accumulator format, bits [4,6): 1 = fp32, 0 = fp16 (one 16-bit value per 32-bit TMEM column).
+__host__ __device__ constexpr uint32_t make_idesc(int fmt, int M, int N, bool d_f32 = true) {
+    return (d_f32 ? (1u << 4) : 0u) | ((uint32_t)fmt << 7) | ((uint32_t)fmt << 10) | ((uint32_t)(N >> 3) << 17) |
            ((uint32_t)(M >> 4) << 24);
 }
 
@@ -123,6 +124,23 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr)
         : "memory");
+}
+// 32 columns holding one 16-bit value each (fp16 accumulators) -> 16 registers of packed pairs.  Costs the TMEM read
+// port half of what tmem_ld32 does (tools/tmem_bench.cu: the port is bound by delivered register bytes).
+__device__ __forceinline__ void tmem_ld16_pack(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+// relu on a packed pair of fp16 (HMNMX2)
+__device__ __forceinline__ uint32_t relu_f16x2(uint32_t v) {
+    uint32_t d;
+    asm("max.f16x2 %0, %1, %2;" : "=r"(d) : "r"(v), "r"(0u));
+    return d;
 }
 __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
     asm volatile(

@@ -134,9 +134,10 @@ __device__ __forceinline__ void tile_build_desc(uint64_t* table, uint32_t img, i
 }
 
 // Issues the MMAs of one step and commits them to bar_d.  ONE thread (the MMA warp's lane 0).
-template <int MODE>
+// ACC16: layer 0 and the hidden layers accumulate in fp16 (the last layer always in fp32).
+template <int MODE, bool ACC16 = false>
 __device__ __forceinline__ void tile_issue_step(const TileCtx& c, int step) {
-    constexpr uint32_t ID32 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 32);
+    constexpr uint32_t ID32 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 32, !ACC16);
     constexpr uint32_t ID16 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 16);
     const uint32_t idesc = step > c.n_sq ? ID16 : ID32;
     const uint64_t* d = c.desc + step * 8;
@@ -180,8 +181,18 @@ __device__ __forceinline__ void tile_store_query(const TileCtx& c, const float (
 
 // Epilogue of layer 0 / a hidden layer: D -> relu -> 16-bit A operand of the next layer.
 // HALVES = 2 processes 16 accumulator columns at a time (smaller live register set).
-template <int MODE, int HALVES = 1>
+template <int MODE, int HALVES = 1, bool ACC16 = false>
 __device__ __forceinline__ void tile_epilogue(const TileCtx& c) {
+    if (ACC16) {   // fp16 accumulators: packed read (half the TMEM read traffic), relu on pairs, no conversion
+        uint32_t v[16];
+        tmem_ld16_pack(c.t_row + Cols<MODE>::D, v);
+        wait_ld();
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = relu_f16x2(v[j]);
+        tmem_st16(c.t_row + Cols<MODE>::A_HI, v);
+        wait_st();
+        return;
+    }
     constexpr int NC = 32 / HALVES;          // accumulator columns per pass
 #pragma unroll
     for (int half = 0; half < HALVES; ++half) {

@@ -19,7 +19,7 @@ import torch
 
 from . import _capi as capi
 from ._capi import (ACT_RELU, ACT_TANH_LINEAR, COLOR_FACING, COLOR_MATCAP, PREC_FP32, PREC_FP32_WARP, PREC_TC_BF16,
-                    PREC_TC_FP16, PREC_TC_FP16X3, SCENE_MANYSPHERE, SCENE_TANH, Camera, RenderOpts, RenderStats)
+                    PREC_TC_FP16, PREC_TC_FP16_ACC16, PREC_TC_FP16X3, SCENE_MANYSPHERE, SCENE_TANH, Camera, RenderOpts, RenderStats)
 
 ReLU, Tanh = ACT_RELU, ACT_TANH_LINEAR  # enum Activation, src/layers/denseLayer.hh:6-9
 

@@ -42,6 +42,8 @@ extern "C" {
 #define NSDF_PREC_TC_FP16 1    /* tcgen05 kind::f16, fp16 operands, fp32 accumulate (bound 4e-3 abs)              */
 #define NSDF_PREC_TC_BF16 2    /* tcgen05 kind::f16, bf16 operands, fp32 accumulate (bound 5e-2 abs)              */
 #define NSDF_PREC_TC_FP16X3 3  /* tcgen05, split-fp16 (hi+lo) operands, 3 MMAs per layer (bound 1e-4 abs)        */
+#define NSDF_PREC_TC_FP16_ACC16 5 /* tcgen05, fp16 operands AND fp16 accumulators in layers 0..n-1 (last layer fp32): halves
+                                    the TMEM read-back that bounds the other rungs (bound 2e-2 abs)              */
 #define NSDF_PREC_FP32_WARP 4  /* fp32, warp-cooperative evaluator (lanes = neurons); same bits as NSDF_PREC_FP32 */
 
 /* Scene functions: sceneSDF, src/volumeRender_kernel.cu:217-230. */

@@ -41,7 +41,7 @@ def main():
     ap.add_argument("--res", type=int, default=256)
     ap.add_argument("--model", default="car_1")
     ap.add_argument("--out", default="")
-    ap.add_argument("--precs", default="fp32,fp16,bf16,fp16x3")
+    ap.add_argument("--precs", default="fp32,fp16,bf16,fp16x3,fp16acc")
     args = ap.parse_args()
     path = os.path.join(ROOT, "data", "neuralGeometries", args.model + ".h5")
     nn = host.NeuralNetwork()
@@ -50,7 +50,8 @@ def main():
     x = np.random.default_rng(0).uniform(-1, 1, (args.n, 3)).astype(np.float32)
     ref = oracle.mlp_forward(om, x).ravel().astype(np.float64)
     xd = torch.from_numpy(x).cuda().contiguous()
-    precs = {"fp32": host.PREC_FP32, "fp16": host.PREC_TC_FP16, "bf16": host.PREC_TC_BF16, "fp16x3": host.PREC_TC_FP16X3}
+    precs = {"fp32": host.PREC_FP32, "fp16": host.PREC_TC_FP16, "bf16": host.PREC_TC_BF16, "fp16x3": host.PREC_TC_FP16X3,
+             "fp16acc": host.PREC_TC_FP16_ACC16}
     res = {}
     for name in args.precs.split(","):
         prec = precs[name]
