@@ -10,6 +10,7 @@
 #include "render_kernels.cuh"
 #include "trace_coop.cuh"
 #include "trace_fused.cuh"
+#include "trace_tc.cuh"
 
 namespace nsdf {
 
@@ -97,12 +98,13 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.max_steps = opts->max_steps;
     rp.stats = d_stats;
 
-    const bool simple = (opts->flags & NSDF_RENDER_SIMPLE) != 0;
+    const bool farfield = (opts->flags & NSDF_RENDER_TC_FARFIELD) != 0;
+    const bool simple = !farfield && (opts->flags & NSDF_RENDER_SIMPLE) != 0;
     const bool coop = !simple && !(opts->flags & (NSDF_RENDER_NO_STRAGGLER | NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
                                                    NSDF_RENDER_TWO_KERNELS | NSDF_RENDER_QUEUE));
     const bool coop_queue = coop && !(opts->flags & NSDF_RENDER_NO_QUIET_SMS) && env_int("NSDF_COOP_QUEUE", 1) != 0;
-    const bool straggler = !simple && (coop ? coop_queue : !(opts->flags & NSDF_RENDER_NO_STRAGGLER));
-    const bool two_kernel = straggler && (opts->flags & (NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
+    const bool straggler = farfield || (!simple && (coop ? coop_queue : !(opts->flags & NSDF_RENDER_NO_STRAGGLER)));
+    const bool two_kernel = !farfield && straggler && (opts->flags & (NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
                                                          NSDF_RENDER_TWO_KERNELS)) != 0;
     // fused kernel: only the long tail leaves the throughput lanes early; two-kernel path: its old default
     rp.evict_steps = opts->evict_steps > 0 ? opts->evict_steps
@@ -151,6 +153,54 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     if (simple) {
         const unsigned int blocks = (rp.total_idx + 127u) / 128u;
         trace_simple_kernel<<<blocks, 128, m->blob_bytes, stream>>>(rp);
+        return (int)cudaGetLastError();
+    }
+
+    if (opts->flags & NSDF_RENDER_TC_FARFIELD) {
+        // ---- mixed precision: far-field marching on the tensor cores (trace_tc.cuh), then the fp32 consumers
+        // of trace_coop_kernel finish every ray that got close to the surface (bit-exact arithmetic from there on)
+        if (opts->scene != NSDF_SCENE_TANH) return NSDF_EUNSUPPORTED;
+        const bool x3 = env_int("NSDF_FARFIELD_FP16", 0) == 0;
+        const int mode = x3 ? tc::MODE_FP16X3 : tc::MODE_FP16;
+        TraceTcParams tp;
+        tp.image = tc_image(m, mode, &tp.image_bytes);
+        if (!tp.image) return NSDF_ENOMEM;
+        const char* e_thr = getenv("NSDF_FARFIELD_THR");
+        const char* e_mar = getenv("NSDF_FARFIELD_MARGIN");
+        tp.thr = (e_thr && *e_thr) ? (float)atof(e_thr) : (x3 ? 1e-4f : 1e-2f);
+        tp.margin = (e_mar && *e_mar) ? (float)atof(e_mar) : (x3 ? 8e-6f : 2.5e-3f);
+        tp.max_tc_steps = env_int("NSDF_FARFIELD_MAX_STEPS", opts->max_steps);   // no cap measured best on the 1080p / 4K frames
+        tp.drain_below = env_int("NSDF_FARFIELD_DRAIN", 16);
+        m->frame_seq = m->frame_seq + 1u ? m->frame_seq + 1u : 1u;
+        rp.frame_seq = m->frame_seq;
+        const int per_sm = 512 / (int)(x3 ? tc::Cols<tc::MODE_FP16X3>::TOTAL : tc::Cols<tc::MODE_FP16>::TOTAL);
+        size_t smem = tp.image_bytes;
+        const size_t min_smem = (size_t)(227 * 1024) / (size_t)(per_sm + 1) + 1;   // never more CTAs than TMEM columns allow
+        if (smem < min_smem) smem = min_smem;
+        static bool tc_attr_done = false;
+        if (!tc_attr_done) {
+            e = cudaFuncSetAttribute(trace_tc_kernel<tc::MODE_FP16X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+            if (e != cudaSuccess) return (int)e;
+            e = cudaFuncSetAttribute(trace_tc_kernel<tc::MODE_FP16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+            if (e != cudaSuccess) return (int)e;
+            tc_attr_done = true;
+        }
+        const unsigned int want_tc = (rp.total_idx + 127u) / 128u;
+        const unsigned int cap_tc = (unsigned int)(sms * per_sm);
+        const unsigned int grid_tc = want_tc < cap_tc ? want_tc : cap_tc;
+        if (x3) trace_tc_kernel<tc::MODE_FP16X3><<<grid_tc, 128, smem, stream>>>(rp, tp);
+        else trace_tc_kernel<tc::MODE_FP16><<<grid_tc, 128, smem, stream>>>(rp, tp);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return (int)e;
+        int occ = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
+        if (e != cudaSuccess) return (int)e;
+        if (occ < 1) return NSDF_EUNSUPPORTED;
+        RenderParams rp2 = rp;
+        rp2.total_idx = 0;          // no pixels of its own: ray slots refill from the queue the first pass filled
+        rp2.consumer_period = 0;
+        rp2.queue_static = 1;
+        trace_coop_kernel<<<sms * occ, COOP_THREADS, coop_smem(m), stream>>>(rp2);
         return (int)cudaGetLastError();
     }
 

@@ -59,6 +59,8 @@ struct RenderParams {
                                    // w % consumer_period == consumer_period - 1 (0 = none)
     StragglerEntry* queue;
     unsigned int queue_capacity;
+    int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
+                                   // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed
     nsdf_render_stats* stats;
 };
 

@@ -63,7 +63,14 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float* abuf = s_w + (rp.blob_bytes >> 2) + warp * (2 * COOP_R * WARP_ACT_STRIDE);
     const unsigned int total_warps = gridDim.x * (COOP_THREADS / 32);
-    const bool use_queue = rp.queue != nullptr;
+    const bool from_queue = rp.queue_static != 0;
+    const bool use_queue = rp.queue != nullptr && !from_queue;
+    unsigned int n_src = rp.total_idx;
+    if (from_queue) {
+        n_src = rp.pixel_counter[1];
+        if (n_src > rp.queue_capacity) n_src = rp.queue_capacity;
+    }
+    unsigned int* const src_counter = from_queue ? rp.pixel_counter + 2 : rp.pixel_counter;
 
     RaySlot slot;
     slot.mode = -1;
@@ -84,13 +91,24 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             const int leader = __ffs(m) - 1;
             const unsigned int cnt = __popc(m);
             unsigned int base = 0;
-            if (lane == leader) base = atomicAdd(rp.pixel_counter, cnt);
+            if (lane == leader) base = atomicAdd(src_counter, cnt);
             base = __shfl_sync(0xffffffffu, base, leader);
             if (need) {
                 const unsigned int idx = base + __popc(m & lanemask_lt());
-                if (idx < rp.total_idx) slot_start(slot, idx, rp, st);
+                if (idx < n_src) {
+                    if (!from_queue) {
+                        slot_start(slot, idx, rp, st);
+                    } else {   // a ray the far-field pass handed over: continue it from its current point
+                        const float4* src = reinterpret_cast<const float4*>(rp.queue + idx);
+                        const float4 e0 = __ldcg(src), e1 = __ldcg(src + 1);
+                        const float tf = __ldcg(reinterpret_cast<const float*>(src + 2));
+                        slot.pix = __float_as_int(e0.x); slot.steps = __float_as_int(e0.y);
+                        slot.p = f3{e0.z, e0.w, e1.x}; slot.d = f3{e1.y, e1.z, e1.w};
+                        slot.tfar = tf; slot.mode = 0;
+                    }
+                }
             }
-            if (base + cnt >= rp.total_idx) exhausted = true;
+            if (base + cnt >= n_src) exhausted = true;
         }
         unsigned int act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
         if (use_queue && exhausted) {

@@ -148,6 +148,9 @@ typedef struct nsdf_render_opts {
 #define NSDF_RENDER_NO_QUIET_SMS 64u    /* default kernel without the quiet-SM queue for long rays (A/B)            */
 #define NSDF_RENDER_QUEUE 32u           /* ray-per-lane producers + cooperative consumers through a queue, one launch (A/B) */
 #define NSDF_RENDER_TWO_KERNELS 16u     /* throughput kernel then latency kernel instead of the fused launch (A/B) */
+#define NSDF_RENDER_TC_FARFIELD 128u    /* mixed precision: march on the tensor cores while t >= threshold (fp16x3 rung,
+                                           |error| <= 1e-4), hand every ray that gets close to the surface to the fp32 path
+                                           (accept test, normals, shading unchanged).  Not bit-identical to the default. */
 #define NSDF_RENDER_PHASE_LATENCY 8u    /* launch only the latency kernel on the queue a PHASE_THROUGHPUT call
                                            of the same model handle left behind (per-kernel timing)            */
 
