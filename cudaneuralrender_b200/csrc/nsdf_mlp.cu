@@ -113,6 +113,7 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
         };
         if (R == 8) return go(mlp_fp32_warp_kernel<8>, 8);
         if (R == 2) return go(mlp_fp32_warp_kernel<2>, 2);
+        if (R == 1) return go(mlp_fp32_warp_kernel<1>, 1);
         return go(mlp_fp32_warp_kernel<4>, 4);
     }
     const int P = env_int("NSDF_FP32_P", 2);

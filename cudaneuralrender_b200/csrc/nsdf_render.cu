@@ -196,6 +196,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
         if (e != cudaSuccess) return (int)e;
         if (occ < 1) return NSDF_EUNSUPPORTED;
+        if (env_int("NSDF_FARFIELD_SKIP_PASS2", 0)) return NSDF_OK;   // development: time the first pass alone
         RenderParams rp2 = rp;
         rp2.total_idx = 0;          // no pixels of its own: ray slots refill from the queue the first pass filled
         rp2.consumer_period = 0;
@@ -262,7 +263,18 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     if (straggler && !only_throughput) {
-        trace_latency_kernel<LAT_R><<<sms, LAT_THREADS, latency_smem(m), stream>>>(rp);
+        if (env_int("NSDF_TWO_PASS2_COOP", 0)) {   // A/B: second pass = cooperative tracer refilling from the static queue
+            int occ = 0;
+            e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
+            if (e != cudaSuccess) return (int)e;
+            RenderParams rp2 = rp;
+            rp2.total_idx = 0;
+            rp2.consumer_period = 0;
+            rp2.queue_static = 1;
+            trace_coop_kernel<<<sms * occ, COOP_THREADS, coop_smem(m), stream>>>(rp2);
+        } else {
+            trace_latency_kernel<LAT_R><<<sms, LAT_THREADS, latency_smem(m), stream>>>(rp);
+        }
         e = cudaGetLastError();
     }
     return (int)e;
