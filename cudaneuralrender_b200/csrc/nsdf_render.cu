@@ -96,6 +96,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     if ((long long)my_tiles * TILE_PIXELS >= (1LL << 32)) return NSDF_EINVAL;
     rp.total_idx = (unsigned int)my_tiles * TILE_PIXELS;
     rp.max_steps = opts->max_steps;
+    rp.isolate_steps = env_int("NSDF_COOP_ISOLATE", 0);
     rp.stats = d_stats;
 
     const bool farfield = (opts->flags & NSDF_RENDER_TC_FARFIELD) != 0;

@@ -59,6 +59,8 @@ struct RenderParams {
                                    // w % consumer_period == consumer_period - 1 (0 = none)
     StragglerEntry* queue;
     unsigned int queue_capacity;
+    int isolate_steps;             // trace_coop_kernel: a warp holding a ray that has marched this many steps stops taking new
+                                   // rays, so the long ray soon runs alone at the 1-ray latency (0 = off)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
                                    // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed
     nsdf_render_stats* stats;
@@ -110,7 +112,11 @@ __device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const 
         s.mode = -1;
         return;
     }
+#ifdef NSDF_DEBUG_TSCALE   // development: every ray crawls and runs to max_steps (per-step latency probe)
+    const float t = scene_sdf(rp.scene, s.p, nsdf, rp.cam.frame) * NSDF_DEBUG_TSCALE + 2e-6f;
+#else
     const float t = scene_sdf(rp.scene, s.p, nsdf, rp.cam.frame);
+#endif
     s.tfar = s.tfar - t;
     ++s.steps;
     if (s.tfar <= 0.0f) {             // left the march budget: background (:463-467)

@@ -44,6 +44,50 @@ __device__ __forceinline__ float coop_eval(const float* s_w, int n_sq, float* ab
     return mine;
 }
 
+// A warp left with ONE marching ray and nothing to refill from: the serial tail of the frame (one
+// plane_1 ray runs all 6000 steps).  Every lane keeps an identical copy of the ray state, so a march step is the
+// network evaluation plus a handful of scalar instructions -- no ballots, shuffles, refill or queue traffic per step
+// (measured: 1.62 us per step in the general loop).  Arithmetic is slot_update's, bit for bit; the owner lane takes the
+// state back when the ray converges, leaves, hits the step cap, or after max_iter steps (so that queues get polled).
+__device__ __forceinline__ void lone_ray_march(RaySlot& slot, int owner, const float* s_w, int n_sq, float* abuf,
+                                               const RenderParams& rp, LocalStats& st, int lane, int max_iter) {
+    f3 p, d;
+    p.x = __shfl_sync(0xffffffffu, slot.p.x, owner); p.y = __shfl_sync(0xffffffffu, slot.p.y, owner);
+    p.z = __shfl_sync(0xffffffffu, slot.p.z, owner);
+    d.x = __shfl_sync(0xffffffffu, slot.d.x, owner); d.y = __shfl_sync(0xffffffffu, slot.d.y, owner);
+    d.z = __shfl_sync(0xffffffffu, slot.d.z, owner);
+    float tfar = __shfl_sync(0xffffffffu, slot.tfar, owner);
+    int steps = __shfl_sync(0xffffffffu, slot.steps, owner);
+    int mode = 0;
+    bool background = false, unfinished = false;
+    unsigned int q = 0;
+#pragma unroll 1
+    for (int it = 0; it < max_iter; ++it) {
+        const float x[1][3] = {{p.x, p.y, p.z}};
+        float y[1];
+        mlp32_eval_warp<1>(s_w, n_sq, abuf, x, y, lane);
+        ++q;
+#ifdef NSDF_DEBUG_TSCALE
+        const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame) * NSDF_DEBUG_TSCALE + 2e-6f;
+#else
+        const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame);
+#endif
+        tfar = tfar - t;
+        ++steps;
+        if (tfar <= 0.0f) { background = true; mode = -1; break; }
+        p = f3{fmaf(d.x, t, p.x), fmaf(d.y, t, p.y), fmaf(d.z, t, p.z)};
+        if (t < NSDF_MARCHING_EPSILON) mode = 1;
+        if (steps >= rp.max_steps) { unfinished = true; mode = -1; break; }
+        if (mode != 0) break;
+    }
+    if (lane == owner) {
+        slot.p = p; slot.tfar = tfar; slot.steps = steps; slot.mode = mode;
+        st.queries += q;
+        if (background || unfinished) rp.out[slot.pix] = 0u;
+        if (unfinished) ++st.unfinished;
+    }
+}
+
 __device__ __forceinline__ unsigned int sm_id() {
     unsigned int v;
     asm("mov.u32 %0, %%smid;" : "=r"(v));
@@ -83,8 +127,10 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     unsigned int idle = 0;
 
     for (;;) {
-        // ---- refill idle ray slots (ballot compaction over the slot lanes)
-        while (!exhausted) {
+        // ---- refill idle ray slots (ballot compaction over the slot lanes); not while a long ray is on board
+        const bool hold = rp.isolate_steps > 0 &&
+                          __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.isolate_steps) != 0u;
+        while (!exhausted && !hold) {
             const bool need = lane < COOP_R && slot.mode < 0;
             const unsigned int m = __ballot_sync(0xffffffffu, need);
             if (!m) break;
@@ -137,6 +183,13 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             idle = 0;
         } else if (!act) {
             break;
+        }
+        if (__popc(act) == 1 && (exhausted || hold)) {
+            const int owner = __ffs(act) - 1;
+            if (__shfl_sync(0xffffffffu, slot.mode, owner) == 0) {
+                lone_ray_march(slot, owner, s_w, rp.n_sq, abuf, rp, st, lane, use_queue ? 64 : (1 << 30));
+                continue;
+            }
         }
         const bool active = lane < COOP_R && slot.mode >= 0;
         const int na = __popc(act);
