@@ -100,16 +100,21 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.stats = d_stats;
 
     const bool farfield = (opts->flags & NSDF_RENDER_TC_FARFIELD) != 0;
+    // two-pass schedule: asked for, or chosen for large calls when the caller expressed no schedule preference
+    const bool two_pass = !farfield && ((opts->flags & NSDF_RENDER_TWO_PASS) != 0 ||
+                                        (opts->flags == 0 && opts->evict_steps == 0 &&
+                                         rp.total_idx >= (unsigned int)env_int("NSDF_TWO_PASS_MIN_PIXELS", 3000000)));
     const bool simple = !farfield && (opts->flags & NSDF_RENDER_SIMPLE) != 0;
-    const bool coop = !simple && !(opts->flags & (NSDF_RENDER_NO_STRAGGLER | NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
+    const bool coop = !simple && !two_pass && !(opts->flags & (NSDF_RENDER_NO_STRAGGLER | NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
                                                    NSDF_RENDER_TWO_KERNELS | NSDF_RENDER_QUEUE));
     const bool coop_queue = coop && !(opts->flags & NSDF_RENDER_NO_QUIET_SMS) && env_int("NSDF_COOP_QUEUE", 1) != 0;
     const bool straggler = farfield || (!simple && (coop ? coop_queue : !(opts->flags & NSDF_RENDER_NO_STRAGGLER)));
-    const bool two_kernel = !farfield && straggler && (opts->flags & (NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
-                                                         NSDF_RENDER_TWO_KERNELS)) != 0;
+    const bool two_kernel = !farfield && straggler && (two_pass || (opts->flags & (NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
+                                                         NSDF_RENDER_TWO_KERNELS)) != 0);
     // fused kernel: only the long tail leaves the throughput lanes early; two-kernel path: its old default
     rp.evict_steps = opts->evict_steps > 0 ? opts->evict_steps
-                                           : (two_kernel ? env_int("NSDF_EVICT_STEPS", 48) : env_int("NSDF_FUSED_EVICT_STEPS", 32));
+                                           : (two_pass ? env_int("NSDF_TWO_PASS_EVICT", 128)
+                                              : two_kernel ? env_int("NSDF_EVICT_STEPS", 48) : env_int("NSDF_FUSED_EVICT_STEPS", 32));
     rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_FUSED_EVICT_HI", 256);
     size_t qcap = 0;
     if (straggler) {
@@ -264,7 +269,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     e = cudaGetLastError();
     if (e != cudaSuccess) return (int)e;
     if (straggler && !only_throughput) {
-        if (env_int("NSDF_TWO_PASS2_COOP", 0)) {   // A/B: second pass = cooperative tracer refilling from the static queue
+        if (two_pass || env_int("NSDF_TWO_PASS2_COOP", 0)) {   // second pass = cooperative tracer refilling from the static queue
             int occ = 0;
             e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
             if (e != cudaSuccess) return (int)e;

@@ -148,6 +148,10 @@ typedef struct nsdf_render_opts {
 #define NSDF_RENDER_NO_QUIET_SMS 64u    /* default kernel without the quiet-SM queue for long rays (A/B)            */
 #define NSDF_RENDER_QUEUE 32u           /* ray-per-lane producers + cooperative consumers through a queue, one launch (A/B) */
 #define NSDF_RENDER_TWO_KERNELS 16u     /* throughput kernel then latency kernel instead of the fused launch (A/B) */
+#define NSDF_RENDER_TWO_PASS 256u       /* ray-per-lane throughput kernel hands rays over after evict_steps (default 128) march steps,
+                                           then the cooperative tracer refills its ray slots from that queue.  Bit-identical to
+                                           the single launch; chosen automatically for calls covering >= 3 M pixels, where the
+                                           bulk dominates the frame (4K: 64.0 -> 55.4 ms)                                        */
 #define NSDF_RENDER_TC_FARFIELD 128u    /* mixed precision: march on the tensor cores while t >= threshold (fp16x3 rung,
                                            |error| <= 1e-4), hand every ray that gets close to the surface to the fp32 path
                                            (accept test, normals, shading unchanged).  Not bit-identical to the default. */

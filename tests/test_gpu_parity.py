@@ -263,7 +263,8 @@ def test_frame_schedules_agree(env):
     outs = []
     for flags, ev in [(host.capi.RENDER_SIMPLE, 0), (host.capi.RENDER_NO_STRAGGLER, 0), (0, 4), (0, 0),
                       (host.capi.RENDER_TWO_KERNELS, 4), (host.capi.RENDER_TWO_KERNELS, 0), (host.capi.RENDER_QUEUE, 1),
-                      (host.capi.RENDER_QUEUE, 37), (host.capi.RENDER_QUEUE, 0)]:
+                      (host.capi.RENDER_QUEUE, 37), (host.capi.RENDER_QUEUE, 0), (host.capi.RENDER_TWO_PASS, 0),
+                      (host.capi.RENDER_TWO_PASS, 3)]:
         img, stats, ref = _render_both(env, "car_1", 96, 96, "blue.png", flags=flags, evict_steps=ev)
         assert np.array_equal(img, ref["image"]), (flags, ev)
         assert stats["queries"] == ref["queries"]
