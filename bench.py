@@ -84,13 +84,66 @@ def cpu_oracle_frame(rows=None, nthreads=0, ry=0.0):
     return time.perf_counter() - t0, r["queries"], oracle.hardware_threads()
 
 
+REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+
+
+def reference_cuda_frame(frames, model=MODEL, w=W, h=H, ry=0.0, timeout=900):
+    """The UNMODIFIED reference's own CUDA render_kernel (oracle/_ref/ref_driver = the reference's translation units
+    compiled from /root/reference by oracle/build_ref.sh + a headless main) on this box's GPU 0: `frames` timed frames
+    after one warm-up call.  Returns the driver's JSON or None when it is not built / there is no GPU."""
+    import tempfile
+    import numpy as np
+    if not os.path.exists(REF_DRIVER):
+        return None
+    from oracle import oracle
+    iv, nm = oracle.view_matrices(0.0, ry)
+    with tempfile.TemporaryDirectory() as td:
+        cam = os.path.join(td, "cam.f32")
+        np.concatenate([np.asarray(iv, np.float32).ravel(), np.asarray(nm, np.float32).ravel()]).tofile(cam)
+        cmd = [REF_DRIVER, "render", os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"), str(w), str(h),
+               os.path.join(ROOT, "data", "matcaps", MATCAP), cam, "0", os.path.join(td, "out.u32"), str(frames)]
+        try:
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+        except (OSError, subprocess.TimeoutExpired):
+            return None
+        if r.returncode != 0:
+            return None
+        for ln in r.stdout.splitlines():
+            if ln.startswith("{"):
+                return json.loads(ln)
+    return None
+
+
 def run_reference(args):
-    """--impl reference: the reference has no CPU implementation of this path (simpleInfer runs on the
-    GPU), so this arm times the CPU oracle (oracle/nsdf_oracle.cpp, a line-by-line restatement) with all
-    host threads.  A step = every 8th row of the 1080p frame (a representative 1/8 sample); value is
-    scaled to whole frames."""
+    """--impl reference.  The reference (daviesthomas/cudaNeuralRender) has NO CPU implementation of this path: its
+    implementation IS CUDA.  When oracle/_ref/ref_driver exists (the reference's own, unmodified CUDA translation units,
+    built by oracle/build_ref.sh) and a GPU is present, this arm times THAT on the same box: whole 1080p plane_1 frames
+    through the reference's render_kernel (host loop of <= 6000 iterations x {thrust scan, D2H, createBatch, 9 CUTLASS
+    GemmBatched, singleMarch}).  Its sceneSDF is what HEAD evaluates (manySphere); the native arm reports the same scene
+    as `head_scene`.  Otherwise it times the CPU oracle (a line-by-line port) with all host threads on 1/8 of the rows."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
+        return
+    cfg = {"workload": f"{MODEL}.h5 {W}x{H} sphere-traced frame, FD normals + matcap {MATCAP}, max_steps=6000"}
+    base = {"impl": "reference", "metric": "1080p frames/sec (plane_1, FD normals + matcap)", "unit": "frames/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "gpu_launches": 0}
+    have_gpu = False
+    try:
+        import torch
+        have_gpu = torch.cuda.is_available()
+    except Exception:
+        pass
+    ref = reference_cuda_frame(max(1, args.steps)) if (have_gpu and not args.cpu_port) else None
+    if ref is not None:
+        fps = 1e3 / ref["mean_ms"]
+        cfg["note"] = "reference's own CUDA kernels (unmodified, sm_100 build), scene = manySphere as at HEAD, one process, GPU 0"
+        line = dict(base, value=fps, ms_per_step=ref["mean_ms"], config=cfg,
+                    cpu_baseline={"value": fps, "unit": "frames/s", "cores": 1, "kind": "reference",
+                                  "sample": f"{ref['frames']} whole {W}x{H} frames through the reference's render_kernel on this "
+                                            f"box's GPU 0 after one warm-up frame (best {ref['best_ms']:.1f} ms, first {ref['first_call_ms']:.1f} ms)"},
+                    e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+        print(json.dumps(line), flush=True)
         return
     stride = 8
     for _ in range(args.warmup):
@@ -103,16 +156,10 @@ def run_reference(args):
     total = sum(ts)
     fps = args.steps / (total * stride)
     sample = f"rows y%{stride}==0 of the {W}x{H} frame per step (1/{stride} of the rays), scaled by {stride}"
-    line = {"impl": "reference", "metric": "1080p frames/sec (plane_1, FD normals + matcap)", "value": fps,
-            "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * total / args.steps * stride, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{MODEL}.h5 {W}x{H} sphere-traced frame, FD normals + matcap {MATCAP}, scene=tanh, "
-                                   "max_steps=6000", "note": "reference has no CPU path; oracle port timed"},
-            "queries_per_s": qs / total,
-            "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
-            "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+    cfg["note"] = "reference has no CPU path and its CUDA build is not available here; oracle port (scene = tanh) timed"
+    line = dict(base, value=fps, ms_per_step=1e3 * total / args.steps * stride, config=cfg, queries_per_s=qs / total,
+                cpu_baseline={"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+                e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
     print(json.dumps(line), flush=True)
 
 
@@ -247,6 +294,24 @@ def run_native(args):
         host.render_kernel(frame, W, H, nn, matcap)   # leave the exact frame behind
         torch.cuda.synchronize()
 
+    # ---- the scene the reference evaluates at HEAD (manySphere), for a like-for-like ratio against --impl reference
+    host.setSceneOptions(host.SCENE_MANYSPHERE, args.max_steps, 0, 0)
+    st_h = torch.zeros(6, dtype=torch.int64, device="cuda")
+    host.render_kernel(frame, W, H, nn, matcap, stats=st_h)
+    evh = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(min(K, 5))]
+    for e in evh:
+        flush.zero_()
+        e[0].record()
+        host.render_kernel(frame, W, H, nn, matcap)
+        e[1].record()
+    torch.cuda.synchronize()
+    t_head = sum(e[0].elapsed_time(e[1]) for e in evh) / len(evh)
+    head_scene = {"ms_per_frame": t_head, "frames_per_s": 1e3 / t_head, "queries": int(st_h[0].item()), "hit_pixels": int(st_h[1].item()),
+                  "note": "scene = manySphere (src/volumeRender_kernel.cu:221), what the reference's HEAD renders; bit-exact path"}
+    host.setSceneOptions(host.SCENE_TANH, args.max_steps, 0, 0)
+    host.render_kernel(frame, W, H, nn, matcap)
+    torch.cuda.synchronize()
+
     # ---- end to end through the C ABI with host buffers (pinned): matcap H2D + frame D2H every step
     mc_host = torch.from_numpy(matcap.hostData.view(np.int32)).pin_memory()
     out_host = torch.empty(W * H, dtype=torch.int32).pin_memory()
@@ -329,8 +394,16 @@ def run_native(args):
                              "peak_gbs": pk["hbm_gbs"]}},
         "clocks": clocks, "wall_s": t_wall,
     }
+    line["head_scene"] = head_scene
     if mixed:
         line["mixed_precision"] = mixed
+    if world == 1 and args.ref_cuda:
+        rc = reference_cuda_frame(2)
+        if rc is not None:
+            line["reference_cuda_same_box"] = {"ms_per_frame": rc["mean_ms"], "frames_per_s": 1e3 / rc["mean_ms"],
+                                               "speedup_vs_head_scene": rc["mean_ms"] / t_head,
+                                               "note": "the reference's own unmodified CUDA kernels (oracle/_ref/ref_driver), same frame, "
+                                                       "same GPU, 2 frames after a warm-up"}
     if dense:
         line["dense_256cubed"] = dense
     if world == 1 and not args.no_cpu:
@@ -474,6 +547,9 @@ def main():
     ap.add_argument("--no-dense", action="store_false", dest="dense")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-mixed", action="store_false", dest="mixed")
+    ap.add_argument("--cpu-port", action="store_true", help="--impl reference: time the CPU oracle port even if the reference's "
+                                                            "CUDA build (oracle/_ref) is present")
+    ap.add_argument("--no-ref-cuda", action="store_false", dest="ref_cuda")
     ap.add_argument("--workload", default="frame1080", choices=["frame1080", "frame4k_tiles"],
                     help="frame1080: BASELINE config 2 (default; N>1 = one view per GPU, weak scaling).  "
                          "frame4k_tiles: BASELINE config 4, ONE 3840x2160 frame tile-partitioned over the N GPUs, "
