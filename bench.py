@@ -383,8 +383,8 @@ def run_native(args):
         "queries_per_s": q_total * K / (total_ms * 1e-3), "queries_per_frame": q_frame, "hit_pixels": hits,
         "evicted_rays": evicted,
         "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": K,
-        "kernels": {"trace_coop_kernel": {"ms": ms_per_step, "queries": q_frame},
+        "gpu_launches": 3 * K,   # per step: tile_probe_kernel, tile_sort_kernel, trace_coop_kernel (+ one 16-byte memset)
+        "kernels": {"trace_coop_kernel (+ tile_probe_kernel, tile_sort_kernel)": {"ms": ms_per_step, "queries": q_frame},
                     "two_launch_schedule_ms": t_two},
         "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved,
                      "peak": pk["tflops_burst"], "unit": "TFLOP/s", "frac": achieved / pk["tflops_burst"],

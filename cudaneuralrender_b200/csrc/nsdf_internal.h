@@ -27,6 +27,8 @@ struct nsdf_model {
     size_t queue_capacity = 0;
     unsigned int frame_seq = 0;           // publication stamp of the fused tracer's queue entries
     nsdf_render_stats* d_stats_scratch = nullptr;
+    int* d_tile_scratch = nullptr;        // [0,cap) probe scores, [cap,2cap) tile order (tile_priority.cuh)
+    size_t tile_scratch_capacity = 0;     // tiles
     float* d_act[2] = {nullptr, nullptr}; // ping-pong activations for the per-layer path
     size_t act_capacity = 0;              // floats per buffer
     int sm_count = 0;

@@ -48,6 +48,7 @@ struct RenderParams {
     int W, H;
     int tiles_x, n_tiles;
     int tile_rank, tile_world;
+    const int* tile_order;         // [j] = tile traced j-th by this call (tile_priority.cuh), or null: rank + j*world
     unsigned int total_idx;        // pixel indices this call enumerates (my tiles * 4096)
     int max_steps, evict_steps;
     int evict_steps_hi;            // fused kernel: unconditional hand-over (evict_steps applies while the backlog is short)
@@ -79,7 +80,7 @@ struct LocalStats { unsigned int queries, hits, rays, evicted, unfinished, pixel
 
 __device__ __forceinline__ bool decode_pixel(const RenderParams& rp, unsigned int idx, int& x, int& y) {
     const unsigned int j = idx / TILE_PIXELS, within = idx % TILE_PIXELS;
-    const int t = rp.tile_rank + (int)j * rp.tile_world;
+    const int t = rp.tile_order ? __ldg(rp.tile_order + j) : rp.tile_rank + (int)j * rp.tile_world;
     const int tx = t % rp.tiles_x, ty = t / rp.tiles_x;
     const unsigned int sb = within >> 5, l = within & 31u;        // 8x4-pixel sub-blocks: one warp's first fill
     x = tx * TILE + (int)(sb & 7u) * 8 + (int)(l & 7u);

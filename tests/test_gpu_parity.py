@@ -272,6 +272,39 @@ def test_frame_schedules_agree(env):
     assert outs[4]["evicted"] > 0 and outs[6]["evicted"] > 0 and outs[0]["evicted"] == 0
 
 
+def test_tile_priority_order_is_invisible(env):
+    """tile_priority.cuh: probing and re-ordering the tiles (forced on for this small frame, also for a 3-rank tile
+    partition and the two-pass / mixed schedules) must not change a byte of an exact frame or a query of its count."""
+    torch, host, oracle, capi = env["torch"], env["host"], env["oracle"], env["capi"]
+    old = {k: os.environ.get(k) for k in ("NSDF_TILE_PRIORITY_FORCE", "NSDF_TILE_PRIORITY_STEPS")}
+    try:
+        os.environ["NSDF_TILE_PRIORITY_FORCE"] = "1"
+        for steps in ("4", "32"):
+            os.environ["NSDF_TILE_PRIORITY_STEPS"] = steps
+            for flags in (0, capi.RENDER_TWO_PASS, capi.RENDER_NO_STRAGGLER):
+                img, stats, ref = _render_both(env, "plane_1", 300, 200, "blue.png", flags=flags, ry=40.0)
+                assert np.array_equal(img, ref["image"]), (steps, flags)
+                assert stats["queries"] == ref["queries"]
+        nn, om = _load(env, "car_1")
+        iv, nm = oracle.view_matrices(0, 30)
+        host.copyStaticSettings(host.COLOR_FACING, 3)
+        host.copyViewMatrices(iv, nm, 0, 3)
+        host.setSceneOptions(host.SCENE_TANH, 6000, 0, 0)
+        W, H = 200, 136
+        c = torch.full((W * H,), 0x55, dtype=torch.int32, device="cuda")
+        for r in range(3):
+            host.render_kernel(c, W, H, nn, tile_rank=r, tile_world=3)
+        torch.cuda.synchronize()
+        ref = oracle.render(om, iv, nm, W, H)
+        assert np.array_equal(c.cpu().numpy().view(np.uint32).reshape(H, W), ref["image"])
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
 def test_frame_rotated_camera_and_head_scene(env):
     img, stats, ref = _render_both(env, "car_1", 100, 80, "blue.png", rx=20.0, ry=135.0)
     assert np.array_equal(img, ref["image"])
