@@ -124,7 +124,7 @@ int launch(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y,
     p.n = n;
     p.lp = lp;
     p.trace = g_tc_trace;
-    static bool attr_done = false;
+    NSDF_PER_DEVICE_FLAG(attr_done);
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(mlp_tc_kernel<MODE, HALVES, ACC16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
         if (e != cudaSuccess) return (int)e;
@@ -163,7 +163,7 @@ int launch3(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y
     p.trace = g_tc_trace;
     const size_t smem = 120 * 1024;   // > half of the SM's shared memory: exactly one CTA (and its 512 TMEM columns) per SM
     if (p.image_bytes > smem) return NSDF_EUNSUPPORTED;
-    static bool attr_done = false;
+    NSDF_PER_DEVICE_FLAG(attr_done);
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc3_kernel<MODE, GW, T, NM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return (int)e;
@@ -211,7 +211,7 @@ int launch4(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y
     const size_t min_smem = (size_t)(227 * 1024) / (size_t)(CPS + 1) + 1;   // never more than CPS CTAs (and their TMEM) per SM
     if (smem < min_smem) smem = min_smem;
     if (smem > 200 * 1024) return NSDF_EUNSUPPORTED;
-    static bool attr_done = false;
+    NSDF_PER_DEVICE_FLAG(attr_done);
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc4_kernel<MODE, G, CPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;

@@ -37,6 +37,13 @@ struct nsdf_model {
     size_t stage_bytes[3] = {0, 0, 0};
 };
 
+// cudaFuncSetAttribute is per DEVICE: a once-flag must be too (a process may drive several devices through nsdf_set_device).
+#define NSDF_PER_DEVICE_FLAG(name)                  \
+    static bool name##_by_device[64] = {};          \
+    int name##_dev = 0;                             \
+    cudaGetDevice(&name##_dev);                     \
+    bool& name = name##_by_device[name##_dev & 63]
+
 namespace nsdf {
 
 // fp32 rungs + per-layer operator (nsdf_mlp.cu)

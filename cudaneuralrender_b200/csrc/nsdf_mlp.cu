@@ -118,7 +118,8 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
     }
     const int P = env_int("NSDF_FP32_P", 2);
     const size_t smem = m->blob_bytes;
-    static bool attr1 = false, attr2 = false;
+    NSDF_PER_DEVICE_FLAG(attr1);
+    NSDF_PER_DEVICE_FLAG(attr2);
     if (P == 1) {
         if (!attr1) {
             e = cudaFuncSetAttribute(mlp_fp32_thread_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);

@@ -144,7 +144,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     }
 
     const int sms = m->sm_count > 0 ? m->sm_count : 148;
-    static bool attr_done = false;
+    NSDF_PER_DEVICE_FLAG(attr_done);
     if (!attr_done) {
         e = cudaFuncSetAttribute(trace_throughput_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
         if (e != cudaSuccess) return (int)e;
@@ -181,7 +181,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         int* d_order = m->d_tile_scratch + m->tile_scratch_capacity;
         e = cudaMemsetAsync(d_score, 0, (size_t)my_tiles * sizeof(int), stream);
         if (e != cudaSuccess) return (int)e;
-        static bool probe_attr = false;
+        NSDF_PER_DEVICE_FLAG(probe_attr);
         if (!probe_attr) {
             e = cudaFuncSetAttribute(tile_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
             if (e != cudaSuccess) return (int)e;
@@ -222,7 +222,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         size_t smem = tp.image_bytes;
         const size_t min_smem = (size_t)(227 * 1024) / (size_t)(per_sm + 1) + 1;   // never more CTAs than TMEM columns allow
         if (smem < min_smem) smem = min_smem;
-        static bool tc_attr_done = false;
+        NSDF_PER_DEVICE_FLAG(tc_attr_done);
         if (!tc_attr_done) {
             e = cudaFuncSetAttribute(trace_tc_kernel<tc::MODE_FP16X3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
             if (e != cudaSuccess) return (int)e;
