@@ -13,7 +13,7 @@ ACT_RELU, ACT_TANH_LINEAR = 0, 1
 PREC_FP32, PREC_TC_FP16, PREC_TC_BF16, PREC_TC_FP16X3, PREC_FP32_WARP, PREC_TC_FP16_ACC16 = 0, 1, 2, 3, 4, 5
 SCENE_TANH, SCENE_MANYSPHERE = 0, 1
 COLOR_FACING, COLOR_MATCAP = 0, 1
-RENDER_SIMPLE, RENDER_NO_STRAGGLER, RENDER_PHASE_THROUGHPUT, RENDER_PHASE_LATENCY, RENDER_TWO_KERNELS, RENDER_QUEUE, RENDER_NO_QUIET_SMS, RENDER_TC_FARFIELD, RENDER_TWO_PASS = 1, 2, 4, 8, 16, 32, 64, 128, 256
+RENDER_SIMPLE, RENDER_NO_STRAGGLER, RENDER_PHASE_THROUGHPUT, RENDER_PHASE_LATENCY, RENDER_TWO_KERNELS, RENDER_QUEUE, RENDER_NO_QUIET_SMS, RENDER_TC_FARFIELD, RENDER_TWO_PASS, RENDER_HYBRID = 1, 2, 4, 8, 16, 32, 64, 128, 256, 512
 IPC_HANDLE_BYTES = 64
 
 

@@ -106,9 +106,14 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
 
     const bool farfield = (opts->flags & NSDF_RENDER_TC_FARFIELD) != 0;
     // two-pass schedule: asked for, or chosen for large calls when the caller expressed no schedule preference
-    const bool two_pass = !farfield && ((opts->flags & NSDF_RENDER_TWO_PASS) != 0 ||
-                                        (opts->flags == 0 && opts->evict_steps == 0 &&
-                                         rp.total_idx >= (unsigned int)env_int("NSDF_TWO_PASS_MIN_PIXELS", 3000000)));
+    // large calls (the bulk dominates, not the longest ray): ray-per-lane producers.  NSDF_LARGE_SCHEDULE: 1 = hybrid single
+    // launch (default), 2 = two-pass, 0 = the cooperative default at every size
+    const bool large = !farfield && opts->flags == 0 && opts->evict_steps == 0 &&
+                       rp.total_idx >= (unsigned int)env_int("NSDF_TWO_PASS_MIN_PIXELS", 3000000);
+    const int large_schedule = large ? env_int("NSDF_LARGE_SCHEDULE", 1) : 0;
+    const bool two_pass = !farfield && ((opts->flags & NSDF_RENDER_TWO_PASS) != 0 || large_schedule == 2);
+    const bool hybrid = !farfield && !two_pass && ((opts->flags & NSDF_RENDER_HYBRID) != 0 || large_schedule == 1 ||
+                                                   env_int("NSDF_COOP_HYBRID", 0) != 0);
     const bool simple = !farfield && (opts->flags & NSDF_RENDER_SIMPLE) != 0;
     const bool coop = !simple && !two_pass && !(opts->flags & (NSDF_RENDER_NO_STRAGGLER | NSDF_RENDER_PHASE_THROUGHPUT | NSDF_RENDER_PHASE_LATENCY |
                                                    NSDF_RENDER_TWO_KERNELS | NSDF_RENDER_QUEUE));
@@ -263,6 +268,14 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         rp.frame_seq = m->frame_seq;
         rp.consumer_period = (unsigned int)env_int("NSDF_COOP_QUIET_PERIOD", 16);
         rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_COOP_EVICT", 256);
+        if (hybrid && coop_queue) {
+            rp.hybrid = env_int("NSDF_COOP_HYBRID", 8);   // a dry producer warp with <= this many rays hands them all over
+            if (rp.hybrid < 1) rp.hybrid = 1;
+            rp.consumer_period = (unsigned int)env_int("NSDF_COOP_QUIET_PERIOD", 32);
+            rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_COOP_EVICT", 192);
+            const unsigned int quiet_sms = rp.consumer_period ? (unsigned int)sms / rp.consumer_period : 0u;
+            rp.queue_room = opts->evict_steps > 0 ? 0u : (unsigned int)env_int("NSDF_COOP_ROOM", (int)(quiet_sms * 2u * per_cta));
+        }
         trace_coop_kernel<<<want < cap ? want : cap, COOP_THREADS, coop_smem(m), stream>>>(rp);
         return (int)cudaGetLastError();
     }

@@ -64,6 +64,9 @@ struct RenderParams {
                                    // rays, so the long ray soon runs alone at the 1-ray latency (0 = off)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
                                    // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed
+    int hybrid;                    // trace_coop_kernel: producing warps march one ray per LANE (mlp32_eval_thread, 32 rays per warp,
+                                   // a third of the shared-memory wavefronts per query) and hand rays that reach evict_steps_hi
+                                   // steps to the cooperative consumers on the quiet SMs; out of pixels they become consumers
     nsdf_render_stats* stats;
 };
 

@@ -126,6 +126,50 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     int poll = 0;
     unsigned int idle = 0;
 
+    // ---- hybrid schedule: the bulk of the frame on the ray-per-lane evaluator, long rays to the quiet SMs
+    if (rp.hybrid && use_queue && producing) {
+        RaySlot ps;
+        ps.mode = -1;
+        bool dry = false;   // warp-uniform
+        for (;;) {
+            while (!dry) {
+                const bool need = ps.mode < 0;
+                const unsigned int m = __ballot_sync(0xffffffffu, need);
+                if (!m) break;
+                const int leader = __ffs(m) - 1;
+                const unsigned int cnt = __popc(m);
+                unsigned int base = 0;
+                if (lane == leader) base = atomicAdd(rp.pixel_counter, cnt);
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (need) {
+                    const unsigned int idx = base + __popc(m & lanemask_lt());
+                    if (idx < rp.total_idx) slot_start(ps, idx, rp, st);
+                }
+                if (base + cnt >= rp.total_idx) dry = true;
+            }
+            if (!__ballot_sync(0xffffffffu, ps.mode >= 0)) break;
+            const f3 q = ps.mode >= 0 ? slot_query_point(ps) : f3{0.0f, 0.0f, 0.0f};
+            float x[1][3] = {{q.x, q.y, q.z}}, y[1];
+            mlp32_eval_thread<1>(s_w, rp.n_sq, x, y);
+            if (ps.mode >= 0) slot_update(ps, y[0], q, rp, st);
+            const int n_act = __popc(__ballot_sync(0xffffffffu, ps.mode >= 0));
+            const bool drain = dry && n_act <= rp.hybrid;
+            // a long ray leaves for the quiet SMs only while their backlog is short: marching on in a full warp costs nothing
+            // extra, waiting in the queue does (looked at every 8th step: the counters live in L2)
+            bool longray = ps.mode == 0 && ps.steps >= rp.evict_steps_hi && (rp.queue_room == 0u || (ps.steps & 7) == 0);
+            if (rp.queue_room && !drain && __ballot_sync(0xffffffffu, longray)) {
+                unsigned int backlog = 0;
+                if (lane == 0) backlog = ld_volatile_u32(rp.pixel_counter + 1) - ld_volatile_u32(rp.pixel_counter + 2);
+                backlog = __shfl_sync(0xffffffffu, backlog, 0);
+                if ((int)backlog >= (int)rp.queue_room) longray = false;
+            }
+            fused_push(ps, ps.mode == 0 && (drain || longray), rp, st);
+        }
+        producing = false;
+        exhausted = true;
+        if (lane == 0) { __threadfence(); atomicAdd(rp.pixel_counter + 3, 1u); }
+    }
+
     for (;;) {
         // ---- refill idle ray slots (ballot compaction over the slot lanes); not while a long ray is on board
         const bool hold = rp.isolate_steps > 0 &&

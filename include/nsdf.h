@@ -150,8 +150,12 @@ typedef struct nsdf_render_opts {
 #define NSDF_RENDER_TWO_KERNELS 16u     /* throughput kernel then latency kernel instead of the fused launch (A/B) */
 #define NSDF_RENDER_TWO_PASS 256u       /* ray-per-lane throughput kernel hands rays over after evict_steps (default 128) march steps,
                                            then the cooperative tracer refills its ray slots from that queue.  Bit-identical to
-                                           the single launch; chosen automatically for calls covering >= 3 M pixels, where the
-                                           bulk dominates the frame (4K: 64.0 -> 55.4 ms)                                        */
+                                           the single launch (4K: 64.0 -> 55.4 ms; superseded as the large-call default by NSDF_RENDER_HYBRID)                                        */
+#define NSDF_RENDER_HYBRID 512u         /* ONE launch: producing warps march one ray per lane (a third of the shared-memory traffic
+                                           per query) and hand rays that reach evict_steps (default 192) march steps to cooperative
+                                           consumer warps on every 32nd SM; out of pixels they become consumers themselves.
+                                           Bit-identical; chosen automatically for calls covering >= 3 M pixels (4K: 54.9 -> 49.4 ms
+                                           against NSDF_RENDER_TWO_PASS, the previous choice there)                                */
 #define NSDF_RENDER_TC_FARFIELD 128u    /* mixed precision: march on the tensor cores while t >= threshold (fp16x3 rung,
                                            |error| <= 1e-4), hand every ray that gets close to the surface to the fp32 path
                                            (accept test, normals, shading unchanged).  Not bit-identical to the default. */

@@ -264,7 +264,7 @@ def test_frame_schedules_agree(env):
     for flags, ev in [(host.capi.RENDER_SIMPLE, 0), (host.capi.RENDER_NO_STRAGGLER, 0), (0, 4), (0, 0),
                       (host.capi.RENDER_TWO_KERNELS, 4), (host.capi.RENDER_TWO_KERNELS, 0), (host.capi.RENDER_QUEUE, 1),
                       (host.capi.RENDER_QUEUE, 37), (host.capi.RENDER_QUEUE, 0), (host.capi.RENDER_TWO_PASS, 0),
-                      (host.capi.RENDER_TWO_PASS, 3)]:
+                      (host.capi.RENDER_TWO_PASS, 3), (host.capi.RENDER_HYBRID, 0), (host.capi.RENDER_HYBRID, 5)]:
         img, stats, ref = _render_both(env, "car_1", 96, 96, "blue.png", flags=flags, evict_steps=ev)
         assert np.array_equal(img, ref["image"]), (flags, ev)
         assert stats["queries"] == ref["queries"]
@@ -281,7 +281,7 @@ def test_tile_priority_order_is_invisible(env):
         os.environ["NSDF_TILE_PRIORITY_FORCE"] = "1"
         for steps in ("4", "32"):
             os.environ["NSDF_TILE_PRIORITY_STEPS"] = steps
-            for flags in (0, capi.RENDER_TWO_PASS, capi.RENDER_NO_STRAGGLER):
+            for flags in (0, capi.RENDER_TWO_PASS, capi.RENDER_HYBRID, capi.RENDER_NO_STRAGGLER):
                 img, stats, ref = _render_both(env, "plane_1", 300, 200, "blue.png", flags=flags, ry=40.0)
                 assert np.array_equal(img, ref["image"]), (steps, flags)
                 assert stats["queries"] == ref["queries"]
