@@ -50,6 +50,7 @@ PROTOTYPES = {
     "nsdf_model_create_packed": (_i, [_fp, _ip, _i, C.POINTER(_vp)]),
     "nsdf_model_load_h5": (_i, [C.c_char_p, C.POINTER(_vp)]),
     "nsdf_h5_read_keras": (_i, [C.c_char_p, _ip, _ip, _i, _fp, _sz, C.POINTER(_sz)]),
+    "nsdf_h5_write_keras": (_i, [C.c_char_p, _fp, _ip, _i]),
     "nsdf_model_destroy": (None, [_vp]),
     "nsdf_model_num_layers": (_i, [_vp]),
     "nsdf_model_dims": (_i, [_vp, _ip]),

@@ -277,6 +277,32 @@ int nsdf_h5_read_keras(const char* path, int* n_layers_out, int* dims_out, int d
     return NSDF_OK;
 }
 
+int nsdf_h5_write_keras(const char* path, const float* params, const int* dims, int n_layers) {
+    if (!path || !params || !dims || n_layers <= 0 || n_layers > 256) return NSDF_EINVAL;
+    std::vector<nsdf::h5::KerasLayer> layers((size_t)n_layers);
+    const float* p = params;
+    for (int l = 0; l < n_layers; ++l) {
+        const int in = dims[l], od = dims[l + 1];
+        if (in <= 0 || od <= 0) return NSDF_EINVAL;
+        nsdf::h5::KerasLayer& L = layers[(size_t)l];
+        L.name = l ? "dense_" + std::to_string(l) : std::string("dense");
+        L.kernel_dims = {(size_t)in, (size_t)od};
+        L.kernel.resize((size_t)in * od);
+        for (int x = 0; x < in; ++x)   // inverse of DenseLayer::initializeWeights (denseLayer.cu:217-227)
+            for (int y = 0; y < od; ++y) L.kernel[(size_t)x * od + y] = p[(size_t)y * in + x];
+        p += (size_t)in * od;
+        L.bias.assign(p, p + od);
+        p += od;
+    }
+    try {
+        nsdf::h5::write_keras_weights(path, layers);
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "nsdf: writing %s: %s\n", path, e.what());
+        return NSDF_EIO;
+    }
+    return NSDF_OK;
+}
+
 int nsdf_model_load_h5(const char* path, nsdf_model** out) {
     if (!path || !out) return NSDF_EINVAL;
     std::vector<int> dims;

@@ -267,6 +267,10 @@ class NeuralNetwork:
         self._handle = h
         return True
 
+    def save(self, path: str) -> None:
+        """Not in the reference: writes the layers back as a Keras save_weights-style file (nsdf_h5_write_keras)."""
+        write_keras_h5(path, [(l.W.hostData.reshape(l.getYDim(), l.getXDim()).T, l.b.hostData) for l in self.layers])
+
     def forward(self, X: Matrix, maxBatchSize: int = -1, precision: Optional[int] = None) -> Matrix:
         batch = X.shape.y
         out_dim = self.layers[-1].getYDim()
@@ -313,6 +317,40 @@ class NeuralNetwork:
         capi.check(capi.lib().nsdf_mlp_forward_lattice(self.handle(), out.data_ptr(), res, lo, hi, first, count,
                                                        precision, _stream_ptr()), "nsdf_mlp_forward_lattice")
         return out
+
+
+# ---- weight files without a device (SURVEY 8 f1) ------------------------------------------------
+def read_keras_h5(path: str):
+    """[(kernel[in][out], bias[out])] in network order, through the library's own HDF5 reader (nsdf_h5_read_keras)."""
+    L = capi.lib()
+    n, cnt = C.c_int(0), C.c_size_t(0)
+    capi.check(L.nsdf_h5_read_keras(path.encode(), C.byref(n), None, 0, None, 0, C.byref(cnt)), "nsdf_h5_read_keras")
+    dims = (C.c_int * (n.value + 1))()
+    params = np.empty(cnt.value, dtype=np.float32)
+    capi.check(L.nsdf_h5_read_keras(path.encode(), C.byref(n), dims, n.value + 1, params.ctypes.data_as(C.POINTER(C.c_float)),
+                                    params.size, C.byref(cnt)), "nsdf_h5_read_keras")
+    out, p = [], 0
+    for l in range(n.value):
+        i, o = dims[l], dims[l + 1]
+        W = params[p:p + i * o].reshape(o, i); p += i * o
+        out.append((np.ascontiguousarray(W.T), params[p:p + o].copy())); p += o
+    return out
+
+
+def write_keras_h5(path: str, layers) -> None:
+    """layers: [(kernel[in][out], bias[out])] -> Keras save_weights-style file (groups dense, dense_1, ...; nsdf_h5_write_keras)."""
+    dims, chunks = [], []
+    for k, (kernel, bias) in enumerate(layers):
+        kernel = np.asarray(kernel, dtype=np.float32); bias = np.asarray(bias, dtype=np.float32).ravel()
+        assert kernel.ndim == 2 and bias.size == kernel.shape[1]
+        if k == 0:
+            dims.append(kernel.shape[0])
+        assert kernel.shape[0] == dims[-1]
+        dims.append(kernel.shape[1])
+        chunks += [np.ascontiguousarray(kernel.T).ravel(), bias]
+    params = np.concatenate(chunks).astype(np.float32)
+    capi.check(capi.lib().nsdf_h5_write_keras(path.encode(), params.ctypes.data_as(C.POINTER(C.c_float)),
+                                              (C.c_int * len(dims))(*dims), len(layers)), "nsdf_h5_write_keras")
 
 
 # ---- renderer: the three extern "C" entry points of src/volumeRender_kernel.cu ------------------

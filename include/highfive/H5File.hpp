@@ -47,6 +47,10 @@ public:
         for (const auto& kv : node_->children) names.push_back(kv.first);   // std::map: ascending byte order
         return names;
     }
+    // Not HighFive: the names in the order of the `layer_names` attribute when it names exactly the objects present
+    // (nsdf::h5::keras_layer_order), else ascending -- what include/neuralNetwork.inl walks so that stacks of more than
+    // ten layers load in network order.
+    std::vector<std::string> kerasLayerOrder() const { return nsdf::h5::keras_layer_order(*node_); }
     size_t getNumberObjects() const { return node_->children.size(); }
     bool exist(const std::string& name) const { return node_->children.count(name) != 0; }
     ObjectType getObjectType(const std::string& name) const {

@@ -90,7 +90,8 @@ inline Matrix NeuralNetwork::forward(Matrix X, int maxBatchSize) {
 // neuralNetwork.cpp:85-151.
 inline bool NeuralNetwork::load(std::string fp, bool hostOnly) {
     HighFive::File file(fp, HighFive::File::ReadOnly);
-    std::vector<std::string> kerasLayers = file.listObjectNames();
+    // listObjectNames() order up to ten layers; Keras' own layer_names order beyond
+    std::vector<std::string> kerasLayers = file.kerasLayerOrder();
     int layerCount = 0;
     for (size_t i = 0; i < kerasLayers.size(); ++i) {
         const std::string& lname = kerasLayers[i];

@@ -93,6 +93,12 @@ int nsdf_model_load_h5(const char* path, nsdf_model** out);
  * Any output pointer may be NULL; n_params_out always receives the float count. */
 int nsdf_h5_read_keras(const char* path, int* n_layers_out, int* dims_out, int dims_capacity, float* params_out,
                        size_t params_capacity, size_t* n_params_out);
+/* Writes a Keras `save_weights`-style .h5 (the subset the shipped files use: superblock v0, symbol-table groups
+ * /L/L/{bias:0,kernel:0}, contiguous float32, root attribute `layer_names`) from packed parameters in the layout of
+ * nsdf_model_create_packed; groups are named dense, dense_1, ...  The reader orders layers by `layer_names` when it names
+ * exactly the groups present, so stacks of more than ten layers load in network order (the reference's name sort,
+ * src/neuralNetwork.cpp:88-91, puts dense_10 before dense_2).  No device needed.  SURVEY 8 f1. */
+int nsdf_h5_write_keras(const char* path, const float* params, const int* dims, int n_layers);
 void nsdf_model_destroy(nsdf_model* m);
 int nsdf_model_num_layers(const nsdf_model* m);
 /* dims_out receives n_layers+1 ints. */

@@ -10,8 +10,13 @@
 // Understands: superblock v0/v1, 8-byte (or 4-byte) offsets and lengths, v1 object headers
 // with continuation blocks, old-style groups (symbol-table message -> v1 B-tree "TREE" ->
 // "SNOD" symbol nodes -> local "HEAP" for names), dataspace v1/v2, IEEE little-endian
-// float32 / float64 datatypes, layout v3 contiguous and compact.  Anything else throws
-// nsdf::h5::FormatError.
+// float32 / float64 datatypes, layout v3 contiguous and compact, attribute messages v1-v3 holding
+// fixed-length string arrays (Keras' `layer_names`, `weight_names`).  Anything else throws
+// nsdf::h5::FormatError (attributes of other types are skipped).
+//
+// write_keras_weights() emits the same subset (superblock v0, old-style groups, contiguous float32
+// datasets, `layer_names` / `weight_names` / `backend` attributes): the synthetic models of the scaling and
+// parity tests (other depths, 4-input animation nets) are real files that go through the same reader.
 // =====================================================================================
 #ifndef NSDF_H5_HPP_
 #define NSDF_H5_HPP_
@@ -45,6 +50,8 @@ struct Node {
     std::vector<size_t> dims;
     std::vector<float> data;      // converted to float32
     int64_t file_offset = -1;     // absolute offset of contiguous raw data, -1 if compact
+    // attributes that are arrays of fixed-length strings (layer_names, weight_names), NUL padding stripped
+    std::map<std::string, std::vector<std::string>> string_attrs;
 };
 
 class File {
@@ -176,6 +183,7 @@ private:
         for (const Msg& m : msgs) {
             if (m.type == 0x0011) stab = &m;
             if (m.type == 0x0008) layout = &m;
+            if (m.type == 0x000C) read_string_attr(*node, m);
         }
         if (stab) {
             node->kind = NodeKind::Group;
@@ -190,6 +198,42 @@ private:
         }
         --depth_;
         return node;
+    }
+
+    // Attribute message (0x000C) versions 1-3: keeps arrays (or scalars) of fixed-length strings, ignores everything else.
+    void read_string_attr(Node& node, const Msg& m) const {
+        if (m.size < 8) return;
+        const unsigned ver = (unsigned)rd(m.body, 1);
+        if (ver < 1 || ver > 3) return;
+        const unsigned name_sz = (unsigned)rd(m.body + 2, 2), dt_sz = (unsigned)rd(m.body + 4, 2), ds_sz = (unsigned)rd(m.body + 6, 2);
+        const auto pad = [&](uint64_t v) { return ver == 1 ? (v + 7u) & ~(uint64_t)7u : v; };
+        uint64_t p = m.body + 8 + (ver == 3 ? 1 : 0);
+        const uint64_t end = m.body + m.size;
+        if (name_sz == 0 || p + pad(name_sz) + pad(dt_sz) + pad(ds_sz) > end) return;
+        const std::string name((const char*)buf_.data() + p, strnlen((const char*)buf_.data() + p, name_sz));
+        p += pad(name_sz);
+        const uint64_t dt = p;
+        p += pad(dt_sz);
+        const uint64_t ds = p;
+        p += pad(ds_sz);
+        if (dt_sz < 8 || ((unsigned)rd(dt, 1) & 0x0F) != 3) return;   // class 3 = fixed-length string
+        const uint64_t len = rd(dt + 4, 4);
+        if (len == 0 || ds_sz < 4) return;
+        const unsigned dsver = (unsigned)rd(ds, 1), rank = (unsigned)rd(ds + 1, 1);
+        if ((dsver != 1 && dsver != 2) || rank > 1) return;
+        uint64_t count = 1;
+        if (rank == 1) {
+            const uint64_t dims = ds + (dsver == 1 ? 8 : 4);
+            if (dims + sl_ > ds + ds_sz) return;
+            count = rd(dims, sl_);
+        }
+        if (count > (end - p) / len) return;
+        std::vector<std::string> v;
+        for (uint64_t i = 0; i < count; ++i) {
+            const char* c = (const char*)buf_.data() + p + i * len;
+            v.emplace_back(c, strnlen(c, (size_t)len));
+        }
+        node.string_attrs[name] = std::move(v);
     }
 
     void read_dataset(Node& d, const std::vector<Msg>& msgs) const {
@@ -272,9 +316,26 @@ struct KerasLayer {
 // Walks the file like NeuralNetwork::load: top-level names ascending; each must be a group with
 // exactly one child group; inside, rank-1 datasets are biases, rank-2 kernels.  On a structure the
 // reference rejects, `error` receives its message ("Unsupported Layer", ...) and false is returned.
+//
+// Order of the layers: the reference takes the name-sorted order (listObjectNames), which is the network's order only up to
+// ten layers ("dense_10" sorts before "dense_2").  When the root carries Keras' `layer_names` attribute and it names exactly
+// the groups present, that order is used instead -- identical for every file the reference can load correctly, right for
+// deeper ones.
+inline std::vector<std::string> keras_layer_order(const Node& root) {
+    std::vector<std::string> sorted;
+    for (const auto& kv : root.children) sorted.push_back(kv.first);
+    const auto it = root.string_attrs.find("layer_names");
+    if (it == root.string_attrs.end() || it->second.size() != sorted.size()) return sorted;
+    std::vector<std::string> named = it->second;
+    std::sort(named.begin(), named.end());
+    if (named != sorted) return sorted;   // (sorted is ascending already; duplicates or strangers fail the comparison)
+    return it->second;
+}
+
 inline bool read_keras_layers(const File& f, std::vector<KerasLayer>& out, std::string& error) {
     out.clear();
-    for (const auto& kv : f.root().children) {
+    for (const std::string& lname : keras_layer_order(f.root())) {
+        const auto kv = *f.root().children.find(lname);
         const Node& g = *kv.second;
         if (g.kind != NodeKind::Group) { error = "Unsupported Layer"; return false; }
         if (g.children.size() != 1) { error = "Unsupported Layer"; return false; }
@@ -294,6 +355,190 @@ inline bool read_keras_layers(const File& f, std::vector<KerasLayer>& out, std::
     }
     if (out.empty()) { error = "no layers in file"; return false; }
     return true;
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// Writer for the same subset: what Keras' save_weights + libhdf5 1.10 lay down for a stack of
+// Dense layers, structure by structure (superblock v0, v1 object headers, symbol-table groups with a level-0
+// "TREE", "SNOD" leaves of at most 2*4 entries, local "HEAP" with a trailing free block, contiguous
+// little-endian float32 datasets with dataspace v1 / datatype v1 / fill-value v2 / layout v3 messages,
+// fixed-length-string attributes `layer_names` and `weight_names`).  Byte patterns follow the HDF5 File
+// Format Specification 2.0 and were compared field by field with the shipped data/neuralGeometries files.
+class Writer {
+public:
+    // kernel: [in][out] row-major (Keras); bias: [out].  Layers are written in the given order; the group of
+    // layer i is names[i] (e.g. dense, dense_1, ...).
+    static std::vector<uint8_t> keras_weights(const std::vector<KerasLayer>& layers) {
+        if (layers.empty()) throw FormatError("no layers to write");
+        Writer w;
+        w.buf_.assign(96, 0);
+        std::vector<std::pair<std::string, Child>> top;
+        std::vector<std::string> layer_names;
+        for (const KerasLayer& L : layers) {
+            if (L.kernel_dims.size() != 2 || L.kernel.size() != L.kernel_dims[0] * L.kernel_dims[1] ||
+                L.bias.size() != L.kernel_dims[1] || L.name.empty())
+                throw FormatError("layer '" + L.name + "': kernel [in][out] and bias [out] do not agree");
+            const Child bias = w.dataset({L.bias.size()}, L.bias);
+            const Child kernel = w.dataset({L.kernel_dims[0], L.kernel_dims[1]}, L.kernel);
+            const Child inner = w.group({{"bias:0", bias}, {"kernel:0", kernel}}, {});
+            const Child outer = w.group({{L.name, inner}},
+                                        {string_attr("weight_names", {L.name + "/kernel:0", L.name + "/bias:0"})});
+            top.emplace_back(L.name, outer);
+            layer_names.push_back(L.name);
+        }
+        for (size_t i = 0; i < layer_names.size(); ++i)
+            for (size_t j = i + 1; j < layer_names.size(); ++j)
+                if (layer_names[i] == layer_names[j]) throw FormatError("duplicate layer name '" + layer_names[i] + "'");
+        std::sort(top.begin(), top.end(), [](const auto& a, const auto& b) { return a.first < b.first; });
+        const Child root = w.group(top, {string_attr("layer_names", layer_names), string_attr("backend", {"tensorflow"})});
+        // superblock v0
+        static const uint8_t magic[8] = {0x89, 'H', 'D', 'F', '\r', '\n', 0x1a, '\n'};
+        std::memcpy(w.buf_.data(), magic, 8);
+        w.buf_[13] = 8; w.buf_[14] = 8;            // sizes of offsets and lengths
+        w.put(16, LEAF_K, 2); w.put(18, INTERNAL_K, 2);
+        w.put(24, 0, 8);                            // base address
+        w.put(32, UNDEF, 8);                        // free-space info
+        w.put(40, w.buf_.size(), 8);                // end of file
+        w.put(48, UNDEF, 8);                        // driver info
+        w.put(56, 0, 8); w.put(64, root.header, 8); // root symbol-table entry: name offset, object header
+        w.put(72, 1, 4);                            // cache type 1: scratch holds B-tree and heap addresses
+        w.put(80, root.btree, 8); w.put(88, root.heap, 8);
+        return std::move(w.buf_);
+    }
+
+    static void keras_weights(const std::string& path, const std::vector<KerasLayer>& layers) {
+        const std::vector<uint8_t> bytes = keras_weights(layers);
+        FILE* f = std::fopen(path.c_str(), "wb");
+        if (!f) throw FormatError("unable to create file '" + path + "'");
+        const size_t put = std::fwrite(bytes.data(), 1, bytes.size(), f);
+        if (std::fclose(f) != 0 || put != bytes.size()) throw FormatError("short write on '" + path + "'");
+    }
+
+private:
+    static constexpr uint64_t UNDEF = ~(uint64_t)0;
+    static constexpr unsigned LEAF_K = 4, INTERNAL_K = 16;
+    struct Child { uint64_t header = 0, btree = 0, heap = 0; bool is_group = false; };
+    typedef std::vector<uint8_t> Bytes;   // one header message: type(2) size(2) flags(1) reserved(3) body (multiple of 8)
+    std::vector<uint8_t> buf_;
+
+    uint64_t alloc(size_t n) {
+        const uint64_t off = (buf_.size() + 7u) & ~(uint64_t)7u;
+        buf_.resize(off + n, 0);
+        return off;
+    }
+    void put(uint64_t off, uint64_t v, unsigned n) {
+        for (unsigned i = 0; i < n; ++i) buf_[off + i] = (uint8_t)(v >> (8 * i));
+    }
+    static void app(Bytes& b, uint64_t v, unsigned n) {
+        for (unsigned i = 0; i < n; ++i) b.push_back((uint8_t)(v >> (8 * i)));
+    }
+    static void pad8(Bytes& b) { while (b.size() & 7u) b.push_back(0); }
+    static Bytes message(unsigned type, unsigned flags, Bytes body) {
+        pad8(body);
+        Bytes m;
+        app(m, type, 2); app(m, body.size(), 2); app(m, flags, 1); app(m, 0, 3);
+        m.insert(m.end(), body.begin(), body.end());
+        return m;
+    }
+    static Bytes string_attr(const std::string& name, const std::vector<std::string>& values) {
+        size_t len = 1;
+        for (const std::string& v : values) len = std::max(len, v.size());
+        Bytes b;
+        app(b, 1, 1); app(b, 0, 1); app(b, name.size() + 1, 2); app(b, 8, 2); app(b, 24, 2);
+        b.insert(b.end(), name.begin(), name.end()); b.push_back(0); pad8(b);
+        app(b, 0x13, 1); app(b, 0x01, 1); app(b, 0, 2); app(b, len, 4);                  // string, NUL-padded, ASCII
+        app(b, 1, 1); app(b, 1, 1); app(b, 1, 1); app(b, 0, 5); app(b, values.size(), 8); app(b, values.size(), 8);
+        for (const std::string& v : values) {
+            b.insert(b.end(), v.begin(), v.end());
+            b.insert(b.end(), len - v.size(), 0);
+        }
+        return message(0x000C, 4, b);
+    }
+    uint64_t object_header(const std::vector<Bytes>& msgs) {
+        size_t total = 0;
+        for (const Bytes& m : msgs) total += m.size();
+        const uint64_t at = alloc(16 + total);
+        put(at, 1, 1); put(at + 2, msgs.size(), 2); put(at + 4, 1, 4); put(at + 8, total, 4);
+        uint64_t p = at + 16;
+        for (const Bytes& m : msgs) { std::memcpy(buf_.data() + p, m.data(), m.size()); p += m.size(); }
+        return at;
+    }
+    Child dataset(const std::vector<size_t>& dims, const std::vector<float>& data) {
+        const uint64_t raw = alloc(data.size() * 4);
+        if (!data.empty()) std::memcpy(buf_.data() + raw, data.data(), data.size() * 4);
+        Bytes space, type, fill, layout;
+        app(space, 1, 1); app(space, dims.size(), 1); app(space, 1, 1); app(space, 0, 5);
+        for (size_t d : dims) app(space, d, 8);
+        for (size_t d : dims) app(space, d, 8);                                          // maximum dimensions
+        app(type, 0x11, 1); app(type, 0x20, 1); app(type, 0x1f, 1); app(type, 0, 1); app(type, 4, 4);
+        app(type, 0, 2); app(type, 32, 2); app(type, 23, 1); app(type, 8, 1); app(type, 0, 1); app(type, 23, 1); app(type, 127, 4);
+        app(fill, 2, 1); app(fill, 2, 1); app(fill, 2, 1); app(fill, 1, 1); app(fill, 0, 4);
+        app(layout, 3, 1); app(layout, 1, 1); app(layout, raw, 8); app(layout, data.size() * 4, 8);
+        Child c;
+        c.header = object_header({message(0x0001, 0, space), message(0x0003, 1, type), message(0x0005, 1, fill),
+                                  message(0x0008, 0, layout)});
+        return c;
+    }
+    // children must be sorted by name (strcmp order), at most 2*LEAF_K * 2*INTERNAL_K of them
+    Child group(const std::vector<std::pair<std::string, Child>>& children, const std::vector<Bytes>& attrs) {
+        const size_t per_leaf = 2 * LEAF_K;
+        const size_t n_leaves = children.empty() ? 0 : (children.size() + per_leaf - 1) / per_leaf;
+        if (n_leaves > 2 * INTERNAL_K) throw FormatError("too many entries for a one-level group B-tree");
+        // local heap: "" at offset 0, names 8-aligned, one trailing free block
+        std::vector<uint64_t> name_off;
+        Bytes seg(8, 0);
+        for (const auto& c : children) {
+            name_off.push_back(seg.size());
+            seg.insert(seg.end(), c.first.begin(), c.first.end());
+            seg.push_back(0);
+            pad8(seg);
+        }
+        const uint64_t free_at = seg.size();
+        const uint64_t seg_size = std::max<uint64_t>(88, free_at + 16);
+        seg.resize(seg_size, 0);
+        for (unsigned i = 0; i < 8; ++i) seg[free_at + i] = (uint8_t)(i == 0 ? 1 : 0);            // next free block: none (1)
+        for (unsigned i = 0; i < 8; ++i) seg[free_at + 8 + i] = (uint8_t)((seg_size - free_at) >> (8 * i));
+        Child g;
+        g.is_group = true;
+        g.btree = alloc(24 + (2 * INTERNAL_K + 1) * 8 + 2 * INTERNAL_K * 8);
+        g.heap = alloc(32);
+        const uint64_t seg_at = alloc(seg.size());
+        std::memcpy(buf_.data() + seg_at, seg.data(), seg.size());
+        std::memcpy(buf_.data() + g.heap, "HEAP", 4);
+        put(g.heap + 8, seg_size, 8); put(g.heap + 16, free_at, 8); put(g.heap + 24, seg_at, 8);
+        std::memcpy(buf_.data() + g.btree, "TREE", 4);
+        put(g.btree + 4, 0, 1); put(g.btree + 5, 0, 1); put(g.btree + 6, n_leaves, 2);
+        put(g.btree + 8, UNDEF, 8); put(g.btree + 16, UNDEF, 8);
+        uint64_t kp = g.btree + 24;
+        put(kp, 0, 8);                                                                        // key 0: the empty name
+        for (size_t leaf = 0; leaf < n_leaves; ++leaf) {
+            const size_t first = leaf * per_leaf, last = std::min(children.size(), first + per_leaf);
+            const uint64_t snod = alloc(8 + per_leaf * 40);
+            std::memcpy(buf_.data() + snod, "SNOD", 4);
+            put(snod + 4, 1, 1); put(snod + 6, last - first, 2);
+            for (size_t i = first; i < last; ++i) {
+                const uint64_t e = snod + 8 + (i - first) * 40;
+                const Child& c = children[i].second;
+                put(e, name_off[i], 8); put(e + 8, c.header, 8);
+                if (c.is_group) { put(e + 16, 1, 4); put(e + 24, c.btree, 8); put(e + 32, c.heap, 8); }
+            }
+            put(kp + 8, snod, 8);                                                             // child pointer
+            put(kp + 16, name_off[last - 1], 8);                                              // key: largest name in the child
+            kp += 16;
+        }
+        Bytes stab;
+        app(stab, g.btree, 8); app(stab, g.heap, 8);
+        std::vector<Bytes> msgs;
+        msgs.push_back(message(0x0011, 0, stab));
+        for (const Bytes& a : attrs) msgs.push_back(a);
+        g.header = object_header(msgs);
+        return g;
+    }
+};
+
+inline void write_keras_weights(const std::string& path, const std::vector<KerasLayer>& layers) {
+    Writer::keras_weights(path, layers);
 }
 
 }  // namespace h5

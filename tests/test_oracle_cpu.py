@@ -140,6 +140,59 @@ def test_product_h5_reader_rejects_garbage(built, tmp_path):
     assert L.nsdf_h5_read_keras(str(q).encode(), None, None, 0, None, 0, None) == 10003
 
 
+def _random_layers(dims, seed):
+    rng = np.random.default_rng(seed)
+    return [(rng.standard_normal((dims[i], dims[i + 1])).astype(np.float32), rng.standard_normal(dims[i + 1]).astype(np.float32))
+            for i in range(len(dims) - 1)]
+
+
+def test_h5_writer_round_trips_shipped_files(built, tmp_path):
+    """nsdf_h5_write_keras: a shipped file read, written and read again gives the same floats through the
+    product reader AND through the independent Python parser."""
+    from cudaneuralrender_b200 import host
+    for name in MODELS:
+        layers = host.read_keras_h5(model_path(name))
+        out = str(tmp_path / (name + ".h5"))
+        host.write_keras_h5(out, layers)
+        back = host.read_keras_h5(out)
+        indep = h5mini.load_keras_mlp(out)
+        assert len(back) == len(layers) == len(indep) == 9
+        for (k0, b0), (k1, b1), (k2, b2) in zip(layers, back, indep):
+            assert np.array_equal(k0, k1) and np.array_equal(b0, b1)
+            assert np.array_equal(k0, np.asarray(k2).reshape(k0.shape)) and np.array_equal(b0, np.asarray(b2).ravel())
+
+
+def test_h5_layer_names_order_beyond_ten_layers(built, tmp_path):
+    """Thirteen layers: the name sort of the reference (src/neuralNetwork.cpp:88-91) yields dense, dense_1, dense_10, ...;
+    the product reader follows the root `layer_names` attribute and returns network order.  Other widths and a 4-input
+    first layer go through the same files."""
+    from cudaneuralrender_b200 import host
+    dims = [4, 16, 64, 32, 128, 32, 32, 8, 32, 32, 32, 32, 32, 1]
+    layers = _random_layers(dims, 7)
+    out = str(tmp_path / "deep.h5")
+    host.write_keras_h5(out, layers)
+    back = host.read_keras_h5(out)
+    assert [k.shape for k, _ in back] == [(dims[i], dims[i + 1]) for i in range(13)]
+    for (k0, b0), (k1, b1) in zip(layers, back):
+        assert np.array_equal(k0, k1) and np.array_equal(b0, b1)
+    names = ["dense"] + [f"dense_{i}" for i in range(1, 13)]
+    indep = h5mini.load_keras_mlp(out)                  # name-sorted, like the reference
+    for nm, (k2, b2) in zip(sorted(names), indep):
+        k0, b0 = layers[names.index(nm)]
+        assert np.array_equal(k0, np.asarray(k2).reshape(k0.shape)) and np.array_equal(b0, np.asarray(b2).ravel())
+
+
+def test_h5_writer_rejects_bad_arguments(built, tmp_path):
+    L = _capi().lib()
+    dims = (C.c_int * 2)(3, 0)
+    params = np.zeros(8, dtype=np.float32)
+    pp = params.ctypes.data_as(C.POINTER(C.c_float))
+    assert L.nsdf_h5_write_keras(str(tmp_path / "x.h5").encode(), pp, dims, 1) == 10001
+    assert L.nsdf_h5_write_keras(None, pp, dims, 1) == 10001
+    dims = (C.c_int * 2)(3, 1)
+    assert L.nsdf_h5_write_keras(str(tmp_path / "no_such_dir" / "x.h5").encode(), pp, dims, 1) == 10003
+
+
 def test_png_decoder_matches_pil(built):
     L = _capi().lib()
     for fn in sorted(os.listdir(MATCAPS)):
