@@ -91,11 +91,28 @@ __device__ __forceinline__ float relu_det(float v) { return (v > 0.0f) ? v : 0.0
 // ---- thread-per-point evaluator ---------------------------------------------------------------
 // x[p][0..2] -> y[p].  sw = fused blob in shared memory.  All weight reads are warp-uniform
 // 16-byte loads; with -fmad=false the only FMAs are the explicit ones, in reference order.
+//
+// 4-input (x, y, z, t) animation nets (src/volumeRender_kernel.cu:524-545, `--animation`): in4 == true adds the fourth
+// product, k = 3, to the ascending-k chain with the call-uniform t4 (the frame number); in4 is uniform and false by
+// default, so 3-input callers compile to what they were.
 template <int P>
 __device__ __forceinline__ void mlp32_eval_thread(const float* __restrict__ sw, int n_sq, const float (&x)[P][3],
-                                                  float (&y)[P]) {
+                                                  float (&y)[P], float t4 = 0.0f, bool in4 = false) {
     float a[P][32];
-    {
+    if (in4) {
+        const float4* L0 = reinterpret_cast<const float4*>(sw);
+#pragma unroll
+        for (int oc = 0; oc < 8; ++oc) {
+            const float4 w0 = L0[oc], w1 = L0[8 + oc], w2 = L0[16 + oc], w3 = L0[24 + oc], bb = L0[32 + oc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                a[p][4 * oc + 0] = relu_det(fmaf(w3.x, t4, fmaf(w2.x, x[p][2], fmaf(w1.x, x[p][1], fmaf(w0.x, x[p][0], 0.0f)))) + bb.x);
+                a[p][4 * oc + 1] = relu_det(fmaf(w3.y, t4, fmaf(w2.y, x[p][2], fmaf(w1.y, x[p][1], fmaf(w0.y, x[p][0], 0.0f)))) + bb.y);
+                a[p][4 * oc + 2] = relu_det(fmaf(w3.z, t4, fmaf(w2.z, x[p][2], fmaf(w1.z, x[p][1], fmaf(w0.z, x[p][0], 0.0f)))) + bb.z);
+                a[p][4 * oc + 3] = relu_det(fmaf(w3.w, t4, fmaf(w2.w, x[p][2], fmaf(w1.w, x[p][1], fmaf(w0.w, x[p][0], 0.0f)))) + bb.w);
+            }
+        }
+    } else {
         const float4* L0 = reinterpret_cast<const float4*>(sw);
 #pragma unroll
         for (int oc = 0; oc < 8; ++oc) {
@@ -171,15 +188,24 @@ __device__ __forceinline__ void mlp32_eval_thread(const float* __restrict__ sw, 
 constexpr int WARP_ACT_STRIDE = 36;  // 32 + 4 pad: rows start 4 banks apart (last-layer reads)
 template <int R>
 __device__ __forceinline__ void mlp32_eval_warp(const float* __restrict__ sw, int n_sq, float* __restrict__ abuf,
-                                                const float (&x)[R][3], float (&y)[R], int lane) {
+                                                const float (&x)[R][3], float (&y)[R], int lane, float t4 = 0.0f,
+                                                bool in4 = false) {
     float* cur = abuf;
     float* nxt = abuf + R * WARP_ACT_STRIDE;
     {
         const float w0 = sw[lane], w1 = sw[32 + lane], w2 = sw[64 + lane], bb = sw[128 + lane];
+        if (in4) {
+            const float w3 = sw[96 + lane];
 #pragma unroll
-        for (int r = 0; r < R; ++r)
-            cur[r * WARP_ACT_STRIDE + lane] =
-                relu_det(fmaf(w2, x[r][2], fmaf(w1, x[r][1], fmaf(w0, x[r][0], 0.0f))) + bb);
+            for (int r = 0; r < R; ++r)
+                cur[r * WARP_ACT_STRIDE + lane] =
+                    relu_det(fmaf(w3, t4, fmaf(w2, x[r][2], fmaf(w1, x[r][1], fmaf(w0, x[r][0], 0.0f)))) + bb);
+        } else {
+#pragma unroll
+            for (int r = 0; r < R; ++r)
+                cur[r * WARP_ACT_STRIDE + lane] =
+                    relu_det(fmaf(w2, x[r][2], fmaf(w1, x[r][1], fmaf(w0, x[r][0], 0.0f))) + bb);
+        }
     }
     __syncwarp();
 #pragma unroll 1

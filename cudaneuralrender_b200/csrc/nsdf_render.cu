@@ -70,7 +70,9 @@ void render_release(nsdf_model* m) {
 int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream) {
-    if (!m->fused || m->in[0] != 3) return NSDF_EUNSUPPORTED;
+    if (!m->fused || (m->in[0] != 3 && m->in[0] != 4)) return NSDF_EUNSUPPORTED;
+    // 4-input (x, y, z, t) nets: fp32 tracers only; t = the frame number (createBatch, volumeRender_kernel.cu:532-545)
+    if (m->in[0] == 4 && (opts->flags & NSDF_RENDER_TC_FARFIELD)) return NSDF_EUNSUPPORTED;
     if (opts->tile_world < 1 || opts->tile_rank < 0 || opts->tile_rank >= opts->tile_world) return NSDF_EINVAL;
     if (opts->color_type == NSDF_COLOR_MATCAP && (!d_matcap || mw <= 0 || mh <= 0)) return NSDF_EINVAL;
 
@@ -101,6 +103,8 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.total_idx = (unsigned int)my_tiles * TILE_PIXELS;
     rp.max_steps = opts->max_steps;
     rp.isolate_steps = env_int("NSDF_COOP_ISOLATE", 0);
+    rp.n_in = m->in[0];
+    rp.t4 = (float)cam->frame;
     rp.tile_order = nullptr;
     rp.stats = d_stats;
 

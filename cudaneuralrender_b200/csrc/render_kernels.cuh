@@ -64,6 +64,8 @@ struct RenderParams {
                                    // rays, so the long ray soon runs alone at the 1-ray latency (0 = off)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
                                    // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed
+    int n_in;                      // network inputs: 3 (x, y, z) or 4 (x, y, z, t) -- animation nets, volumeRender_kernel.cu:524-545
+    float t4;                      // the fourth input of every query of this call: (float)frame number (c_frameNumber)
     int hybrid;                    // trace_coop_kernel: producing warps march one ray per LANE (mlp32_eval_thread, 32 rays per warp,
                                    // a third of the shared-memory wavefronts per query) and hand rays that reach evict_steps_hi
                                    // steps to the cooperative consumers on the quiet SMs; out of pixels they become consumers
@@ -246,7 +248,7 @@ __global__ void __launch_bounds__(256, (P >= 2) ? 1 : 2) trace_throughput_kernel
             q[p] = (slot[p].mode >= 0) ? slot_query_point(slot[p]) : f3{0.0f, 0.0f, 0.0f};
             x[p][0] = q[p].x; x[p][1] = q[p].y; x[p][2] = q[p].z;
         }
-        mlp32_eval_thread<P>(s_w, rp.n_sq, x, y);
+        mlp32_eval_thread<P>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
 #pragma unroll
         for (int p = 0; p < P; ++p)
             if (slot[p].mode >= 0) slot_update(slot[p], y[p], q[p], rp, st);
@@ -316,7 +318,7 @@ __global__ void __launch_bounds__(512, 1) trace_latency_kernel(const __grid_cons
             x[r][1] = __shfl_sync(0xffffffffu, q.y, r);
             x[r][2] = __shfl_sync(0xffffffffu, q.z, r);
         }
-        mlp32_eval_warp<R>(s_w, rp.n_sq, abuf, x, y, lane);
+        mlp32_eval_warp<R>(s_w, rp.n_sq, abuf, x, y, lane, rp.t4, rp.n_in == 4);
         float mine = y[0];
 #pragma unroll
         for (int r = 1; r < R; ++r) mine = (lane == r) ? y[r] : mine;
@@ -339,7 +341,7 @@ __global__ void __launch_bounds__(128) trace_simple_kernel(const __grid_constant
     while (__ballot_sync(0xffffffffu, slot.mode >= 0)) {
         const f3 q = (slot.mode >= 0) ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
         float x[1][3] = {{q.x, q.y, q.z}}, y[1];
-        mlp32_eval_thread<1>(s_w, rp.n_sq, x, y);
+        mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
         if (slot.mode >= 0) slot_update(slot, y[0], q, rp, st);
     }
     flush_stats(st, rp.stats);

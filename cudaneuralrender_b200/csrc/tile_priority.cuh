@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__
     for (int k = 0; k < probe_steps; ++k) {
         if (!__ballot_sync(0xffffffffu, marching)) break;
         float x[1][3] = {{p.x, p.y, p.z}}, y[1];
-        mlp32_eval_thread<1>(s_w, rp.n_sq, x, y);
+        mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
         if (marching) {
             const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame);
             tfar = tfar - t;

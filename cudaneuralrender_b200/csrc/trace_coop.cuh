@@ -29,7 +29,7 @@ constexpr int COOP_R = 8;   // ray slots per warp (lanes 0..COOP_R-1 own them)
 // Evaluates the K lowest-ranked active rays of the warp.  src[j] = lane of the j-th active ray.
 template <int K>
 __device__ __forceinline__ float coop_eval(const float* s_w, int n_sq, float* abuf, const f3& q, const int (&src)[COOP_R],
-                                           int rank, int lane) {
+                                           int rank, int lane, float t4, bool in4) {
     float x[K][3], y[K];
 #pragma unroll
     for (int j = 0; j < K; ++j) {
@@ -37,7 +37,7 @@ __device__ __forceinline__ float coop_eval(const float* s_w, int n_sq, float* ab
         x[j][1] = __shfl_sync(0xffffffffu, q.y, src[j]);
         x[j][2] = __shfl_sync(0xffffffffu, q.z, src[j]);
     }
-    mlp32_eval_warp<K>(s_w, n_sq, abuf, x, y, lane);
+    mlp32_eval_warp<K>(s_w, n_sq, abuf, x, y, lane, t4, in4);
     float mine = y[0];
 #pragma unroll
     for (int j = 1; j < K; ++j) mine = (rank == j) ? y[j] : mine;
@@ -65,7 +65,7 @@ __device__ __forceinline__ void lone_ray_march(RaySlot& slot, int owner, const f
     for (int it = 0; it < max_iter; ++it) {
         const float x[1][3] = {{p.x, p.y, p.z}};
         float y[1];
-        mlp32_eval_warp<1>(s_w, n_sq, abuf, x, y, lane);
+        mlp32_eval_warp<1>(s_w, n_sq, abuf, x, y, lane, rp.t4, rp.n_in == 4);
         ++q;
 #ifdef NSDF_DEBUG_TSCALE
         const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame) * NSDF_DEBUG_TSCALE + 2e-6f;
@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             if (!__ballot_sync(0xffffffffu, ps.mode >= 0)) break;
             const f3 q = ps.mode >= 0 ? slot_query_point(ps) : f3{0.0f, 0.0f, 0.0f};
             float x[1][3] = {{q.x, q.y, q.z}}, y[1];
-            mlp32_eval_thread<1>(s_w, rp.n_sq, x, y);
+            mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
             if (ps.mode >= 0) slot_update(ps, y[0], q, rp, st);
             const int n_act = __popc(__ballot_sync(0xffffffffu, ps.mode >= 0));
             const bool drain = dry && n_act <= rp.hybrid;
@@ -249,10 +249,10 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
         }
         const f3 q = active ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
         float mine;
-        if (na > 4) mine = coop_eval<8>(s_w, rp.n_sq, abuf, q, src, rank, lane);
-        else if (na > 2) mine = coop_eval<4>(s_w, rp.n_sq, abuf, q, src, rank, lane);
-        else if (na == 2) mine = coop_eval<2>(s_w, rp.n_sq, abuf, q, src, rank, lane);
-        else mine = coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane);
+        if (na > 4) mine = coop_eval<8>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
+        else if (na > 2) mine = coop_eval<4>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
+        else if (na == 2) mine = coop_eval<2>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
+        else mine = coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
         if (active) slot_update(slot, mine, q, rp, st);
         // ---- long rays leave for the quiet SMs
         if (use_queue && producing)

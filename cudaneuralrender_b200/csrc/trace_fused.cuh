@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 2) trace_fused_kernel(const __g
             if (!act) break;
             const f3 q = (slot.mode >= 0) ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
             float x[1][3] = {{q.x, q.y, q.z}}, y[1];
-            mlp32_eval_thread<1>(s_w, rp.n_sq, x, y);
+            mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
             if (slot.mode >= 0) slot_update(slot, y[0], q, rp, st);
             if (rp.queue) {
                 if ((++it & 3u) == 0u) {
@@ -198,7 +198,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 2) trace_fused_kernel(const __g
                 x[0][0] = __shfl_sync(0xffffffffu, q.x, src);
                 x[0][1] = __shfl_sync(0xffffffffu, q.y, src);
                 x[0][2] = __shfl_sync(0xffffffffu, q.z, src);
-                mlp32_eval_warp<1>(s_w, rp.n_sq, abuf, x, y, (int)lane);
+                mlp32_eval_warp<1>(s_w, rp.n_sq, abuf, x, y, (int)lane, rp.t4, rp.n_in == 4);
                 mine = y[0];
             } else {
                 float x[FUSED_R][3], y[FUSED_R];
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 2) trace_fused_kernel(const __g
                     x[r][1] = __shfl_sync(0xffffffffu, q.y, r);
                     x[r][2] = __shfl_sync(0xffffffffu, q.z, r);
                 }
-                mlp32_eval_warp<FUSED_R>(s_w, rp.n_sq, abuf, x, y, (int)lane);
+                mlp32_eval_warp<FUSED_R>(s_w, rp.n_sq, abuf, x, y, (int)lane, rp.t4, rp.n_in == 4);
                 mine = y[0];
 #pragma unroll
                 for (int r = 1; r < FUSED_R; ++r) mine = ((int)lane == r) ? y[r] : mine;

@@ -103,7 +103,10 @@ void nsdf_model_destroy(nsdf_model* m);
 int nsdf_model_num_layers(const nsdf_model* m);
 /* dims_out receives n_layers+1 ints. */
 int nsdf_model_dims(const nsdf_model* m, int* dims_out);
-/* 1 if the fused kernels apply (3|4 -> 32 x k -> 1, ReLU hidden, linear last), else 0. */
+/* 1 if the fused kernels apply (3|4 -> 32 x k -> 1, ReLU hidden, linear last), else 0.  4-input nets are the reference's
+ * --animation mode (x, y, z, t; src/volumeRender_kernel.cu:524-545): nsdf_render feeds t = (float)cam->frame to every query
+ * (fp32 schedules only; NSDF_RENDER_TC_FARFIELD returns NSDF_EUNSUPPORTED); nsdf_mlp_forward takes B x 4 inputs through the
+ * layer-by-layer kernels. */
 int nsdf_model_is_fused(const nsdf_model* m);
 /* Copies the packed host parameters (layout of nsdf_model_create_packed) into params_out
  * (capacity in floats); returns the number of floats through n_out. */

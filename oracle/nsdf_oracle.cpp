@@ -311,8 +311,9 @@ template <int L>
 void render_block(const Model& m, const Camera& cam, const uint32_t* matcap, int mw, int mh, int color_type,
                   int scene, int W, int H, int max_steps, const int* px, const int* py, int n, uint32_t* out,
                   int32_t* steps_out, uint8_t* hit_out, int64_t& queries, float* scratch) {
-    float* xin = scratch;                       // [3][L]
-    float* yout = xin + 3 * L;                  // [L]
+    const int in0 = m.in[0];                    // 3, or 4 for (x, y, z, t) animation nets
+    float* xin = scratch;                       // [in0][L]
+    float* yout = xin + in0 * L;                // [L]
     float* s0 = yout + L;                       // [max_width][L]
     float* s1 = s0 + (size_t)m.max_width * L;
     Ray ray[L];
@@ -340,6 +341,9 @@ void render_block(const Model& m, const Camera& cam, const uint32_t* matcap, int
                        fmaf(t[2], NORMAL_EPSILON, ray[j].p.z)};
             }
             xin[0 * L + j] = q.x; xin[1 * L + j] = q.y; xin[2 * L + j] = q.z;
+            // createBatch :532-545: the fourth input of every request is c_frameNumber.  (For the four normal requests the
+            // reference strides its writes by 3 instead of 4 and scrambles them; this is the intended layout)
+            if (in0 == 4) xin[3 * L + j] = (float)cam.frame;
         }
         mlp_block<L>(m, xin, yout, s0, s1);
         for (int j = 0; j < L; ++j) {
@@ -521,7 +525,7 @@ int oracle_render_rows(const float* params, const int* dims, int n_layers, const
     if (n_layers <= 0 || W <= 0 || H <= 0 || ystride <= 0 || y0 < 0 || y1 > H) return 1;
     if (color_type != 0 && (!matcap || mw <= 0 || mh <= 0)) return 2;
     const Model m = make_model(params, dims, n_layers);
-    if (m.in[0] != 3 || m.out[n_layers - 1] != 1) return 3;
+    if ((m.in[0] != 3 && m.in[0] != 4) || m.out[n_layers - 1] != 1) return 3;
     Camera cam{};
     std::memcpy(cam.inv_view, inv_view12, sizeof(cam.inv_view));
     std::memcpy(cam.normal, normal16, sizeof(cam.normal));
@@ -531,7 +535,7 @@ int oracle_render_rows(const float* params, const int* dims, int n_layers, const
     const int64_t nblocks = (N + LANES - 1) / LANES;
     std::atomic<int64_t> total_q(0);
     parallel_for(nblocks, nthreads, [&](int64_t b0, int64_t b1, int) {
-        std::vector<float> scratch((size_t)(4 + 2 * m.max_width) * LANES);
+        std::vector<float> scratch((size_t)(5 + 2 * m.max_width) * LANES);
         int64_t q = 0;
         int px[LANES], py[LANES];
         for (int64_t blk = b0; blk < b1; ++blk) {

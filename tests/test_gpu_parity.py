@@ -272,6 +272,52 @@ def test_frame_schedules_agree(env):
     assert outs[4]["evicted"] > 0 and outs[6]["evicted"] > 0 and outs[0]["evicted"] == 0
 
 
+def test_animation_net_frames_bit_exact(env, tmp_path):
+    """4-input (x, y, z, t) nets, the reference's --animation mode (src/volumeRender_kernel.cu:524-545, t = frame number):
+    a shipped shape with a fourth input row added to its first layer is written with nsdf_h5_write_keras, loaded through
+    the product reader and rendered at several frame numbers by every schedule; frames equal the oracle's bytes, frame 0
+    equals the 3-input shape's frame (the fourth product is exactly 0), later frames differ from it."""
+    torch, host, oracle, capi = env["torch"], env["host"], env["oracle"], env["capi"]
+    layers = host.read_keras_h5(model_path("car_1"))
+    rng = np.random.default_rng(11)
+    k0, b0 = layers[0]
+    layers[0] = (np.concatenate([k0, (0.02 * rng.standard_normal((1, k0.shape[1]))).astype(np.float32)], axis=0), b0)
+    path = str(tmp_path / "car_xyzt.h5")
+    host.write_keras_h5(path, layers)
+    nn = host.NeuralNetwork()
+    assert nn.load(path) and nn.layers[0].getXDim() == 4
+    om = oracle.Model.from_h5(path)
+    matcap = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    iv, nm = oracle.view_matrices(0.0, 20.0)
+    W, H = 112, 80
+    host.copyStaticSettings(host.COLOR_MATCAP, 4)
+    frames = {}
+    try:
+        for frame in (0, 3, 17):
+            host.copyViewMatrices(iv, nm, frame, 4)
+            ref = oracle.render(om, iv, nm, W, H, matcap=matcap, frame=frame)
+            for flags in (0, capi.RENDER_SIMPLE, capi.RENDER_NO_STRAGGLER, capi.RENDER_TWO_PASS, capi.RENDER_HYBRID, capi.RENDER_QUEUE):
+                host.setSceneOptions(host.SCENE_TANH, 6000, flags, 0)
+                img, stats = host.render_host(nn, W, H, matcap)
+                assert np.array_equal(img, ref["image"]), (frame, flags)
+                assert stats["queries"] == ref["queries"]
+            frames[frame] = ref["image"]
+        img3, _, ref3 = _render_both(env, "car_1", W, H, "blue.png", ry=20.0)
+        assert np.array_equal(frames[0], ref3["image"]) and np.array_equal(img3, frames[0])
+        assert not np.array_equal(frames[3], frames[0]) and not np.array_equal(frames[17], frames[3])
+        # the tensor-core far field is a 3-input path
+        host.setSceneOptions(host.SCENE_TANH, 6000, capi.RENDER_TC_FARFIELD, 0)
+        with pytest.raises(Exception):
+            host.render_host(nn, W, H, matcap)
+    finally:
+        host.setSceneOptions()
+        host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    # dense forward of the same net: layer-by-layer path, bits of the oracle
+    x = rng.uniform(-1, 1, (4096, 4)).astype(np.float32)
+    y = nn.forward_host(x)
+    assert np.array_equal(_bits(y), _bits(oracle.mlp_forward(om, x).ravel()))
+
+
 def test_tile_priority_order_is_invisible(env):
     """tile_priority.cuh: probing and re-ordering the tiles (forced on for this small frame, also for a 3-rank tile
     partition and the two-pass / mixed schedules) must not change a byte of an exact frame or a query of its count."""

@@ -182,6 +182,39 @@ def test_h5_layer_names_order_beyond_ten_layers(built, tmp_path):
         assert np.array_equal(k0, np.asarray(k2).reshape(k0.shape)) and np.array_equal(b0, np.asarray(b2).ravel())
 
 
+def test_oracle_animation_net_frame0_equals_static_net(built, tmp_path):
+    """Oracle, 4-input (x, y, z, t) nets (src/volumeRender_kernel.cu:524-545): with t = frame = 0 the fourth product of the
+    first layer is exactly 0, so the frame equals the 3-input shape's; a later frame differs; the dense forward agrees with
+    a float64-free numpy restatement of the same ascending-k chain on a few points."""
+    from cudaneuralrender_b200 import host
+    layers = host.read_keras_h5(model_path("car_1"))
+    rng = np.random.default_rng(11)
+    k0, b0 = layers[0]
+    layers[0] = (np.concatenate([k0, (0.02 * rng.standard_normal((1, k0.shape[1]))).astype(np.float32)], axis=0), b0)
+    path = str(tmp_path / "car_xyzt.h5")
+    host.write_keras_h5(path, layers)
+    om4, om3 = oracle.Model.from_h5(path), oracle.Model.from_h5(model_path("car_1"))
+    assert list(om4.dims) == [4] + [32] * 8 + [1]
+    iv, nm = oracle.view_matrices(0.0, 20.0)
+    a = oracle.render(om4, iv, nm, 64, 48, frame=0)
+    b = oracle.render(om3, iv, nm, 64, 48, frame=0)
+    c = oracle.render(om4, iv, nm, 64, 48, frame=9)
+    assert np.array_equal(a["image"], b["image"]) and a["queries"] == b["queries"]
+    assert not np.array_equal(c["image"], a["image"])
+    x = rng.uniform(-1, 1, (5, 4)).astype(np.float32)
+    x[:, 3] = 9.0
+    y = oracle.mlp_forward(om4, x).ravel()
+    for i in range(5):
+        act = x[i]
+        for li, (k, bias) in enumerate(layers):
+            z = np.zeros(k.shape[1], dtype=np.float32)
+            for kk in range(k.shape[0]):   # ascending k, one rounding per fused multiply-add
+                z = (k[kk].astype(np.float64) * np.float64(act[kk]) + z.astype(np.float64)).astype(np.float32)
+            z = z + bias
+            act = np.maximum(z, 0) if li < len(layers) - 1 else z
+        assert act[0] == y[i]
+
+
 def test_h5_writer_rejects_bad_arguments(built, tmp_path):
     L = _capi().lib()
     dims = (C.c_int * 2)(3, 0)
