@@ -11,7 +11,6 @@ LIB_PATH = os.path.join(_HERE, "libnsdf.so")
 NSDF_OK = 0
 ACT_RELU, ACT_TANH_LINEAR = 0, 1
 PREC_FP32, PREC_TC_FP16, PREC_TC_BF16, PREC_TC_FP16X3, PREC_FP32_WARP, PREC_TC_FP16_ACC16 = 0, 1, 2, 3, 4, 5
-SCENE_TANH, SCENE_MANYSPHERE = 0, 1
 COLOR_FACING, COLOR_MATCAP = 0, 1
 RENDER_SIMPLE, RENDER_NO_STRAGGLER, RENDER_PHASE_THROUGHPUT, RENDER_PHASE_LATENCY, RENDER_TWO_KERNELS, RENDER_QUEUE, RENDER_NO_QUIET_SMS, RENDER_TC_FARFIELD, RENDER_TWO_PASS, RENDER_HYBRID = 1, 2, 4, 8, 16, 32, 64, 128, 256, 512
 IPC_HANDLE_BYTES = 64
@@ -21,9 +20,32 @@ class Camera(C.Structure):
     _fields_ = [("inv_view", C.c_float * 12), ("normal", C.c_float * 16), ("frame", C.c_int)]
 
 
+class SceneOp(C.Structure):
+    """nsdf_scene_op (include/nsdf.h): one step of a scene program."""
+    _fields_ = [("prim", C.c_int), ("combine", C.c_int), ("a", C.c_float * 8)]
+
+
 class RenderOpts(C.Structure):
     _fields_ = [("color_type", C.c_int), ("scene", C.c_int), ("max_steps", C.c_int), ("tile_rank", C.c_int),
-                ("tile_world", C.c_int), ("evict_steps", C.c_int), ("flags", C.c_int)]
+                ("tile_world", C.c_int), ("evict_steps", C.c_int), ("flags", C.c_int), ("program", C.POINTER(SceneOp)),
+                ("n_ops", C.c_int)]
+
+
+SCENE_TANH, SCENE_MANYSPHERE, SCENE_PROGRAM = 0, 1, 2
+PRIM_NSDF, PRIM_TANH, PRIM_SPHERE, PRIM_BOX, PRIM_PLANE, PRIM_CYLINDER = range(6)
+MOD_DISPLACE, MOD_ROUND, MOD_ONION, MOD_MANY_SPHERE, MOD_MANY_CYLINDER_CUT = range(16, 21)
+(COMB_SET, COMB_UNION, COMB_INTERSECT, COMB_SUBTRACT, COMB_SUBTRACT_FROM, COMB_SMOOTH_UNION, COMB_SMOOTH_SUBTRACT,
+ COMB_SMOOTH_SUBTRACT_FROM) = range(8)
+
+
+def scene_ops(ops):
+    """[(prim, combine, [a0..]) ...] -> (SceneOp * n) array."""
+    arr = (SceneOp * len(ops))()
+    for i, (prim, comb, a) in enumerate(ops):
+        arr[i].prim, arr[i].combine = int(prim), int(comb)
+        for j, v in enumerate(a):
+            arr[i].a[j] = float(v)
+    return arr
 
 
 class RenderStats(C.Structure):
@@ -61,6 +83,7 @@ PROTOTYPES = {
     "nsdf_mlp_forward_lattice": (_i, [_vp, _vp, _i, _f, _f, _i64, _i64, _i, _vp]),
     "nsdf_dense_layer_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "nsdf_render_opts_default": (None, [C.POINTER(RenderOpts)]),
+    "nsdf_scene_eval": (_i, [C.POINTER(SceneOp), _i, _vp, _vp, _i, _vp, _i64, _vp]),
     "nsdf_camera_from_view": (None, [_f, _f, _f, _f, _f, _i, C.POINTER(Camera)]),
     "nsdf_render": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
     "nsdf_render_host": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i,

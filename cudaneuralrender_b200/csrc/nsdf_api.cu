@@ -398,6 +398,14 @@ void nsdf_render_opts_default(nsdf_render_opts* o) {
     o->tile_world = 1;
     o->evict_steps = 0;
     o->flags = 0;
+    o->program = nullptr;
+    o->n_ops = 0;
+}
+
+int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+                    float* d_out, int64_t n, void* stream) {
+    if (n < 0 || (n > 0 && (!d_xyz || !d_nsdf || !d_out))) return NSDF_EINVAL;
+    return nsdf::scene_eval_launch(program, n_ops, d_xyz, d_nsdf, frame, d_out, n, (cudaStream_t)stream);
 }
 
 // updateViewMatrices, src/main.cpp:207-222.  Eigen composes AngleAxis(-rx, X) * AngleAxis(-ry, Y)

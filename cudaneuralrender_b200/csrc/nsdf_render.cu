@@ -67,6 +67,41 @@ void render_release(nsdf_model* m) {
     m->queue_capacity = 0;
 }
 
+// nsdf_scene_op list (host) -> kernel-parameter form; rejects unknown opcodes so that a typo is an error, not a scene
+int scene_program_pack(const nsdf_scene_op* program, int n_ops, SceneProgram* out) {
+    if (!program || n_ops < 1 || n_ops > SCENE_MAX_OPS) return NSDF_EINVAL;
+    static_assert(sizeof(SceneOp) == sizeof(nsdf_scene_op) && SCENE_MAX_OPS == NSDF_SCENE_MAX_OPS, "scene op layout");
+    std::memset(out, 0, sizeof(*out));
+    out->n_ops = n_ops;
+    for (int i = 0; i < n_ops; ++i) {
+        const int pr = program[i].prim, cb = program[i].combine;
+        const bool prim_ok = (pr >= NSDF_PRIM_NSDF && pr <= NSDF_PRIM_CYLINDER);
+        const bool mod_ok = (pr >= NSDF_MOD_DISPLACE && pr <= NSDF_MOD_MANY_CYLINDER_CUT);
+        if (!prim_ok && !mod_ok) return NSDF_EINVAL;
+        if (prim_ok && (cb < NSDF_COMB_SET || cb > NSDF_COMB_SMOOTH_SUBTRACT_FROM)) return NSDF_EINVAL;
+        std::memcpy(&out->ops[i], &program[i], sizeof(SceneOp));
+    }
+    return NSDF_OK;
+}
+
+__global__ void __launch_bounds__(256) scene_eval_kernel(const __grid_constant__ SceneProgram prog, const float* __restrict__ xyz,
+                                                         const float* __restrict__ nsdf, int frame, float* __restrict__ out,
+                                                         int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = scene_program_eval(prog, f3{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}, nsdf[i], frame);
+}
+
+int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+                      float* d_out, int64_t n, cudaStream_t stream) {
+    SceneProgram prog;
+    const int rc = scene_program_pack(program, n_ops, &prog);
+    if (rc) return rc;
+    if (n <= 0) return NSDF_OK;
+    scene_eval_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, stream>>>(prog, d_xyz, d_nsdf, frame, d_out, n);
+    return (int)cudaGetLastError();
+}
+
 int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream) {
@@ -89,6 +124,12 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.mh = mh;
     rp.color_type = opts->color_type;
     rp.scene = opts->scene;
+    if (opts->scene == NSDF_SCENE_PROGRAM) {
+        const int rc_prog = scene_program_pack(opts->program, opts->n_ops, &rp.prog);
+        if (rc_prog) return rc_prog;
+    } else if (opts->scene != NSDF_SCENE_TANH && opts->scene != NSDF_SCENE_MANYSPHERE) {
+        return NSDF_EINVAL;
+    }
     rp.out = d_out;
     rp.W = W;
     rp.H = H;

@@ -20,6 +20,7 @@
 // =====================================================================================
 #pragma once
 #include "device_math.cuh"
+#include "scene_program.cuh"
 #include "mlp_fp32.cuh"
 #include "../../include/nsdf.h"
 
@@ -64,6 +65,7 @@ struct RenderParams {
                                    // rays, so the long ray soon runs alone at the 1-ray latency (0 = off)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
                                    // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed
+    SceneProgram prog;             // scene == NSDF_SCENE_PROGRAM: the op list (scene_program.cuh)
     int n_in;                      // network inputs: 3 (x, y, z) or 4 (x, y, z, t) -- animation nets, volumeRender_kernel.cu:524-545
     float t4;                      // the fourth input of every query of this call: (float)frame number (c_frameNumber)
     int hybrid;                    // trace_coop_kernel: producing warps march one ray per LANE (mlp32_eval_thread, 32 rays per warp,
@@ -71,6 +73,12 @@ struct RenderParams {
                                    // steps to the cooperative consumers on the quiet SMs; out of pixels they become consumers
     nsdf_render_stats* stats;
 };
+
+// sceneSDF (volumeRender_kernel.cu:217-230) of this call: one of the two compiled scenes, or the op list
+__device__ __forceinline__ float scene_eval(const RenderParams& rp, f3 p, float nsdf) {
+    if (rp.scene == NSDF_SCENE_PROGRAM) return scene_program_eval(rp.prog, p, nsdf, rp.cam.frame);
+    return scene_sdf(rp.scene, p, nsdf, rp.cam.frame);
+}
 
 struct RaySlot {
     int pix;      // linear pixel id y*W+x
@@ -105,7 +113,7 @@ __device__ __forceinline__ f3 slot_query_point(const RaySlot& s) {
 __device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const RenderParams& rp, LocalStats& st) {
     ++st.queries;
     if (s.mode > 0) {
-        const float sv = scene_sdf(rp.scene, q, nsdf, rp.cam.frame);
+        const float sv = scene_eval(rp, q, nsdf);
         if (s.mode == 1) s.s0 = sv;
         else if (s.mode == 2) s.s1 = sv;
         else if (s.mode == 3) s.s2 = sv;
@@ -119,9 +127,9 @@ __device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const 
         return;
     }
 #ifdef NSDF_DEBUG_TSCALE   // development: every ray crawls and runs to max_steps (per-step latency probe)
-    const float t = scene_sdf(rp.scene, s.p, nsdf, rp.cam.frame) * NSDF_DEBUG_TSCALE + 2e-6f;
+    const float t = scene_eval(rp, s.p, nsdf) * NSDF_DEBUG_TSCALE + 2e-6f;
 #else
-    const float t = scene_sdf(rp.scene, s.p, nsdf, rp.cam.frame);
+    const float t = scene_eval(rp, s.p, nsdf);
 #endif
     s.tfar = s.tfar - t;
     ++s.steps;

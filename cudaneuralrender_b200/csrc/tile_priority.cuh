@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__
         float x[1][3] = {{p.x, p.y, p.z}}, y[1];
         mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
         if (marching) {
-            const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame);
+            const float t = scene_eval(rp, p, y[0]);
             tfar = tfar - t;
             if (tfar <= 0.0f || t < NSDF_MARCHING_EPSILON) marching = false;
             else p = f3{fmaf(d.x, t, p.x), fmaf(d.y, t, p.y), fmaf(d.z, t, p.z)};

@@ -68,9 +68,9 @@ __device__ __forceinline__ void lone_ray_march(RaySlot& slot, int owner, const f
         mlp32_eval_warp<1>(s_w, n_sq, abuf, x, y, lane, rp.t4, rp.n_in == 4);
         ++q;
 #ifdef NSDF_DEBUG_TSCALE
-        const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame) * NSDF_DEBUG_TSCALE + 2e-6f;
+        const float t = scene_eval(rp, p, y[0]) * NSDF_DEBUG_TSCALE + 2e-6f;
 #else
-        const float t = scene_sdf(rp.scene, p, y[0], rp.cam.frame);
+        const float t = scene_eval(rp, p, y[0]);
 #endif
         tfar = tfar - t;
         ++steps;

@@ -133,7 +133,7 @@ trace_tc_kernel(const __grid_constant__ RenderParams rp, const TraceTcParams tp)
         bool hand_over = false;
         if (active) {
             ++st.queries;
-            const float t = scene_sdf(rp.scene, slot.p, nsdf, rp.cam.frame);
+            const float t = scene_eval(rp, slot.p, nsdf);
             if (t >= tp.thr) {
                 const float ts = t - tp.margin;
                 slot.tfar = slot.tfar - ts;

@@ -19,7 +19,7 @@ import torch
 
 from . import _capi as capi
 from ._capi import (ACT_RELU, ACT_TANH_LINEAR, COLOR_FACING, COLOR_MATCAP, PREC_FP32, PREC_FP32_WARP, PREC_TC_BF16,
-                    PREC_TC_FP16, PREC_TC_FP16_ACC16, PREC_TC_FP16X3, SCENE_MANYSPHERE, SCENE_TANH, Camera, RenderOpts, RenderStats)
+                    PREC_TC_FP16, PREC_TC_FP16_ACC16, PREC_TC_FP16X3, SCENE_MANYSPHERE, SCENE_PROGRAM, SCENE_TANH, Camera, RenderOpts, RenderStats)
 
 ReLU, Tanh = ACT_RELU, ACT_TANH_LINEAR  # enum Activation, src/layers/denseLayer.hh:6-9
 
@@ -360,6 +360,7 @@ class _RenderState:
         self.color_type = COLOR_FACING
         self.num_inputs = 3
         self.scene = SCENE_TANH
+        self.program = None     # (SceneOp * n) for SCENE_PROGRAM
         self.max_steps = 6000
         self.flags = 0
         self.evict_steps = 0
@@ -399,6 +400,32 @@ def updateViewMatrices(viewRotation=(0.0, 0.0, 0.0), viewTranslation=(0.0, 0.0, 
 def setSceneOptions(scene: int = SCENE_TANH, max_steps: int = 6000, flags: int = 0, evict_steps: int = 0):
     """Compile-time settings of the reference (sceneSDF variant, MAX_STEPS) as run-time options."""
     _state.scene, _state.max_steps, _state.flags, _state.evict_steps = int(scene), int(max_steps), int(flags), int(evict_steps)
+    if _state.scene != SCENE_PROGRAM:
+        _state.program = None
+
+
+def setSceneProgram(ops, max_steps: int = 6000, flags: int = 0, evict_steps: int = 0):
+    """Run-time form of editing sceneSDF (src/volumeRender_kernel.cu:217-230): ops = [(prim, combine, [params]) ...] over the
+    reference's analytic SDF library (:67-196), see include/nsdf.h nsdf_scene_op."""
+    setSceneOptions(SCENE_PROGRAM, max_steps, flags, evict_steps)
+    _state.program = ops if not isinstance(ops, (list, tuple)) else capi.scene_ops(ops)
+
+
+def _opts(tile_rank: int = 0, tile_world: int = 1) -> RenderOpts:
+    o = RenderOpts(_state.color_type, _state.scene, _state.max_steps, tile_rank, tile_world, _state.evict_steps, _state.flags)
+    if _state.program is not None:
+        o.program = C.cast(_state.program, C.POINTER(capi.SceneOp))
+        o.n_ops = len(_state.program)
+    return o
+
+
+def scene_eval(ops, xyz: torch.Tensor, nsdf: torch.Tensor, frame: int = 0) -> torch.Tensor:
+    """nsdf_scene_eval: the program's sceneSDF at n device points with given network outputs."""
+    prog = ops if not isinstance(ops, (list, tuple)) else capi.scene_ops(ops)
+    out = torch.empty_like(nsdf)
+    capi.check(capi.lib().nsdf_scene_eval(C.cast(prog, C.POINTER(capi.SceneOp)), len(prog), xyz.data_ptr(), nsdf.data_ptr(),
+                                          frame, out.data_ptr(), nsdf.numel(), _stream_ptr()), "nsdf_scene_eval")
+    return out
 
 
 def render_kernel(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNetwork, matcap: Optional[Image] = None,
@@ -408,8 +435,7 @@ def render_kernel(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNe
     meaning for the persistent tracer and are dropped.  d_output: W*H int32/uint32 device tensor
     (or d_output_ptr: a raw, possibly peer-mapped, device address).  stats: 6 x int64 device tensor
     accumulated into (nsdf_render_stats)."""
-    opts = RenderOpts(_state.color_type, _state.scene, _state.max_steps, tile_rank, tile_world, _state.evict_steps,
-                      _state.flags)
+    opts = _opts(tile_rank, tile_world)
     mat_ptr, mw, mh = None, 0, 0
     if matcap is not None and matcap.deviceData is not None:
         mat_ptr, mw, mh = matcap.deviceData.data_ptr(), matcap.shape.x, matcap.shape.y
@@ -421,7 +447,7 @@ def render_kernel(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNe
 
 def render_host(nn: NeuralNetwork, imageW: int, imageH: int, matcap: Optional[np.ndarray] = None):
     """Host-buffer call (nsdf_render_host): uploads the matcap, renders, returns (uint32[H,W], stats dict)."""
-    opts = RenderOpts(_state.color_type, _state.scene, _state.max_steps, 0, 1, _state.evict_steps, _state.flags)
+    opts = _opts()
     out = np.empty((imageH, imageW), dtype=np.uint32)
     st = RenderStats()
     mp, mw, mh = None, 0, 0

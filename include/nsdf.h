@@ -49,6 +49,42 @@ extern "C" {
 /* Scene functions: sceneSDF, src/volumeRender_kernel.cu:217-230. */
 #define NSDF_SCENE_TANH 0       /* tanh(nSDF)  (:229, the shipped renders)                 */
 #define NSDF_SCENE_MANYSPHERE 1 /* manySphere(p, nSDF, true)  (:221, what HEAD evaluates)  */
+#define NSDF_SCENE_PROGRAM 2    /* nsdf_render_opts.program: the analytic-SDF library of :67-196 composed at run time */
+
+/* ---- scene programs: the reference's analytic SDF primitives and operators (src/volumeRender_kernel.cu:67-196), which it
+ * composes by editing sceneSDF (:217-230) and recompiling, as data.  A program is a chain over one accumulator s:
+ *     for each op:  d = primitive(p, nSDF);  s = combine(s, d)        (modifiers act on s alone)
+ * and the scene's distance is the final s.  Every scene the reference's sceneSDF holds (live or commented out) is such a
+ * chain.  Arithmetic: fp32 as written in the reference, its double-promoting literals kept, tanh / saturate / sin in the
+ * deterministic forms of DESIGN.md section 4; device and oracle agree bit for bit.                                          */
+typedef struct nsdf_scene_op {
+    int prim;    /* NSDF_PRIM_* or NSDF_MOD_*                                   */
+    int combine; /* NSDF_COMB_* (ignored for modifiers)                         */
+    float a[8];  /* parameters, see below                                       */
+} nsdf_scene_op;
+#define NSDF_SCENE_MAX_OPS 16
+/* primitives: d = ...                                                                                          */
+#define NSDF_PRIM_NSDF 0     /* the network output, raw                                                          */
+#define NSDF_PRIM_TANH 1     /* tanh(nSDF) (:229)                                                                */
+#define NSDF_PRIM_SPHERE 2   /* sdfSphere(p - a[0..2], a[3])                                       (:67-71)      */
+#define NSDF_PRIM_BOX 3      /* sdfBox(p - a[0..2], b = a[3..5], r = a[6])                          (:81-89)      */
+#define NSDF_PRIM_PLANE 4    /* sdfPlane: p.y - a[0]  (the reference hard-codes 0.5)                (:91-94)      */
+#define NSDF_PRIM_CYLINDER 5 /* sdfCylinder(p - a[0..2], c = a[3..5]): length(p.xy - (c.x, c.z)) - c.y (:96-101) */
+/* modifiers: s = ...                                                                                           */
+#define NSDF_MOD_DISPLACE 16 /* sdfOpDisplace: s + sin(a[0] x) sin(a[0] y) sin(a[0] z) * a[1]  (5, 0.05 in :103-110) */
+#define NSDF_MOD_ROUND 17    /* sdfOpRound: s - a[0]                                                (:112-115)    */
+#define NSDF_MOD_ONION 18    /* sdfOpOnion: |s| - a[0]                                              (:117-120)    */
+#define NSDF_MOD_MANY_SPHERE 19        /* manySphere(p, s, a[0] != 0)   (:176-196, animated by the frame number)  */
+#define NSDF_MOD_MANY_CYLINDER_CUT 20  /* manyCylinderCut(p, s)         (:156-174)                                */
+/* combiners: s = ...                                                                                           */
+#define NSDF_COMB_SET 0              /* d                                                                        */
+#define NSDF_COMB_UNION 1            /* min(s, d)                                                   (:128-131)    */
+#define NSDF_COMB_INTERSECT 2        /* max(s, d)                                                   (:123-126)    */
+#define NSDF_COMB_SUBTRACT 3         /* max(s, -d): d carved out of s                               (:133-136)    */
+#define NSDF_COMB_SUBTRACT_FROM 4    /* max(d, -s): s carved out of d                                            */
+#define NSDF_COMB_SMOOTH_UNION 5     /* sdfOpSmoothUnion(s, d, k = a[7])                            (:144-149)    */
+#define NSDF_COMB_SMOOTH_SUBTRACT 6  /* sdfOpSmoothSubtraction(s, d, k = a[7])                      (:138-142)    */
+#define NSDF_COMB_SMOOTH_SUBTRACT_FROM 7 /* sdfOpSmoothSubtraction(d, s, k = a[7])  (the commented scene of :225-227) */
 
 /* c_coloringType, src/volumeRender_kernel.cu:33 */
 #define NSDF_COLOR_FACING 0
@@ -149,6 +185,8 @@ typedef struct nsdf_render_opts {
     int tile_world;   /* 1 = whole frame                                                   */
     int evict_steps;  /* rays still marching after this many steps move to the latency path; 0 = library default */
     int flags;        /* NSDF_RENDER_* bits                                                */
+    const nsdf_scene_op* program; /* HOST array, read during the call; used when scene == NSDF_SCENE_PROGRAM */
+    int n_ops;        /* 1..NSDF_SCENE_MAX_OPS                                             */
 } nsdf_render_opts;
 
 #define NSDF_RENDER_SIMPLE 1u      /* one-thread-per-pixel kernel without refill (debug / A-B testing) */
@@ -182,6 +220,10 @@ typedef struct nsdf_render_stats {
 
 /* Fills opts with the reference's compile-time settings (tanh scene, 6000 steps, whole frame). */
 void nsdf_render_opts_default(nsdf_render_opts* opts);
+/* sceneSDF for n points on the device: d_out[i] = program(d_xyz[3i..3i+2], d_nsdf[i]) with c_frameNumber = frame
+ * (what singleMarch :459 and surfaceNormal :361-377 evaluate per query).  program is a HOST array. */
+int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+                    float* d_out, int64_t n, void* stream);
 
 /* updateViewMatrices (src/main.cpp:207-222): modelView from viewRotation (degrees) and
  * viewTranslation, without Eigen.  Host-side helper. */

@@ -204,12 +204,153 @@ inline float many_sphere_union(f3 p, float nsdf, int frame) {
     return s;
 }
 
-enum Scene { SCENE_TANH = 0, SCENE_MANYSPHERE = 1 };
+// ---- the rest of the analytic library, src/volumeRender_kernel.cu:67-174.  Dead code in the reference build
+// (sceneSDF returns before reaching it), so there is no SASS to read contraction from: fp32 as written, the source's
+// double-promoting literals as double operations, dot products the way nvcc contracts helper_math's dot
+// (fma(z,z, fma(x,x, y*y))), min/max with explicit NaN rules, sin by the deterministic form below.
+inline float min_det(float a, float b) { return (a != a) ? b : ((b != b) ? a : ((b < a) ? b : a)); }
+inline float max_det(float a, float b) { return (a != a) ? b : ((b != b) ? a : ((b > a) ? b : a)); }
+
+// sin (sdfOpDisplace :103-110 calls sinf): Cody-Waite by pi/2 in three parts, Cephes sinf/cosf kernels on |r| <= pi/4
+inline float sinf_det(float x) {
+    if (!(fabsf(x) < 1.0e6f)) return x - x;
+    const float q = rintf(x * 0.636619772f);
+    float r = fmaf(q, -1.5703125f, x);
+    r = fmaf(q, -4.837512969970703125e-4f, r);
+    r = fmaf(q, -7.54978995489188216e-8f, r);
+    const int n = (int)q;
+    const float z = r * r;
+    const float sn = fmaf(fmaf(fmaf(-1.9515295891e-4f, z, 8.3321608736e-3f), z, -1.6666654611e-1f) * z, r, r);
+    const float cs = fmaf(fmaf(fmaf(2.443315711809948e-5f, z, -1.388731625493765e-3f), z, 4.166664568298827e-2f) * z, z,
+                          fmaf(-0.5f, z, 1.0f));
+    const float v = (n & 1) ? cs : sn;
+    return (n & 2) ? -v : v;
+}
+
+// sdfOpSmoothSubtraction :138-142: h = saturate(0.5 - 0.5*(d1+d2)/k); mix = d1*(1.0-h) - d2*h; mix + k*h*(1.0-h)
+inline float smooth_subtract(float d1, float d2, float k) {
+    const float sum = d1 + d2;
+    const double hd = 0.5 - ((double)sum * 0.5) / (double)k;
+    const float h = saturatef((float)hd);
+    const double omh = 1.0 - (double)h;
+    const float d2h = d2 * h;
+    const float mix = (float)fma(omh, (double)d1, -(double)d2h);
+    const float kh = k * h;
+    return (float)fma(omh, (double)kh, (double)mix);
+}
+
+inline float length3(f3 v) { return sqrtf(dot3(v, v)); }
+
+// sdfBox :81-89
+inline float sdf_box(f3 p, f3 b, float r) {
+    const f3 q = f3{fabsf(p.x) - b.x, fabsf(p.y) - b.y, fabsf(p.z) - b.z};
+    const f3 m = f3{max_det(q.x, 0.0f), max_det(q.y, 0.0f), max_det(q.z, 0.0f)};
+    const float inner = max_det(q.x, max_det(q.y, q.z));
+    const double in0 = (double)inner < 0.0 ? (double)inner : 0.0;           // min(float, 0.0) is a double min
+    return (float)(((double)length3(m) + in0) - (double)r);
+}
+
+// sdfCylinder :96-101
+inline float sdf_cylinder(f3 p, f3 c) {
+    const float dx = p.x - c.x, dy = p.y - c.z;
+    return sqrtf(fmaf(dx, dx, dy * dy)) - c.y;
+}
+
+// manySphere(p, nSDF, false) :176-196 (the subtraction form)
+inline float many_sphere_subtract(f3 p, float nsdf, int frame) {
+    float s = nsdf;
+    float cx = p.x;
+    float cy = (float)((double)p.y - 0.6);
+    const double zoff = -0.7 + ((double)(frame * 2) * 0.7) / 360.0;
+    const float cz = (float)((double)p.z + zoff);
+    const float zz = cz * cz;
+    for (int i = 0; i < 9; ++i) {
+        if (i % 3 == 0) {
+            cy = (float)((double)cy + 0.4);
+            cx = p.x + 0.5f;
+        }
+        const float len2 = zz + fmaf(cx, cx, cy * cy);
+        const float d = sqrtf(len2) + (-0.1f);
+        s = smooth_subtract(s, d, 0.01f);
+        cx = (float)((double)cx - 0.4);
+    }
+    return s;
+}
+
+// manyCylinderCut :156-174
+inline float many_cylinder_cut(f3 p, float nsdf) {
+    float s = nsdf;
+    const f3 c = f3{0.02f, 0.02f, 0.02f};
+    f3 cp = p;
+    cp.y = (float)((double)cp.y - 0.5);
+    for (int i = 0; i < 300; ++i) {
+        if (i % 20 == 0) {
+            cp.y = (float)((double)cp.y + 0.1);
+            cp.x = (float)((double)p.x + 0.9);
+        }
+        s = smooth_subtract(s, sdf_cylinder(cp, c), 0.01f);
+        cp.x = (float)((double)cp.x - 0.1);
+    }
+    return s;
+}
+
+// One accumulator chain over the library: the run-time form of editing sceneSDF (:217-230).  Layout = nsdf_scene_op.
+struct SceneOp { int prim; int combine; float a[8]; };
+static std::vector<SceneOp> g_program;   // set by oracle_set_scene_program; scene == 2 evaluates it
+
+inline float scene_program_eval(const SceneOp* ops, int n, f3 p, float nsdf, int frame) {
+    float s = 0.0f;
+    for (int i = 0; i < n; ++i) {
+        const SceneOp& op = ops[i];
+        const float* a = op.a;
+        if (op.prim >= 16) {
+            switch (op.prim) {
+                case 16: {   // sdfOpDisplace :103-110 (frequency 5 and amplitude 0.05 there; float parameters here)
+                    const float w = (sinf_det(a[0] * p.x) * sinf_det(a[0] * p.y)) * sinf_det(a[0] * p.z);
+                    s = (float)fma((double)w, (double)a[1], (double)s);
+                    break;
+                }
+                case 17: s = s - a[0]; break;                              // sdfOpRound :112-115
+                case 18: s = fabsf(s) - a[0]; break;                       // sdfOpOnion :117-120
+                case 19: s = (a[0] != 0.0f) ? many_sphere_union(p, s, frame) : many_sphere_subtract(p, s, frame); break;
+                case 20: s = many_cylinder_cut(p, s); break;
+                default: break;
+            }
+            continue;
+        }
+        float d;
+        const f3 q = f3{p.x - a[0], p.y - a[1], p.z - a[2]};
+        switch (op.prim) {
+            case 0: d = nsdf; break;
+            case 1: d = tanhf_det(nsdf); break;                            // :229
+            case 2: d = length3(q) - a[3]; break;                          // sdfSphere :67-71
+            case 3: d = sdf_box(q, f3{a[3], a[4], a[5]}, a[6]); break;
+            case 4: d = p.y - a[0]; break;                                 // sdfPlane :91-94 (0.5 there)
+            case 5: d = sdf_cylinder(q, f3{a[3], a[4], a[5]}); break;
+            default: d = nsdf; break;
+        }
+        switch (op.combine) {
+            case 1: s = min_det(s, d); break;                              // sdfOpUnion :128-131
+            case 2: s = max_det(s, d); break;                              // sdfOpIntersect :123-126
+            case 3: s = max_det(s, -d); break;                             // sdfOpSubtraction :133-136
+            case 4: s = max_det(d, -s); break;
+            case 5: s = smooth_union(s, d, a[7]); break;
+            case 6: s = smooth_subtract(s, d, a[7]); break;
+            case 7: s = smooth_subtract(d, s, a[7]); break;
+            default: s = d; break;
+        }
+    }
+    return s;
+}
+
+enum Scene { SCENE_TANH = 0, SCENE_MANYSPHERE = 1, SCENE_PROGRAM = 2 };
 
 // sceneSDF, src/volumeRender_kernel.cu:217-230.  scene 1 = HEAD (manySphere union);
-// scene 0 = the unreachable-but-intended `tanh(nSDF)` (:229) used for the shipped renders.
+// scene 0 = the unreachable-but-intended `tanh(nSDF)` (:229) used for the shipped renders;
+// scene 2 = the op list last given to oracle_set_scene_program.
 inline float scene_sdf(int scene, f3 p, float nsdf, int frame) {
     if (scene == SCENE_MANYSPHERE) return many_sphere_union(p, nsdf, frame);
+    if (scene == SCENE_PROGRAM) return scene_program_eval(g_program.data(), (int)g_program.size(), p, nsdf, frame);
     return tanhf_det(nsdf);
 }
 
@@ -420,6 +561,21 @@ void oracle_tanhf_array(const float* x, float* y, int64_t n) {
 float oracle_scene_sdf(int scene, float x, float y, float z, float nsdf, int frame) {
     return scene_sdf(scene, f3{x, y, z}, nsdf, frame);
 }
+
+// ops: n records of {int prim, int combine, float a[8]} (include/nsdf.h, nsdf_scene_op).  Not thread-safe against a
+// render in flight; tests set it between calls.
+void oracle_set_scene_program(const void* ops, int n) {
+    g_program.clear();
+    if (ops && n > 0) g_program.assign((const SceneOp*)ops, (const SceneOp*)ops + n);
+}
+
+void oracle_scene_program_eval(const float* xyz, const float* nsdf, int frame, float* out, int64_t n) {
+    for (int64_t i = 0; i < n; ++i)
+        out[i] = scene_program_eval(g_program.data(), (int)g_program.size(), f3{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]},
+                                    nsdf[i], frame);
+}
+
+float oracle_sinf(float x) { return sinf_det(x); }
 
 // NeuralNetwork::forward (src/neuralNetwork.cpp:54-63) on n points.
 // x: [n][in0] (the reference's Matrix(Shape(3, B)) layout, element b*3+c); y: [n][out_last].

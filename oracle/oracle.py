@@ -43,6 +43,10 @@ def lib():
         L.oracle_tanhf_array.argtypes = [fp, fp, C.c_int64]
         L.oracle_scene_sdf.restype = C.c_float
         L.oracle_scene_sdf.argtypes = [C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int]
+        L.oracle_set_scene_program.argtypes = [C.c_void_p, C.c_int]
+        L.oracle_scene_program_eval.argtypes = [fp, fp, C.c_int, fp, C.c_int64]
+        L.oracle_sinf.restype = C.c_float
+        L.oracle_sinf.argtypes = [C.c_float]
         L.oracle_mlp_forward.restype = C.c_int
         L.oracle_mlp_forward.argtypes = [fp, ip, C.c_int, fp, C.c_int64, fp, C.c_int]
         L.oracle_view_matrices.argtypes = [C.c_float] * 5 + [fp, fp]
@@ -120,6 +124,43 @@ def tanhf(x: np.ndarray) -> np.ndarray:
 
 def scene_sdf(scene: int, p, nsdf: float, frame: int = 0) -> float:
     return float(lib().oracle_scene_sdf(scene, float(p[0]), float(p[1]), float(p[2]), float(nsdf), frame))
+
+
+SCENE_PROGRAM = 2
+# op codes of include/nsdf.h (nsdf_scene_op)
+PRIM_NSDF, PRIM_TANH, PRIM_SPHERE, PRIM_BOX, PRIM_PLANE, PRIM_CYLINDER = range(6)
+MOD_DISPLACE, MOD_ROUND, MOD_ONION, MOD_MANY_SPHERE, MOD_MANY_CYLINDER_CUT = range(16, 21)
+(COMB_SET, COMB_UNION, COMB_INTERSECT, COMB_SUBTRACT, COMB_SUBTRACT_FROM, COMB_SMOOTH_UNION, COMB_SMOOTH_SUBTRACT,
+ COMB_SMOOTH_SUBTRACT_FROM) = range(8)
+SCENE_OP_DTYPE = np.dtype([("prim", np.int32), ("combine", np.int32), ("a", np.float32, (8,))])
+
+
+def scene_ops(ops) -> np.ndarray:
+    """[(prim, combine, [a0..]) ...] -> packed nsdf_scene_op records (40 bytes each)."""
+    out = np.zeros(len(ops), dtype=SCENE_OP_DTYPE)
+    for i, (prim, comb, a) in enumerate(ops):
+        out[i]["prim"], out[i]["combine"] = prim, comb
+        out[i]["a"][:len(a)] = np.asarray(a, dtype=np.float32)
+    return out
+
+
+def set_scene_program(ops) -> np.ndarray:
+    """Program evaluated by scene == SCENE_PROGRAM in scene_sdf / render (process-global in the oracle library)."""
+    packed = ops if isinstance(ops, np.ndarray) else scene_ops(ops)
+    lib().oracle_set_scene_program(packed.ctypes.data, len(packed))
+    return packed
+
+
+def scene_program_eval(xyz: np.ndarray, nsdf: np.ndarray, frame: int = 0) -> np.ndarray:
+    xyz = np.ascontiguousarray(xyz, dtype=np.float32)
+    nsdf = np.ascontiguousarray(nsdf, dtype=np.float32)
+    out = np.empty(nsdf.size, dtype=np.float32)
+    lib().oracle_scene_program_eval(_fp(xyz), _fp(nsdf), frame, _fp(out), nsdf.size)
+    return out
+
+
+def sinf(x: float) -> float:
+    return float(lib().oracle_sinf(float(x)))
 
 
 def view_matrices(rx: float = 0.0, ry: float = 0.0, translation=(0.0, 0.0, -2.0)) -> Tuple[np.ndarray, np.ndarray]:

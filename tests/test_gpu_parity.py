@@ -318,6 +318,83 @@ def test_animation_net_frames_bit_exact(env, tmp_path):
     assert np.array_equal(_bits(y), _bits(oracle.mlp_forward(om, x).ravel()))
 
 
+def _scene_programs(O):
+    """Scene programs covering every primitive, modifier and combiner, among them the scenes sceneSDF holds commented out
+    (src/volumeRender_kernel.cu:217-230)."""
+    return {
+        "round(tanh, 0.04) :220": [(O.PRIM_TANH, O.COMB_SET, []), (O.MOD_ROUND, 0, [0.04])],
+        "displacementPattern :218": [(O.PRIM_TANH, O.COMB_SET, []), (O.MOD_DISPLACE, 0, [5.0, 0.05])],
+        "sphere 0.9 :219": [(O.PRIM_SPHERE, O.COMB_SET, [0, 0, 0, 0.9])],
+        "cylinder smooth-cut out of tanh :224-227": [(O.PRIM_TANH, O.COMB_SET, []),
+                                                      (O.PRIM_CYLINDER, O.COMB_SMOOTH_SUBTRACT_FROM, [-0.5, -0.2, 0.4, 0.1, 0.1, 0.1, 0, 0.05])],
+        "manySphere subtract": [(O.PRIM_NSDF, O.COMB_SET, []), (O.MOD_MANY_SPHERE, 0, [0.0])],
+        "manyCylinderCut :222": [(O.PRIM_NSDF, O.COMB_SET, []), (O.MOD_MANY_CYLINDER_CUT, 0, [])],
+        "box / plane / onion / hard booleans": [(O.PRIM_TANH, O.COMB_SET, []), (O.MOD_ONION, 0, [0.02]),
+                                                 (O.PRIM_BOX, O.COMB_INTERSECT, [0.0, 0.1, 0.0, 0.6, 0.5, 0.7, 0.03]),
+                                                 (O.PRIM_SPHERE, O.COMB_SUBTRACT, [0.3, 0.2, 0.4, 0.25]),
+                                                 (O.PRIM_PLANE, O.COMB_UNION, [0.5]),
+                                                 (O.PRIM_SPHERE, O.COMB_SUBTRACT_FROM, [0, 0, 0, 1.1]),
+                                                 (O.PRIM_SPHERE, O.COMB_SMOOTH_UNION, [-0.4, 0.3, 0.2, 0.2, 0, 0, 0, 0.05]),
+                                                 (O.PRIM_CYLINDER, O.COMB_SMOOTH_SUBTRACT, [0.1, 0.1, 0, 0.0, 0.08, 0.0, 0, 0.03])],
+    }
+
+
+def test_scene_program_points_bit_exact(env):
+    """nsdf_scene_eval (the analytic SDF library of src/volumeRender_kernel.cu:67-196 composed at run time) against the
+    oracle's restatement on random points and network outputs: same bits for every program."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    rng = np.random.default_rng(5)
+    n = 100000
+    p = rng.uniform(-1.3, 1.3, (n, 3)).astype(np.float32)
+    ns = np.concatenate([rng.uniform(-0.5, 0.8, n - 6), [0.0, -0.0, 1e-7, -1e-7, 30.0, -30.0]]).astype(np.float32)
+    dp, dn = torch.from_numpy(p).cuda(), torch.from_numpy(ns).cuda()
+    try:
+        for name, ops in _scene_programs(oracle).items():
+            for frame in (0, 45):
+                oracle.set_scene_program(ops)
+                want = oracle.scene_program_eval(p, ns, frame)
+                got = host.scene_eval(ops, dp, dn, frame).cpu().numpy()
+                assert np.array_equal(_bits(got), _bits(want)), (name, frame, int((_bits(got) != _bits(want)).sum()))
+    finally:
+        oracle.set_scene_program([])
+    bad = host.capi.scene_ops([(99, 0, [])])
+    with pytest.raises(Exception):
+        host.scene_eval(bad, dp, dn, 0)
+
+
+def test_scene_program_frames_bit_exact(env):
+    """Frames of program scenes equal the oracle's bytes (hit mask, RGBA, query count) for the default and the ray-per-lane
+    schedules; the two compiled scenes rendered as programs equal their compiled frames."""
+    torch, host, oracle, capi = env["torch"], env["host"], env["oracle"], env["capi"]
+    nn, om = _load(env, "car_1")
+    matcap = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    iv, nm = oracle.view_matrices(10.0, 25.0)
+    W, H = 96, 72
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.copyViewMatrices(iv, nm, 30, 3)
+    try:
+        for name, ops in _scene_programs(oracle).items():
+            heavy = "manyCylinderCut" in name
+            oracle.set_scene_program(ops)
+            ref = oracle.render(om, iv, nm, W, H, matcap=matcap, scene=oracle.SCENE_PROGRAM, frame=30,
+                                max_steps=300 if heavy else 6000)
+            for flags in ((0,) if heavy else (0, capi.RENDER_NO_STRAGGLER, capi.RENDER_HYBRID)):
+                host.setSceneProgram(ops, max_steps=300 if heavy else 6000, flags=flags)
+                img, stats = host.render_host(nn, W, H, matcap)
+                assert np.array_equal(img, ref["image"]), (name, flags)
+                assert stats["queries"] == ref["queries"], (name, flags)
+        for scene, ops in ((host.SCENE_TANH, [(oracle.PRIM_TANH, oracle.COMB_SET, [])]),
+                           (host.SCENE_MANYSPHERE, [(oracle.PRIM_NSDF, oracle.COMB_SET, []), (oracle.MOD_MANY_SPHERE, 0, [1.0])])):
+            host.setSceneOptions(scene)
+            a, sa = host.render_host(nn, W, H, matcap)
+            host.setSceneProgram(ops)
+            b, sb = host.render_host(nn, W, H, matcap)
+            assert np.array_equal(a, b) and sa["queries"] == sb["queries"]
+    finally:
+        host.setSceneOptions()
+        oracle.set_scene_program([])
+
+
 def test_tile_priority_order_is_invisible(env):
     """tile_priority.cuh: probing and re-ordering the tiles (forced on for this small frame, also for a 3-rank tile
     partition and the two-pass / mixed schedules) must not change a byte of an exact frame or a query of its count."""

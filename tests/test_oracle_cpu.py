@@ -215,6 +215,76 @@ def test_oracle_animation_net_frame0_equals_static_net(built, tmp_path):
         assert act[0] == y[i]
 
 
+def test_oracle_sinf_accuracy(built):
+    """sinf_det (the deterministic sin both sides use for sdfOpDisplace, src/volumeRender_kernel.cu:103-110)."""
+    xs = np.concatenate([np.linspace(-20, 20, 20001), np.linspace(-1000, 1000, 2001)]).astype(np.float32)
+    got = np.array([oracle.sinf(float(x)) for x in xs], dtype=np.float64)
+    assert np.max(np.abs(got - np.sin(xs.astype(np.float64)))) < 3e-7
+    assert np.isnan(oracle.sinf(float("inf"))) and np.isnan(oracle.sinf(float("nan"))) and oracle.sinf(0.0) == 0.0
+
+
+def test_oracle_scene_library_matches_float64_formulas(built):
+    """The analytic SDF library (src/volumeRender_kernel.cu:67-174) as scene programs against float64 numpy restatements of
+    the same formulas: primitives, hard and smooth booleans, modifiers, and the two composite scenes."""
+    rng = np.random.default_rng(3)
+    n = 4000
+    p = rng.uniform(-1.2, 1.2, (n, 3)).astype(np.float32)
+    ns = rng.uniform(-0.3, 0.6, n).astype(np.float32)
+    P, N = p.astype(np.float64), ns.astype(np.float64)
+    sat = lambda x: np.clip(x, 0.0, 1.0)
+    def ssub(d1, d2, k):
+        h = sat(0.5 - 0.5 * (d1 + d2) / k); return d1 * (1 - h) - d2 * h + k * h * (1 - h)
+    def suni(d1, d2, k):
+        h = sat(0.5 + 0.5 * (d2 - d1) / k); return d2 * (1 - h) + d1 * h - k * h * (1 - h)
+    def box(q, b, r):
+        d = np.abs(q) - b; return np.linalg.norm(np.maximum(d, 0), axis=1) + np.minimum(d.max(axis=1), 0) - r
+    def cyl(q, c):
+        return np.hypot(q[:, 0] - c[0], q[:, 1] - c[2]) - c[1]
+    O = oracle
+    cases = []
+    c0 = np.array([0.2, -0.1, 0.3])
+    cases.append(([(O.PRIM_SPHERE, O.COMB_SET, [0.2, -0.1, 0.3, 0.9])], np.linalg.norm(P - c0, axis=1) - 0.9))
+    cases.append(([(O.PRIM_BOX, O.COMB_SET, [0.2, -0.1, 0.3, 0.4, 0.3, 0.2, 0.05])], box(P - c0, np.array([0.4, 0.3, 0.2]), 0.05)))
+    cases.append(([(O.PRIM_PLANE, O.COMB_SET, [0.5])], P[:, 1] - 0.5))
+    cases.append(([(O.PRIM_CYLINDER, O.COMB_SET, [-0.5, -0.2, 0.4, 0.1, 0.1, 0.1])],
+                  cyl(P - np.array([-0.5, -0.2, 0.4]), [0.1, 0.1, 0.1])))
+    cases.append(([(O.PRIM_TANH, O.COMB_SET, []), (O.MOD_ROUND, 0, [0.04])], np.tanh(N) - 0.04))
+    cases.append(([(O.PRIM_TANH, O.COMB_SET, []), (O.MOD_ONION, 0, [0.02])], np.abs(np.tanh(N)) - 0.02))
+    cases.append(([(O.PRIM_TANH, O.COMB_SET, []), (O.MOD_DISPLACE, 0, [5.0, 0.05])],
+                  np.tanh(N) + np.sin(5 * P[:, 0]) * np.sin(5 * P[:, 1]) * np.sin(5 * P[:, 2]) * np.float64(np.float32(0.05))))
+    sph = np.linalg.norm(P, axis=1) - 0.5
+    for comb, f in ((O.COMB_UNION, lambda s, d: np.minimum(s, d)), (O.COMB_INTERSECT, lambda s, d: np.maximum(s, d)),
+                    (O.COMB_SUBTRACT, lambda s, d: np.maximum(s, -d)), (O.COMB_SUBTRACT_FROM, lambda s, d: np.maximum(d, -s)),
+                    (O.COMB_SMOOTH_UNION, lambda s, d: suni(s, d, 0.05)), (O.COMB_SMOOTH_SUBTRACT, lambda s, d: ssub(s, d, 0.05)),
+                    (O.COMB_SMOOTH_SUBTRACT_FROM, lambda s, d: ssub(d, s, 0.05))):
+        k = np.float64(np.float32(0.05))
+        cases.append(([(O.PRIM_TANH, O.COMB_SET, []), (O.PRIM_SPHERE, comb, [0, 0, 0, 0.5, 0, 0, 0, 0.05])], f(np.tanh(N), sph)))
+    # manyCylinderCut :156-174 in float64
+    s = N.copy(); cp = P.copy(); cp[:, 1] -= 0.5
+    for i in range(300):
+        if i % 20 == 0:
+            cp[:, 1] += 0.1; cp[:, 0] = P[:, 0] + 0.9
+        s = ssub(s, cyl(cp, [0.02, 0.02, 0.02]), 0.01); cp[:, 0] -= 0.1
+    cases.append(([(O.PRIM_NSDF, O.COMB_SET, []), (O.MOD_MANY_CYLINDER_CUT, 0, [])], s))
+    # manySphere(p, nSDF, false) :176-196, frame 90
+    s = N.copy(); cp = P.copy(); cp[:, 1] -= 0.6; cp[:, 2] += -0.7 + 90 * 2 * 0.7 / 360
+    for i in range(9):
+        if i % 3 == 0:
+            cp[:, 1] += 0.4; cp[:, 0] = P[:, 0] + 0.5
+        s = ssub(s, np.linalg.norm(cp, axis=1) - 0.1, 0.01); cp[:, 0] -= 0.4
+    cases.append(([(O.PRIM_NSDF, O.COMB_SET, []), (O.MOD_MANY_SPHERE, 0, [0.0])], s))
+    for ops, want in cases:
+        oracle.set_scene_program(ops)
+        got = oracle.scene_program_eval(p, ns, frame=90).astype(np.float64)
+        assert np.max(np.abs(got - want)) < 2e-5, (ops, np.max(np.abs(got - want)))
+    # the two compiled scenes are programs too
+    oracle.set_scene_program([(O.PRIM_NSDF, O.COMB_SET, []), (O.MOD_MANY_SPHERE, 0, [1.0])])
+    a = oracle.scene_program_eval(p[:200], ns[:200], frame=7)
+    b = np.array([oracle.scene_sdf(1, p[i], ns[i], 7) for i in range(200)], dtype=np.float32)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    oracle.set_scene_program([])
+
+
 def test_h5_writer_rejects_bad_arguments(built, tmp_path):
     L = _capi().lib()
     dims = (C.c_int * 2)(3, 0)
