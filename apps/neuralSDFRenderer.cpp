@@ -5,7 +5,7 @@
 // (the reference's --single path, generateSingleImage :404-468); --spin renders 360 frames with
 // viewRotation.y = i and frameNumber = i (doABarrelRoll :470-478).  Output: <prefix><basename>.png with the
 // reference's 180-degree turn (Image::savePNG), and the same frame as PPM with --ppm.
-// Extra flags: --ppm, --scene tanh|manysphere, --max-steps N, --precision N (NSDF_PREC_*), --views N
+// Extra flags: --ppm, --scene tanh|manysphere|round|displace|sphere|cylindercut|spherecut (scene programs), --max-steps N, --precision N (NSDF_PREC_*), --views N
 // (turntable of N views instead of 360), --gpu K (device ordinal), --stats.
 #include <chrono>
 #include <cmath>
@@ -35,7 +35,7 @@ static void usage() {
                  "\t--single one frame (default here: there is no interactive mode)\n"
                  "\t--spin 360 frames (or --views N) rotating about y\n"
                  "\t--animation 4-input (xyzt) networks\n"
-                 "\t--ppm also write <name>.ppm   --scene tanh|manysphere   --max-steps N   --precision N\n"
+                 "\t--ppm also write <name>.ppm   --scene tanh|manysphere|round|displace|sphere|cylindercut|spherecut   --max-steps N   --precision N\n"
                  "\t--gpu K   --stats   -h (--help)\n";
 }
 static int countDigit(int n) {
@@ -65,6 +65,23 @@ int main(int argc, char** argv) {
     const int maxSteps = getCmdOption(argv, end, "--max-steps") ? atoi(getCmdOption(argv, end, "--max-steps")) : 6000;
     const char* sceneName = getCmdOption(argv, end, "--scene");
     const int scene = (sceneName && std::strcmp(sceneName, "manysphere") == 0) ? NSDF_SCENE_MANYSPHERE : NSDF_SCENE_TANH;
+    // the scenes sceneSDF (src/volumeRender_kernel.cu:217-230) holds commented out, as scene programs
+    nsdf_scene_op prog[2] = {};
+    int progOps = 0;
+    if (sceneName && std::strcmp(sceneName, "round") == 0) {                 // sdfOpRound(tanh(nSDF), 0.04)
+        prog[0].prim = NSDF_PRIM_TANH; prog[1].prim = NSDF_MOD_ROUND; prog[1].a[0] = 0.04f; progOps = 2;
+    } else if (sceneName && std::strcmp(sceneName, "displace") == 0) {       // displacementPattern(p, nSDF)
+        prog[0].prim = NSDF_PRIM_TANH; prog[1].prim = NSDF_MOD_DISPLACE; prog[1].a[0] = 5.0f; prog[1].a[1] = 0.05f; progOps = 2;
+    } else if (sceneName && std::strcmp(sceneName, "sphere") == 0) {         // sdfSphere(p, 0.9)
+        prog[0].prim = NSDF_PRIM_SPHERE; prog[0].a[3] = 0.9f; progOps = 1;
+    } else if (sceneName && std::strcmp(sceneName, "cylindercut") == 0) {    // manyCylinderCut(p, nSDF)
+        prog[0].prim = NSDF_PRIM_NSDF; prog[1].prim = NSDF_MOD_MANY_CYLINDER_CUT; progOps = 2;
+    } else if (sceneName && std::strcmp(sceneName, "spherecut") == 0) {      // manySphere(p, nSDF, false)
+        prog[0].prim = NSDF_PRIM_NSDF; prog[1].prim = NSDF_MOD_MANY_SPHERE; prog[1].a[0] = 0.0f; progOps = 2;
+    } else if (sceneName && std::strcmp(sceneName, "tanh") != 0 && std::strcmp(sceneName, "manysphere") != 0) {
+        std::cerr << "unknown --scene " << sceneName << "\n";
+        return 1;
+    }
     if (getCmdOption(argv, end, "--gpu")) nsdfCheck(nsdf_set_device(atoi(getCmdOption(argv, end, "--gpu"))));
     if (width <= 0 || height <= 0) { std::cerr << "bad image size\n"; return 1; }
 
@@ -86,6 +103,7 @@ int main(int argc, char** argv) {
     }
     copyStaticSettings(colorType, numInputs);
     setRenderOptions(scene, maxSteps, 0);
+    if (progOps) setSceneProgram(prog, progOps);
 
     uint* d_output = nullptr;
     nsdfCheck(nsdf_dev_malloc(reinterpret_cast<void**>(&d_output), (size_t)width * height * sizeof(uint)));

@@ -59,6 +59,19 @@ extern "C" void setRenderOptions(int scene, int maxSteps, int flags) {
     g.opts.flags = flags;
 }
 
+extern "C" void setSceneProgram(const nsdf_scene_op* ops, int nOps) {
+    ensure_init();
+    static nsdf_scene_op program[NSDF_SCENE_MAX_OPS];
+    if (!ops || nOps < 1 || nOps > NSDF_SCENE_MAX_OPS) {
+        std::fprintf(stderr, "setSceneProgram: 1..%d ops expected\n", NSDF_SCENE_MAX_OPS);
+        std::exit(EXIT_FAILURE);
+    }
+    std::memcpy(program, ops, sizeof(nsdf_scene_op) * (size_t)nOps);
+    g.opts.scene = NSDF_SCENE_PROGRAM;
+    g.opts.program = program;
+    g.opts.n_ops = nOps;
+}
+
 extern "C" void getLastRenderStats(nsdf_render_stats* out) {
     ensure_init();
     *out = g.last;

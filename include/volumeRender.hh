@@ -6,7 +6,7 @@
 //                      (the reference's by-value declaration destroys the caller's layers).
 //   copyViewMatrices   c_invViewMatrix (3x4) and c_normalMatrix (4x4) + frame number, as cudaMemcpyToSymbol did.
 //   copyStaticSettings c_coloringType / c_numInputs.
-// Extensions: setRenderOptions (scene function, MAX_STEPS, NSDF_RENDER_* flags), getLastRenderStats,
+// Extensions: setRenderOptions (scene function, MAX_STEPS, NSDF_RENDER_* flags), setSceneProgram, getLastRenderStats,
 // updateViewMatrices (src/main.cpp:207-222 without Eigen).
 #pragma once
 #include <cstddef>
@@ -32,5 +32,7 @@ extern "C" void copyViewMatrices(float* invViewMatrix, size_t sizeofInvModelView
 extern "C" void copyStaticSettings(int colorType, int numInputs);
 
 extern "C" void setRenderOptions(int scene, int maxSteps, int flags);
+// sceneSDF (volumeRender_kernel.cu:217-230) as data: the op list is copied; selects NSDF_SCENE_PROGRAM (include/nsdf.h)
+extern "C" void setSceneProgram(const nsdf_scene_op* ops, int nOps);
 extern "C" void getLastRenderStats(nsdf_render_stats* out);
 extern "C" void updateViewMatrices(float rxDeg, float ryDeg, float tx, float ty, float tz, int frameNumber);

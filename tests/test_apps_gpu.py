@@ -51,3 +51,31 @@ def test_renderer_app_single_frame(gpu, tmp_path, matcap):
     ppm = open(prefix + "car_1.h5.ppm", "rb").read()
     head = f"P6\n{W}\n{H}\n255\n".encode()
     assert ppm.startswith(head) and ppm[len(head):] == rgba[:, :, :3].tobytes()
+
+
+def test_renderer_app_scene_program(gpu, tmp_path):
+    """--scene displace: sceneSDF's commented `displacementPattern` (src/volumeRender_kernel.cu:218) selected at run time
+    through the C++ mirror's setSceneProgram; query count and frame equal the oracle's."""
+    from PIL import Image
+    from oracle import oracle
+    W, H = 96, 64
+    prefix = str(tmp_path) + "/"
+    cmd = [os.path.join(ROOT, "apps", "neuralSDFRenderer"), "-i", model_path("plane_1"), "-o", prefix, "-W", str(W), "-H", str(H),
+           "-ry", "15", "--single", "--stats", "--scene", "displace", "-M", os.path.join(MATCAPS, "blue.png")]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    om = oracle.Model.from_h5(model_path("plane_1"))
+    iv, nm = oracle.view_matrices(0.0, 15.0)
+    mc = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    oracle.set_scene_program([(oracle.PRIM_TANH, oracle.COMB_SET, []), (oracle.MOD_DISPLACE, 0, [5.0, 0.05])])
+    try:
+        ref = oracle.render(om, iv, nm, W, H, matcap=mc, scene=oracle.SCENE_PROGRAM)
+    finally:
+        oracle.set_scene_program([])
+    assert int(re.search(r"(\d+) MLP queries", out.stdout).group(1)) == ref["queries"]
+    img = ref["image"].reshape(H, W)
+    rgba = np.stack([img & 255, (img >> 8) & 255, (img >> 16) & 255, (img >> 24) & 255], -1).astype(np.uint8)
+    png = np.asarray(Image.open(prefix + "plane_1.h5.png").convert("RGBA"))
+    assert np.array_equal(png, rgba[::-1, ::-1, :])
+    bad = subprocess.run(cmd[:-4] + ["--scene", "nonsense"], capture_output=True, text=True)
+    assert bad.returncode != 0
