@@ -182,6 +182,113 @@ __device__ __forceinline__ void mlp32_eval_thread(const float* __restrict__ sw, 
     }
 }
 
+// ---- thread-per-4-points evaluator, activations in shared memory -------------------------------------
+// Measured on a B200 (profiles/r01_smem_delivery_notes.md): shared memory delivers ~128 B/clk/SM into registers
+// (a warp-uniform LDS.128 costs two wavefronts, a quarter-warp-replicated one four), so an evaluator is bound by that
+// pipe unless every loaded weight feeds >= 4 FFMAs of its lane.  mlp32_eval_thread<2> sits at 8 FFMA per LDS.128
+// (pipe-balanced, 53 % of the FMA peak); this form keeps the 4 x 32 accumulators of FOUR points in registers and
+// the points' activations in a thread-private shared-memory column (act[k * stride + thread] = float4 of the four
+// points' a[k]): per k one LDS.128 of activations and eight warp-uniform LDS.128 of weights feed 128 FFMAs.
+// P = 2 is the same idea inside a 128-register budget (64 accumulators): 8 FFMA per weight load like
+// mlp32_eval_thread<2>, at half its registers.  Same chains, same bits.
+template <int P> struct ActVec;
+template <> struct ActVec<2> {
+    typedef float2 type;
+    static __device__ __forceinline__ float2 make(const float (&z)[2]) { return make_float2(z[0], z[1]); }
+    static __device__ __forceinline__ void get(const float2& v, float (&a)[2]) { a[0] = v.x; a[1] = v.y; }
+};
+template <> struct ActVec<4> {
+    typedef float4 type;
+    static __device__ __forceinline__ float4 make(const float (&z)[4]) { return make_float4(z[0], z[1], z[2], z[3]); }
+    static __device__ __forceinline__ void get(const float4& v, float (&a)[4]) { a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w; }
+};
+// act: this thread's column (element k at act[k * stride]); P = 2 or 4 points per thread.
+template <int P>
+__device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw, int n_sq,
+                                                    typename ActVec<P>::type* __restrict__ act, int stride,
+                                                    const float (&x)[P][3], float (&y)[P], float t4 = 0.0f,
+                                                    bool in4 = false) {
+    float z[32][P];
+    {
+        const float4* L0 = reinterpret_cast<const float4*>(sw);
+#pragma unroll
+        for (int oc = 0; oc < 8; ++oc) {
+            const float4 w0 = L0[oc], w1 = L0[8 + oc], w2 = L0[16 + oc], bb = L0[32 + oc];
+            float4 w3 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (in4) w3 = L0[24 + oc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                float c0 = fmaf(w2.x, x[p][2], fmaf(w1.x, x[p][1], fmaf(w0.x, x[p][0], 0.0f)));
+                float c1 = fmaf(w2.y, x[p][2], fmaf(w1.y, x[p][1], fmaf(w0.y, x[p][0], 0.0f)));
+                float c2 = fmaf(w2.z, x[p][2], fmaf(w1.z, x[p][1], fmaf(w0.z, x[p][0], 0.0f)));
+                float c3 = fmaf(w2.w, x[p][2], fmaf(w1.w, x[p][1], fmaf(w0.w, x[p][0], 0.0f)));
+                if (in4) { c0 = fmaf(w3.x, t4, c0); c1 = fmaf(w3.y, t4, c1); c2 = fmaf(w3.z, t4, c2); c3 = fmaf(w3.w, t4, c3); }
+                z[4 * oc + 0][p] = relu_det(c0 + bb.x);
+                z[4 * oc + 1][p] = relu_det(c1 + bb.y);
+                z[4 * oc + 2][p] = relu_det(c2 + bb.z);
+                z[4 * oc + 3][p] = relu_det(c3 + bb.w);
+            }
+        }
+    }
+#pragma unroll 1
+    for (int l = 0; l < n_sq; ++l) {
+#pragma unroll
+        for (int o = 0; o < 32; ++o) {
+            act[o * stride] = ActVec<P>::make(z[o]);
+#pragma unroll
+            for (int p = 0; p < P; ++p) z[o][p] = 0.0f;
+        }
+        const float4* Wt = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS);
+#pragma unroll 4
+        for (int k = 0; k < 32; ++k) {
+            float av[P];
+            ActVec<P>::get(act[k * stride], av);
+#pragma unroll
+            for (int oc = 0; oc < 8; ++oc) {
+                const float4 w = Wt[k * 8 + oc];
+#pragma unroll
+                for (int p = 0; p < P; ++p) {
+                    z[4 * oc + 0][p] = fmaf(w.x, av[p], z[4 * oc + 0][p]);
+                    z[4 * oc + 1][p] = fmaf(w.y, av[p], z[4 * oc + 1][p]);
+                    z[4 * oc + 2][p] = fmaf(w.z, av[p], z[4 * oc + 2][p]);
+                    z[4 * oc + 3][p] = fmaf(w.w, av[p], z[4 * oc + 3][p]);
+                }
+            }
+        }
+#pragma unroll
+        for (int oc = 0; oc < 8; ++oc) {
+            const float4 bb = Wt[256 + oc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                z[4 * oc + 0][p] = relu_det(z[4 * oc + 0][p] + bb.x);
+                z[4 * oc + 1][p] = relu_det(z[4 * oc + 1][p] + bb.y);
+                z[4 * oc + 2][p] = relu_det(z[4 * oc + 2][p] + bb.z);
+                z[4 * oc + 3][p] = relu_det(z[4 * oc + 3][p] + bb.w);
+            }
+        }
+    }
+    {
+        const float4* LL = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS);
+        float acc[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) acc[p] = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const float4 w = LL[kc];
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                acc[p] = fmaf(w.x, z[4 * kc + 0][p], acc[p]);
+                acc[p] = fmaf(w.y, z[4 * kc + 1][p], acc[p]);
+                acc[p] = fmaf(w.z, z[4 * kc + 2][p], acc[p]);
+                acc[p] = fmaf(w.w, z[4 * kc + 3][p], acc[p]);
+            }
+        }
+        const float bl = sw[FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS + 32];
+#pragma unroll
+        for (int p = 0; p < P; ++p) y[p] = acc[p] + bl;
+    }
+}
+
 // ---- warp-cooperative evaluator ------------------------------------------------------------------
 // One warp evaluates R points; lane = neuron.  x must be warp-uniform.  abuf: per-warp scratch of
 // 2*R*WARP_ACT_STRIDE floats in shared memory.  y is returned warp-uniform.  Same bits as above.

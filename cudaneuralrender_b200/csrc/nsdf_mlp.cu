@@ -37,6 +37,37 @@ mlp_fp32_thread_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int 
     }
 }
 
+// Thread-per-4-points fused MLP (mlp32_eval_thread4s): accumulators in registers, activations in a thread-private
+// shared-memory column behind the weights.  One CTA per SM.
+template <int P, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+mlp_fp32_thread_s_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_sq, const float* __restrict__ xin,
+                        float* __restrict__ yout, long long n, const LatticeParams lp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, blob, blob_bytes, &s_bar);
+    typename ActVec<P>::type* act = reinterpret_cast<typename ActVec<P>::type*>(s_w + (blob_bytes >> 2)) + threadIdx.x;
+    const long long chunk = (long long)THREADS * P;
+    for (long long base = (long long)blockIdx.x * chunk; base < n; base += (long long)gridDim.x * chunk) {
+        float x[P][3], y[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const long long i = base + (long long)p * THREADS + threadIdx.x;
+            x[p][0] = x[p][1] = x[p][2] = 0.0f;
+            if (i < n) {
+                if (lp.enabled) lattice_point(lp, lp.first + i, x[p]);
+                else { x[p][0] = __ldg(xin + 3 * i); x[p][1] = __ldg(xin + 3 * i + 1); x[p][2] = __ldg(xin + 3 * i + 2); }
+            }
+        }
+        mlp32_eval_thread_s<P>(s_w, n_sq, act, THREADS, x, y);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const long long i = base + (long long)p * THREADS + threadIdx.x;
+            if (i < n) yout[i] = y[p];
+        }
+    }
+}
+
 // Warp-cooperative fused MLP on a dense batch (exercises the latency evaluator of the tracer).
 template <int R>
 __global__ void __launch_bounds__(1024, 1)
@@ -116,10 +147,40 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
         if (R == 1) return go(mlp_fp32_warp_kernel<1>, 1);
         return go(mlp_fp32_warp_kernel<4>, 4);
     }
-    const int P = env_int("NSDF_FP32_P", 2);
+    // measured on 16.8 M points (tools/fp32_p4_probe.py): P = 2 2.72 Gq/s, P = 4 with 128/256/384 threads 2.90/3.34/3.46 Gq/s
+    const int P = env_int("NSDF_FP32_P", 4);
     const size_t smem = m->blob_bytes;
     NSDF_PER_DEVICE_FLAG(attr1);
     NSDF_PER_DEVICE_FLAG(attr2);
+    if (P == 4) {
+        // 384 threads x 512 B of activations + the weights must fit the 227 KB a CTA may own (deep nets: 256 threads)
+        const int threads = env_int("NSDF_FP32_P4_THREADS", m->blob_bytes + 384u * 512u <= 227u * 1024u ? 384 : 256);
+        auto go4 = [&](auto kern, int th, int pp = 4, int minb = 1) -> int {
+            const size_t smem4 = m->blob_bytes + (size_t)th * 32 * pp * sizeof(float);
+            cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
+            if (e2 != cudaSuccess) return (int)e2;
+            const long long chunk = (long long)th * pp;
+            long long want = (n + chunk - 1) / chunk;
+            const int grid = (int)(want < (long long)sms * minb ? want : (long long)sms * minb);
+            kern<<<grid, th, smem4, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+            return (int)cudaGetLastError();
+        };
+        if (threads == 384) return go4(mlp_fp32_thread_s_kernel<4, 384, 1>, 384);
+        if (threads == 128) return go4(mlp_fp32_thread_s_kernel<4, 128, 1>, 128);
+        return go4(mlp_fp32_thread_s_kernel<4, 256, 1>, 256);
+    }
+    if (P == 22) {   // development: two points per thread, activations in shared memory, the tracer's register budget
+        auto go2 = [&](auto kern) -> int {
+            const size_t smem2 = m->blob_bytes + (size_t)256 * 32 * 2 * sizeof(float);
+            cudaError_t e2 = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+            if (e2 != cudaSuccess) return (int)e2;
+            long long want = (n + 511) / 512;
+            const int grid = (int)(want < 2LL * sms ? want : 2LL * sms);
+            kern<<<grid, 256, smem2, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+            return (int)cudaGetLastError();
+        };
+        return go2(mlp_fp32_thread_s_kernel<2, 256, 2>);
+    }
     if (P == 1) {
         if (!attr1) {
             e = cudaFuncSetAttribute(mlp_fp32_thread_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);

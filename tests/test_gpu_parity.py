@@ -72,6 +72,25 @@ def test_fp32_mlp_bit_exact(env, n):
         assert np.array_equal(_bits(nn.forward_host(x)), _bits(ref))
 
 
+def test_fp32_thread_evaluator_variants_bit_exact(env, monkeypatch):
+    """Every thread-per-point schedule of the fp32 rung (1, 2 points per thread in registers; 4 points per thread with the
+    activations in shared memory at 128/256/384 threads) returns the oracle's bits, on ragged sizes too."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "plane_1")
+    for n in (1, 1535, 1536, 1537, 300001):
+        x = np.random.default_rng(n).uniform(-1, 1, (n, 3)).astype(np.float32)
+        ref = oracle.mlp_forward(om, x).ravel()
+        xd = torch.from_numpy(x).cuda().contiguous()
+        for p, th in (("1", None), ("2", None), ("22", None), ("4", "128"), ("4", "256"), ("4", "384"), (None, None)):
+            for k, v in (("NSDF_FP32_P", p), ("NSDF_FP32_P4_THREADS", th)):
+                if v is None:
+                    monkeypatch.delenv(k, raising=False)
+                else:
+                    monkeypatch.setenv(k, v)
+            y = nn.forward_tensor(xd, host.PREC_FP32).cpu().numpy()
+            assert np.array_equal(_bits(y), _bits(ref)), (n, p, th)
+
+
 def test_fp32_all_models_and_special_values(env):
     torch, host, oracle = env["torch"], env["host"], env["oracle"]
     rng = np.random.default_rng(5)
