@@ -361,4 +361,104 @@ __device__ __forceinline__ void mlp32_eval_warp(const float* __restrict__ sw, in
     __syncwarp();   // abuf may be rewritten by the caller's next evaluation
 }
 
+// ---- warp-cooperative evaluator, 16 points, register-tiled ------------------------------------------
+// One warp evaluates 16 points; lane = (g = lane & 7, rg = lane >> 3) owns the 4 x 4 tile
+// {neurons 4g..4g+3} x {points rg, rg+4, rg+8, rg+12}.  A hidden layer is still a 32-deep FFMA chain per output
+// (the latency of mlp32_eval_warp), but every LDS.128 now feeds 16 FFMA instead of 4: per warp and layer
+// 32 weight + 32 activation wavefronts + 16 store wavefronts against 512 FFMA instructions, so the FMA pipe and
+// not the shared-memory pipe bounds it (mlp32_eval_warp<8>: 104 wavefronts per 256 FFMA, LSU 94 % busy in ncu).
+// Bank layout: weights Wt[k][4g..4g+3] are 8 consecutive float4 (one wavefront); activations live point-major with
+// the WARP_ACT_STRIDE = 36 row stride, so the four points rg (+4j) of one load start 4 banks apart (one wavefront),
+// and the float4 stores of a quarter warp (g = 0..7) cover all 32 banks.
+// xin: abuf + 16*WARP_ACT_STRIDE (the second activation buffer) holds the 16 points as float4 {x, y, z, -} written
+// by the caller before the call (a __syncwarp() is issued here).  Returns point (lane & 15)'s value in every lane
+// of that residue.  Same bits as the evaluators above (ascending-k fmaf chain from 0, + bias, relu).
+__device__ __forceinline__ float mlp32_eval_warp16(const float* __restrict__ sw, int n_sq, float* __restrict__ abuf,
+                                                   int lane, float t4 = 0.0f, bool in4 = false) {
+    float* cur = abuf;
+    float* nxt = abuf + 16 * WARP_ACT_STRIDE;
+    const int g = lane & 7, rg = lane >> 3;
+    __syncwarp();
+    {
+        const float4* S4 = reinterpret_cast<const float4*>(sw);
+        const float4 w0 = S4[g], w1 = S4[8 + g], w2 = S4[16 + g], w3 = S4[24 + g], bb = S4[32 + g];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int r = rg + 4 * j;
+            const float4 x = *reinterpret_cast<const float4*>(nxt + 4 * r);
+            float4 z;
+            z.x = fmaf(w2.x, x.z, fmaf(w1.x, x.y, fmaf(w0.x, x.x, 0.0f)));
+            z.y = fmaf(w2.y, x.z, fmaf(w1.y, x.y, fmaf(w0.y, x.x, 0.0f)));
+            z.z = fmaf(w2.z, x.z, fmaf(w1.z, x.y, fmaf(w0.z, x.x, 0.0f)));
+            z.w = fmaf(w2.w, x.z, fmaf(w1.w, x.y, fmaf(w0.w, x.x, 0.0f)));
+            if (in4) {
+                z.x = fmaf(w3.x, t4, z.x); z.y = fmaf(w3.y, t4, z.y);
+                z.z = fmaf(w3.z, t4, z.z); z.w = fmaf(w3.w, t4, z.w);
+            }
+            z.x = relu_det(z.x + bb.x); z.y = relu_det(z.y + bb.y);
+            z.z = relu_det(z.z + bb.z); z.w = relu_det(z.w + bb.w);
+            *reinterpret_cast<float4*>(cur + r * WARP_ACT_STRIDE + 4 * g) = z;
+        }
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int l = 0; l < n_sq; ++l) {
+        const float4* Wt = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS) + g;
+        const float* arow = cur + rg * WARP_ACT_STRIDE;
+        float z[4][4];   // [neuron i][point j]
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) z[i][j] = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            float a[4][4];   // [point j][k within the chunk]
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 av = *reinterpret_cast<const float4*>(arow + 4 * j * WARP_ACT_STRIDE + 4 * kc);
+                a[j][0] = av.x; a[j][1] = av.y; a[j][2] = av.z; a[j][3] = av.w;
+            }
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const float4 w = Wt[(4 * kc + kk) * 8];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    z[0][j] = fmaf(w.x, a[j][kk], z[0][j]);
+                    z[1][j] = fmaf(w.y, a[j][kk], z[1][j]);
+                    z[2][j] = fmaf(w.z, a[j][kk], z[2][j]);
+                    z[3][j] = fmaf(w.w, a[j][kk], z[3][j]);
+                }
+            }
+        }
+        const float4 bb = Wt[256];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float4 o;
+            o.x = relu_det(z[0][j] + bb.x); o.y = relu_det(z[1][j] + bb.y);
+            o.z = relu_det(z[2][j] + bb.z); o.w = relu_det(z[3][j] + bb.w);
+            *reinterpret_cast<float4*>(nxt + (rg + 4 * j) * WARP_ACT_STRIDE + 4 * g) = o;
+        }
+        __syncwarp();
+        float* t = cur; cur = nxt; nxt = t;
+    }
+    float out;
+    {
+        const float* LL = sw + FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS;
+        const float* arow = cur + (lane & 15) * WARP_ACT_STRIDE;
+        float acc = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const float4 w = *reinterpret_cast<const float4*>(LL + 4 * kc);
+            const float4 av = *reinterpret_cast<const float4*>(arow + 4 * kc);
+            acc = fmaf(w.x, av.x, acc);
+            acc = fmaf(w.y, av.y, acc);
+            acc = fmaf(w.z, av.z, acc);
+            acc = fmaf(w.w, av.w, acc);
+        }
+        out = acc + LL[32];
+    }
+    __syncwarp();   // abuf may be rewritten by the caller's next evaluation
+    return out;
+}
+
 }  // namespace nsdf

@@ -24,6 +24,7 @@ struct nsdf_model {
     // src/volumeRender_kernel.cu:578-585); one render at a time per model handle
     unsigned int* d_counters = nullptr;   // [0] pixel counter [1] queue tail [2] queue head [3] pad
     void* d_queue = nullptr;
+    void* d_xqueue = nullptr;             // express queue of the cooperative tracer (fixed capacity, trace_coop.cuh)
     size_t queue_capacity = 0;
     unsigned int frame_seq = 0;           // publication stamp of the fused tracer's queue entries
     nsdf_render_stats* d_stats_scratch = nullptr;

@@ -97,6 +97,32 @@ mlp_fp32_warp_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_
     }
 }
 
+// The 16-point register-tiled form of the same evaluator (mlp32_eval_warp16): what the tracer's warps run while
+// more than 8 of their 16 ray slots are busy.
+__global__ void __launch_bounds__(256, 2)
+mlp_fp32_warp16_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_sq, const float* __restrict__ xin,
+                       float* __restrict__ yout, long long n, const LatticeParams lp) {
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, blob, blob_bytes, &s_bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    float* abuf = s_w + (blob_bytes >> 2) + warp * (2 * 16 * WARP_ACT_STRIDE);
+    const long long gw = (long long)blockIdx.x * wpb + warp, nw = (long long)gridDim.x * wpb;
+    for (long long base = gw * 16; base < n; base += nw * 16) {
+        const long long i = base + lane;
+        if (lane < 16) {
+            float x[3] = {0.0f, 0.0f, 0.0f};
+            if (i < n) {
+                if (lp.enabled) lattice_point(lp, lp.first + i, x);
+                else { x[0] = __ldg(xin + 3 * i); x[1] = __ldg(xin + 3 * i + 1); x[2] = __ldg(xin + 3 * i + 2); }
+            }
+            *reinterpret_cast<float4*>(abuf + 16 * WARP_ACT_STRIDE + 4 * lane) = make_float4(x[0], x[1], x[2], 0.0f);
+        }
+        const float y = mlp32_eval_warp16(s_w, n_sq, abuf, lane);
+        if (lane < 16 && i < n) yout[i] = y;
+    }
+}
+
 // Generic dense layer (any M, K; N = 1 per batch): replaces denseLayerForward /
 // batchedDenseLayerForward (src/layers/denseLayer.cu:86-176) with the same arithmetic.
 __global__ void __launch_bounds__(256)
@@ -142,6 +168,15 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
             kern<<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         };
+        if (R == 16) {
+            const size_t smem = m->blob_bytes + 8 * 2 * 16 * WARP_ACT_STRIDE * sizeof(float);
+            cudaError_t e2 = cudaFuncSetAttribute(mlp_fp32_warp16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e2 != cudaSuccess) return (int)e2;
+            long long want = (n + 127) / 128;
+            const int grid = (int)(want < 2LL * sms ? want : 2LL * sms);
+            mlp_fp32_warp16_kernel<<<grid, 256, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+            return (int)cudaGetLastError();
+        }
         if (R == 8) return go(mlp_fp32_warp_kernel<8>, 8);
         if (R == 2) return go(mlp_fp32_warp_kernel<2>, 2);
         if (R == 1) return go(mlp_fp32_warp_kernel<1>, 1);

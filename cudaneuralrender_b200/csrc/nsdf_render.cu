@@ -35,10 +35,17 @@ static size_t coop_smem(const nsdf_model* m) {
     return m->blob_bytes + (COOP_THREADS / 32) * 2 * COOP_R * WARP_ACT_STRIDE * sizeof(float);
 }
 
+// express queue of the cooperative tracer: pushes stop at half of it; the other half is room for every warp's last push
+constexpr size_t XQUEUE_ENTRIES = 1u << 17;
+
 static int ensure_scratch(nsdf_model* m, size_t queue_entries) {
     cudaError_t e;
     if (!m->d_counters) {
-        e = cudaMalloc(&m->d_counters, 4 * sizeof(unsigned int));
+        e = cudaMalloc(&m->d_counters, 8 * sizeof(unsigned int));
+        if (e != cudaSuccess) return (int)e;
+        e = cudaMalloc(&m->d_xqueue, XQUEUE_ENTRIES * sizeof(StragglerEntry));
+        if (e != cudaSuccess) return (int)e;
+        e = cudaMemset(m->d_xqueue, 0, XQUEUE_ENTRIES * sizeof(StragglerEntry));
         if (e != cudaSuccess) return (int)e;
     }
     if (queue_entries > m->queue_capacity) {
@@ -57,6 +64,8 @@ static int ensure_scratch(nsdf_model* m, size_t queue_entries) {
 void render_release(nsdf_model* m) {
     if (m->d_counters) cudaFree(m->d_counters);
     if (m->d_queue) cudaFree(m->d_queue);
+    if (m->d_xqueue) cudaFree(m->d_xqueue);
+    m->d_xqueue = nullptr;
     if (m->d_stats_scratch) cudaFree(m->d_stats_scratch);
     if (m->d_tile_scratch) cudaFree(m->d_tile_scratch);
     m->d_tile_scratch = nullptr;
@@ -144,6 +153,15 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.total_idx = (unsigned int)my_tiles * TILE_PIXELS;
     rp.max_steps = opts->max_steps;
     rp.isolate_steps = env_int("NSDF_COOP_ISOLATE", 0);
+    rp.marathon_steps = env_int("NSDF_COOP_MARATHON", 0);
+    rp.timeline = env_int("NSDF_COOP_TIMELINE", 0);
+    rp.xqueue = nullptr;
+    rp.xqueue_soft_cap = 0u;
+    rp.express_steps = 0;
+    rp.express_period = 0u;
+    rp.express_lanes = 0u;
+    rp.consumer_warps = env_int("NSDF_COOP_CONSUMER_WARPS", 0);
+    rp.pop_max = env_int("NSDF_COOP_POP_MAX", 0);
     rp.n_in = m->in[0];
     rp.t4 = (float)cam->frame;
     rp.tile_order = nullptr;
@@ -189,7 +207,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     const bool only_throughput = straggler && (opts->flags & NSDF_RENDER_PHASE_THROUGHPUT) != 0;
     cudaError_t e = cudaSuccess;
     if (!only_latency) {
-        e = cudaMemsetAsync(m->d_counters, 0, 4 * sizeof(unsigned int), stream);
+        e = cudaMemsetAsync(m->d_counters, 0, 8 * sizeof(unsigned int), stream);
         if (e != cudaSuccess) return (int)e;
     }
 
@@ -313,6 +331,13 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         rp.frame_seq = m->frame_seq;
         rp.consumer_period = (unsigned int)env_int("NSDF_COOP_QUIET_PERIOD", 16);
         rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_COOP_EVICT", 256);
+        rp.express_period = (unsigned int)env_int("NSDF_COOP_EXPRESS_PERIOD", 0);
+        rp.express_steps = env_int("NSDF_COOP_EXPRESS_STEPS", 512);
+        if (coop_queue && rp.express_period > 0 && rp.express_steps > 0) {
+            rp.xqueue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);
+            rp.xqueue_soft_cap = (unsigned int)(XQUEUE_ENTRIES / 2);
+            rp.express_lanes = ((unsigned int)sms / rp.express_period) * (unsigned int)occ * 4u;
+        }
         if (hybrid && coop_queue) {
             rp.hybrid = env_int("NSDF_COOP_HYBRID", 8);   // a dry producer warp with <= this many rays hands them all over
             if (rp.hybrid < 1) rp.hybrid = 1;
@@ -384,3 +409,17 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
 }
 
 }  // namespace nsdf
+
+// Development hook (not part of include/nsdf.h): copies the tracer's timeline log to the host and clears it.
+extern "C" int nsdf_dev_timeline_read(unsigned long long* out, int n_words) {
+    const size_t total = sizeof(unsigned long long) * (4 + 4 * nsdf::TIMELINE_EVENTS);
+    size_t bytes = sizeof(unsigned long long) * (size_t)n_words;
+    if (bytes > total) bytes = total;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(out, nsdf::g_timeline, bytes);
+    if (e == cudaSuccess) {
+        static unsigned long long zeros[4] = {0, 0, 0, 0};
+        e = cudaMemcpyToSymbol(nsdf::g_timeline, zeros, sizeof(zeros));
+    }
+    return (int)e;
+}

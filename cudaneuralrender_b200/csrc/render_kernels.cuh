@@ -63,6 +63,15 @@ struct RenderParams {
     unsigned int queue_capacity;
     int isolate_steps;             // trace_coop_kernel: a warp holding a ray that has marched this many steps stops taking new
                                    // rays, so the long ray soon runs alone at the 1-ray latency (0 = off)
+    int marathon_steps;            // trace_coop_kernel: a consumer warp holding a ray with this many steps stops popping (0 = off)
+    int consumer_warps;            // trace_coop_kernel: the last this-many warps of every CTA consume from the start
+    int pop_max;                   // trace_coop_kernel: a consumer warp holds at most this many popped rays (0 = all slots)
+    StragglerEntry* xqueue;        // trace_coop_kernel: express queue (counters pixel_counter[4] tail, [5] head, [6] express rays in flight)
+    unsigned int xqueue_soft_cap;  //   nothing is pushed beyond this index (the allocation has room for every warp's last push behind it)
+    int express_steps;             //   a consumer's ray with this many steps moves to an express lane when one is free (0 = off)
+    unsigned int express_period;   //   the warps 0..3 of every CTA on SMs with smid % express_period == express_period - 1 are express
+    unsigned int express_lanes;    //   lanes: they hold ONE ray each, so that it marches at the 1-ray latency on a quiet scheduler
+    int timeline;                  // development: record the timeline of long rays (trace_coop.cuh g_timeline)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
                                    // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed
     SceneProgram prog;             // scene == NSDF_SCENE_PROGRAM: the op list (scene_program.cuh)

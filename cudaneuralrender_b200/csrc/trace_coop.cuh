@@ -23,12 +23,29 @@
 
 namespace nsdf {
 
+// Development timeline (NSDF_COOP_TIMELINE=1): [0] kernel start, [1] last warp out of pixels, [2] kernel end (globaltimer ns),
+// [3] number of events, then events {time, pix, steps, kind}: kind 100 = pushed, 101 = popped, else rays in the warp.
+constexpr int TIMELINE_EVENTS = 32768;
+__device__ unsigned long long g_timeline[4 + 4 * TIMELINE_EVENTS];
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void timeline_event(int pix, int steps, int kind) {
+    const unsigned long long i = atomicAdd(&g_timeline[3], 1ull);
+    if (i < TIMELINE_EVENTS) {
+        g_timeline[4 + 4 * i] = global_ns(); g_timeline[5 + 4 * i] = (unsigned long long)pix;
+        g_timeline[6 + 4 * i] = (unsigned long long)steps; g_timeline[7 + 4 * i] = (unsigned long long)kind;
+    }
+}
+
 constexpr int COOP_THREADS = 256;
-constexpr int COOP_R = 8;   // ray slots per warp (lanes 0..COOP_R-1 own them)
+constexpr int COOP_R = 16;  // ray slots per warp (lanes 0..COOP_R-1 own them)
 
 // Evaluates the K lowest-ranked active rays of the warp.  src[j] = lane of the j-th active ray.
 template <int K>
-__device__ __forceinline__ float coop_eval(const float* s_w, int n_sq, float* abuf, const f3& q, const int (&src)[COOP_R],
+__device__ __forceinline__ float coop_eval(const float* s_w, int n_sq, float* abuf, const f3& q, const int (&src)[8],
                                            int rank, int lane, float t4, bool in4) {
     float x[K][3], y[K];
 #pragma unroll
@@ -105,6 +122,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (rp.timeline && blockIdx.x == 0 && threadIdx.x == 0) g_timeline[0] = global_ns();
     float* abuf = s_w + (rp.blob_bytes >> 2) + warp * (2 * COOP_R * WARP_ACT_STRIDE);
     const unsigned int total_warps = gridDim.x * (COOP_THREADS / 32);
     const bool from_queue = rp.queue_static != 0;
@@ -120,7 +138,17 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     slot.mode = -1;
     LocalStats st = {0, 0, 0, 0, 0, 0};
     // warp-uniform role state
-    bool producing = !(use_queue && rp.consumer_period && (sm_id() % rp.consumer_period) == rp.consumer_period - 1);
+    // consumers from the start: every warp of the quiet SMs, and the last rp.consumer_warps warps of every CTA ("fast lanes":
+    // a warp that marches one or two long rays is latency-bound and takes few issue slots from the 16-ray warps beside it)
+    // express SMs (trace timeline: a lone ray steps in 1.14 us on an SM where nothing else runs, in 3.5 us beside the crowded
+    // warps of a quiet SM, in 5.5 us beside 16-ray warps): warps 0..3 of their CTAs hold ONE ray each, taken from the express queue
+    const bool express_sm = use_queue && rp.xqueue && rp.express_period && (sm_id() % rp.express_period) == rp.express_period - 1;
+    const bool express_lane = express_sm && warp < 4;
+    bool producing = !(use_queue && (express_sm || (rp.consumer_period && (sm_id() % rp.consumer_period) == rp.consumer_period - 1) ||
+                                     warp >= COOP_THREADS / 32 - rp.consumer_warps));
+    bool bulk_over = false, xbusy = false;   // warp-uniform
+    unsigned int* const pc = rp.pixel_counter;
+    const int pop_max = rp.pop_max > 0 && rp.pop_max < COOP_R ? rp.pop_max : COOP_R;
     bool exhausted = !producing;
     if (use_queue && !producing && lane == 0) atomicAdd(rp.pixel_counter + 3, 1u);
     int poll = 0;
@@ -198,7 +226,10 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
                     }
                 }
             }
-            if (base + cnt >= n_src) exhausted = true;
+            if (base + cnt >= n_src) {
+                exhausted = true;
+                if (rp.timeline && lane == 0) atomicMax(&g_timeline[1], global_ns());
+            }
         }
         unsigned int act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
         if (use_queue && exhausted) {
@@ -206,21 +237,73 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
                 producing = false;
                 if (lane == 0) { __threadfence(); atomicAdd(rp.pixel_counter + 3, 1u); }
             }
-            if (!producing && (!act || --poll <= 0)) {
-                fused_pop(slot, lane < COOP_R && slot.mode < 0, rp);
+            // a consumer warp that holds a marathon ray (>= rp.marathon_steps steps) takes no more rays: its other rays
+            // finish within a few hundred steps and the marathon ray then marches alone at the 1-ray latency instead of
+            // sharing every step with up to 15 newcomers for as long as the queue has a backlog
+            const bool marathon = rp.marathon_steps > 0 &&
+                __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.marathon_steps) != 0u;
+            if (!producing && !marathon && (!act || --poll <= 0)) {
                 poll = 8;
+                if (express_sm) {
+                    if (xbusy && !act) {                       // the express ray of this lane is done
+                        if (lane == 0) atomicSub(pc + 6, 1u);
+                        xbusy = false;
+                    }
+                    if (express_lane && !act) {
+                        const bool popped = queue_pop(slot, lane == 0, rp.xqueue, pc + 4, pc + 5, rp);
+                        if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 103);
+                        if (__ballot_sync(0xffffffffu, popped)) {
+                            xbusy = true;
+                            if (lane == 0) atomicAdd(pc + 6, 1u);
+                        }
+                    }
+                    // once every warp is out of pixels an express SM consumes like any other
+                    if (bulk_over && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
+                        fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
+                } else {
+                    if (rp.xqueue && rp.express_steps > 0 && !bulk_over) {
+                        // rays that have come this far move to an express lane, if one is free
+                        const bool go = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_steps;
+                        const unsigned int gm = __ballot_sync(0xffffffffu, go);
+                        if (gm) {
+                            unsigned int ok = 0, over = 0;
+                            if (lane == 0) {
+                                const unsigned int tail2 = ld_volatile_u32(pc + 4), head2 = ld_volatile_u32(pc + 5);
+                                const unsigned int infl = ld_volatile_u32(pc + 6);
+                                over = ld_volatile_u32(pc + 3) >= total_warps ? 1u : 0u;
+                                ok = (!over && (tail2 - head2) + infl + __popc(gm) <= rp.express_lanes &&
+                                      tail2 + 32u <= rp.xqueue_soft_cap) ? 1u : 0u;
+                            }
+                            ok = __shfl_sync(0xffffffffu, ok, 0);
+                            bulk_over = __shfl_sync(0xffffffffu, over, 0) != 0u;
+                            if (ok) {
+                                if (rp.timeline && go) timeline_event(slot.pix, slot.steps, 102);
+                                queue_push(slot, go, rp.xqueue, pc + 4, rp, st);
+                            }
+                        }
+                    }
+                    const bool popped = fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
+                    if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 101);
+                    // leftovers of the express queue once its lanes may have gone
+                    if (rp.xqueue && bulk_over && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
+                        queue_pop(slot, lane == 0, rp.xqueue, pc + 4, pc + 5, rp);
+                }
                 act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
             }
             if (!act) {
-                unsigned int done = 0;
+                unsigned int done = 0, over = 0;
                 if (lane == 0) {
-                    const unsigned int fin = ld_volatile_u32(rp.pixel_counter + 3);
-                    const unsigned int tail = ld_volatile_u32(rp.pixel_counter + 1);
-                    const unsigned int head = ld_volatile_u32(rp.pixel_counter + 2);
-                    done = (fin >= total_warps && head >= tail) ? 1u : 0u;
+                    const unsigned int fin = ld_volatile_u32(pc + 3);
+                    const unsigned int tail = ld_volatile_u32(pc + 1);
+                    const unsigned int head = ld_volatile_u32(pc + 2);
+                    over = fin >= total_warps ? 1u : 0u;
+                    done = (over && head >= tail) ? 1u : 0u;
+                    if (done && rp.xqueue) done = ld_volatile_u32(pc + 5) >= ld_volatile_u32(pc + 4) ? 1u : 0u;
                 }
+                bulk_over = __shfl_sync(0xffffffffu, over, 0) != 0u;
                 if (__shfl_sync(0xffffffffu, done, 0)) break;
-                __nanosleep(200);
+                if (bulk_over) poll = 0;                   // look at the queues again right away
+                __nanosleep(express_sm && !express_lane && !bulk_over ? 2000 : 200);
                 if (++idle > 50000000u) __trap();     // > 10 s without work: never hang the device
                 continue;
             }
@@ -232,32 +315,47 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             const int owner = __ffs(act) - 1;
             if (__shfl_sync(0xffffffffu, slot.mode, owner) == 0) {
                 lone_ray_march(slot, owner, s_w, rp.n_sq, abuf, rp, st, lane, use_queue ? 64 : (1 << 30));
+                if (rp.timeline && lane == owner && (slot.steps & 255) < 64 && slot.steps >= 256) timeline_event(slot.pix, slot.steps, 1);
                 continue;
             }
         }
         const bool active = lane < COOP_R && slot.mode >= 0;
         const int na = __popc(act);
         const int rank = __popc(act & lanemask_lt());
-        int src[COOP_R];
-        {
+        const f3 q = active ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
+        float mine;
+        if (na > 8) {
+            // 9..16 busy slots: the register-tiled 16-point evaluator.  Owners write their query point at their rank,
+            // unused ranks are zeroed (their results are computed and dropped).
+            float4* xin = reinterpret_cast<float4*>(abuf + 16 * WARP_ACT_STRIDE);
+            if (active) xin[rank] = make_float4(q.x, q.y, q.z, 0.0f);
+            else if (lane < 16 && lane >= na) xin[lane] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            const float out = mlp32_eval_warp16(s_w, rp.n_sq, abuf, lane, rp.t4, rp.n_in == 4);
+            mine = __shfl_sync(0xffffffffu, out, rank & 15);
+        } else {
+            int src[8];
             unsigned int mm = act;
 #pragma unroll
-            for (int j = 0; j < COOP_R; ++j) {
+            for (int j = 0; j < 8; ++j) {
                 src[j] = mm ? (__ffs(mm) - 1) : 0;
                 mm &= mm - 1u;
             }
+            if (na > 4) mine = coop_eval<8>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
+            else if (na > 2) mine = coop_eval<4>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
+            else if (na == 2) mine = coop_eval<2>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
+            else mine = coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
         }
-        const f3 q = active ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
-        float mine;
-        if (na > 4) mine = coop_eval<8>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
-        else if (na > 2) mine = coop_eval<4>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
-        else if (na == 2) mine = coop_eval<2>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
-        else mine = coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
         if (active) slot_update(slot, mine, q, rp, st);
+        if (rp.timeline && active && slot.mode == 0 && slot.steps >= 256 && (slot.steps & 255) == 0) timeline_event(slot.pix, slot.steps, na);
         // ---- long rays leave for the quiet SMs
         if (use_queue && producing)
-            fused_push(slot, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.evict_steps_hi, rp, st);
+        {
+            const bool leave = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.evict_steps_hi;
+            if (rp.timeline && leave) timeline_event(slot.pix, slot.steps, 100);
+            fused_push(slot, leave, rp, st);
+        }
     }
+    if (rp.timeline && lane == 0) atomicMax(&g_timeline[2], global_ns());
     flush_stats(st, rp.stats);
 }
 

@@ -37,41 +37,46 @@ __device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int* p) {
 }
 
 // Producer side: append marching rays to the queue (warp-aggregated) and publish them.
-__device__ __forceinline__ void fused_push(RaySlot& s, bool do_evict, const RenderParams& rp, LocalStats& st) {
+__device__ __forceinline__ void queue_push(RaySlot& s, bool do_evict, StragglerEntry* queue, unsigned int* tail_counter,
+                                           const RenderParams& rp, LocalStats& st) {
     const unsigned int m = __ballot_sync(0xffffffffu, do_evict);
     if (!m) return;
     const int leader = __ffs(m) - 1;
     unsigned int base = 0;
-    if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(rp.pixel_counter + 1, (unsigned int)__popc(m));
+    if ((int)(threadIdx.x & 31) == leader) base = atomicAdd(tail_counter, (unsigned int)__popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
     if (do_evict) {
         const unsigned int slot = base + __popc(m & lanemask_lt());
-        // capacity == number of pixels of this call: every ray is pushed at most once
-        float4* dst = reinterpret_cast<float4*>(rp.queue + slot);
+        // main queue: capacity == number of pixels of this call, every ray is pushed at most once
+        float4* dst = reinterpret_cast<float4*>(queue + slot);
         dst[0] = make_float4(__int_as_float(s.pix), __int_as_float(s.steps), s.p.x, s.p.y);
         dst[1] = make_float4(s.p.z, s.d.x, s.d.y, s.d.z);
         reinterpret_cast<float2*>(dst + 2)[0] = make_float2(s.tfar, 0.0f);
         __threadfence();
-        asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(&rp.queue[slot].ready), "r"(rp.frame_seq) : "memory");
-        ++st.evicted;
+        asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(&queue[slot].ready), "r"(rp.frame_seq) : "memory");
+        if (queue == rp.queue) ++st.evicted;
         s.mode = -1;
     }
 }
+__device__ __forceinline__ void fused_push(RaySlot& s, bool do_evict, const RenderParams& rp, LocalStats& st) {
+    queue_push(s, do_evict, rp.queue, rp.pixel_counter + 1, rp, st);
+}
 
 // Consumer side: lanes with want == true try to pop one entry each.  Returns true in the lanes that got one.
-__device__ __forceinline__ bool fused_pop(RaySlot& s, bool want, const RenderParams& rp) {
+__device__ __forceinline__ bool queue_pop(RaySlot& s, bool want, const StragglerEntry* queue, unsigned int* tail_counter,
+                                          unsigned int* head_counter, const RenderParams& rp) {
     const unsigned int m = __ballot_sync(0xffffffffu, want);
     if (!m) return false;
     const int leader = __ffs(m) - 1;
     unsigned int base = 0, got = 0;
     if ((int)(threadIdx.x & 31) == leader) {
         const unsigned int cnt = __popc(m);
-        unsigned int head = ld_volatile_u32(rp.pixel_counter + 2);
+        unsigned int head = ld_volatile_u32(head_counter);
         for (;;) {
-            const unsigned int tail = ld_volatile_u32(rp.pixel_counter + 1);
+            const unsigned int tail = ld_volatile_u32(tail_counter);
             if (head >= tail) { got = 0; break; }
             const unsigned int take = (tail - head) < cnt ? (tail - head) : cnt;
-            const unsigned int old = atomicCAS(rp.pixel_counter + 2, head, head + take);
+            const unsigned int old = atomicCAS(head_counter, head, head + take);
             if (old == head) { base = head; got = take; break; }
             head = old;
         }
@@ -81,7 +86,7 @@ __device__ __forceinline__ bool fused_pop(RaySlot& s, bool want, const RenderPar
     const unsigned int rank = __popc(m & lanemask_lt());
     const bool mine = want && rank < got;
     if (mine) {
-        const StragglerEntry* e = rp.queue + base + rank;
+        const StragglerEntry* e = queue + base + rank;
         unsigned int spins = 0;
         while (ld_volatile_u32(&e->ready) != rp.frame_seq) {
             __nanosleep(20);
@@ -96,6 +101,9 @@ __device__ __forceinline__ bool fused_pop(RaySlot& s, bool want, const RenderPar
         s.tfar = tf; s.mode = 0;
     }
     return mine;
+}
+__device__ __forceinline__ bool fused_pop(RaySlot& s, bool want, const RenderParams& rp) {
+    return queue_pop(s, want, rp.queue, rp.pixel_counter + 1, rp.pixel_counter + 2, rp);
 }
 
 __global__ void __launch_bounds__(FUSED_THREADS, 2) trace_fused_kernel(const __grid_constant__ RenderParams rp) {

@@ -91,6 +91,23 @@ def test_fp32_thread_evaluator_variants_bit_exact(env, monkeypatch):
             assert np.array_equal(_bits(y), _bits(ref)), (n, p, th)
 
 
+def test_fp32_warp_evaluator_widths_bit_exact(env, monkeypatch):
+    """The tracer's warp-cooperative evaluators on dense batches: 1/2/4/8 points per warp (lane = neuron) and the
+    register-tiled 16-point form (mlp32_eval_warp16) return the oracle's bits, on ragged sizes and on every model."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    for name in MODELS:
+        nn, om = _load(env, name)
+        for n in (1, 15, 16, 17, 4095, 100003):
+            x = np.random.default_rng(n).uniform(-1, 1, (n, 3)).astype(np.float32)
+            ref = oracle.mlp_forward(om, x).ravel()
+            xd = torch.from_numpy(x).cuda().contiguous()
+            for r in ("16", "8", "4", "2", "1"):
+                monkeypatch.setenv("NSDF_FP32_WARP_R", r)
+                y = nn.forward_tensor(xd, host.PREC_FP32_WARP).cpu().numpy()
+                assert np.array_equal(_bits(y), _bits(ref)), (name, n, r)
+    monkeypatch.delenv("NSDF_FP32_WARP_R", raising=False)
+
+
 def test_fp32_all_models_and_special_values(env):
     torch, host, oracle = env["torch"], env["host"], env["oracle"]
     rng = np.random.default_rng(5)
