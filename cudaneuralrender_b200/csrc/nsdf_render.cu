@@ -160,6 +160,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.express_steps = 0;
     rp.express_period = 0u;
     rp.express_lanes = 0u;
+    rp.express_from_bulk = 0;
     rp.consumer_warps = env_int("NSDF_COOP_CONSUMER_WARPS", 0);
     rp.pop_max = env_int("NSDF_COOP_POP_MAX", 0);
     rp.n_in = m->in[0];
@@ -170,10 +171,10 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     const bool farfield = (opts->flags & NSDF_RENDER_TC_FARFIELD) != 0;
     // two-pass schedule: asked for, or chosen for large calls when the caller expressed no schedule preference
     // large calls (the bulk dominates, not the longest ray): ray-per-lane producers.  NSDF_LARGE_SCHEDULE: 1 = hybrid single
-    // launch (default), 2 = two-pass, 0 = the cooperative default at every size
+    // launch, 2 = two-pass, 0 = the cooperative tracer at every size (default since its 16-ray tiled evaluator: 4K 49.5 -> 41.3 ms)
     const bool large = !farfield && opts->flags == 0 && opts->evict_steps == 0 &&
                        rp.total_idx >= (unsigned int)env_int("NSDF_TWO_PASS_MIN_PIXELS", 3000000);
-    const int large_schedule = large ? env_int("NSDF_LARGE_SCHEDULE", 1) : 0;
+    const int large_schedule = large ? env_int("NSDF_LARGE_SCHEDULE", 0) : 0;
     const bool two_pass = !farfield && ((opts->flags & NSDF_RENDER_TWO_PASS) != 0 || large_schedule == 2);
     const bool hybrid = !farfield && !two_pass && ((opts->flags & NSDF_RENDER_HYBRID) != 0 || large_schedule == 1 ||
                                                    env_int("NSDF_COOP_HYBRID", 0) != 0);
@@ -324,15 +325,25 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
         if (e != cudaSuccess) return (int)e;
         if (occ < 1) return NSDF_EUNSUPPORTED;
+        { const int occ_max = env_int("NSDF_COOP_OCC", 0); if (occ_max > 0 && occ > occ_max) occ = occ_max; }
         const unsigned int per_cta = (COOP_THREADS / 32) * COOP_R;
         const unsigned int cap = (unsigned int)(sms * occ);
         const unsigned int want = (rp.total_idx + per_cta - 1) / per_cta;
         m->frame_seq = m->frame_seq + 1u ? m->frame_seq + 1u : 1u;
         rp.frame_seq = m->frame_seq;
-        rp.consumer_period = (unsigned int)env_int("NSDF_COOP_QUIET_PERIOD", 16);
-        rp.evict_steps_hi = opts->evict_steps > 0 ? opts->evict_steps : env_int("NSDF_COOP_EVICT", 256);
-        rp.express_period = (unsigned int)env_int("NSDF_COOP_EXPRESS_PERIOD", 0);
-        rp.express_steps = env_int("NSDF_COOP_EXPRESS_STEPS", 512);
+        // Serial tail.  Measured with the timeline hook (tools/timeline_probe.py): a ray inside a 16-ray warp steps
+        // every ~13 us, a lone ray beside crowded warps every 3.5-5.5 us, a lone ray on an SM whose schedulers run nothing but lone
+        // rays every 1.15-1.6 us.  So every express_period-th SM is an express SM (4 warps per CTA hold ONE ray each) and any warp
+        // hands a ray that has marched express_steps steps to a free express lane; rays that find no lane stay where they are.
+        // That replaces the quiet SMs + unconditional hand-over at 256 steps (kept for callers that set evict_steps).
+        // Only for full grids: a grid smaller than the machine could land on express SMs alone and trace nothing.
+        const bool full_grid = want >= cap;
+        const bool caller_evicts = opts->evict_steps > 0;
+        rp.consumer_period = full_grid ? (unsigned int)env_int("NSDF_COOP_QUIET_PERIOD", caller_evicts ? 16 : 0) : 0u;
+        rp.evict_steps_hi = caller_evicts ? opts->evict_steps : env_int("NSDF_COOP_EVICT", 1 << 30);
+        rp.express_period = full_grid && !caller_evicts && !(hybrid && coop_queue) ? (unsigned int)env_int("NSDF_COOP_EXPRESS_PERIOD", rp.total_idx >= 3000000u ? 24 : 12) : 0u;   // large calls are bound by the bulk
+        rp.express_steps = env_int("NSDF_COOP_EXPRESS_STEPS", 160);
+        rp.express_from_bulk = env_int("NSDF_COOP_EXPRESS_FROM_BULK", 1);
         if (coop_queue && rp.express_period > 0 && rp.express_steps > 0) {
             rp.xqueue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);
             rp.xqueue_soft_cap = (unsigned int)(XQUEUE_ENTRIES / 2);

@@ -71,6 +71,7 @@ struct RenderParams {
     int express_steps;             //   a consumer's ray with this many steps moves to an express lane when one is free (0 = off)
     unsigned int express_period;   //   the warps 0..3 of every CTA on SMs with smid % express_period == express_period - 1 are express
     unsigned int express_lanes;    //   lanes: they hold ONE ray each, so that it marches at the 1-ray latency on a quiet scheduler
+    int express_from_bulk;         //   producing warps hand rays over to free express lanes too (else only the consumers do)
     int timeline;                  // development: record the timeline of long rays (trace_coop.cuh g_timeline)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source
                                    // (second pass of the mixed-precision tracer): slots refill from it, nothing is pushed

@@ -232,6 +232,30 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             }
         }
         unsigned int act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
+        if (rp.xqueue && rp.express_steps > 0 && (!producing || rp.express_from_bulk) && !express_sm && !bulk_over) {
+            // rays that have come this far move to an express lane, if one is free
+            // (looked at when a ray's step count is a multiple of 16: the counters live in L2; a lone ray comes back every 64 steps)
+            const bool go = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_steps && (slot.steps & 15) == 0;
+            const unsigned int gm = __ballot_sync(0xffffffffu, go);
+            if (gm) {
+                unsigned int ok = 0, over = 0;
+                if (lane == 0) {
+                    const unsigned int tail2 = ld_volatile_u32(pc + 4), head2 = ld_volatile_u32(pc + 5);
+                    const unsigned int infl = ld_volatile_u32(pc + 6);
+                    over = ld_volatile_u32(pc + 3) >= total_warps ? 1u : 0u;
+                    ok = (!over && (tail2 - head2) + infl + __popc(gm) <= rp.express_lanes &&
+                          tail2 + 32u <= rp.xqueue_soft_cap) ? 1u : 0u;
+                }
+                ok = __shfl_sync(0xffffffffu, ok, 0);
+                bulk_over = __shfl_sync(0xffffffffu, over, 0) != 0u;
+                if (ok) {
+                    if (rp.timeline && go) timeline_event(slot.pix, slot.steps, 102);
+                    queue_push(slot, go, rp.xqueue, pc + 4, rp, st);
+                    if (!exhausted) continue;      // a producing warp refills the slots it has just emptied
+                    act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
+                }
+            }
+        }
         if (use_queue && exhausted) {
             if (producing && !act) {          // out of pixels and rays: from now on a consumer
                 producing = false;
@@ -261,27 +285,6 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
                     if (bulk_over && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
                         fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
                 } else {
-                    if (rp.xqueue && rp.express_steps > 0 && !bulk_over) {
-                        // rays that have come this far move to an express lane, if one is free
-                        const bool go = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_steps;
-                        const unsigned int gm = __ballot_sync(0xffffffffu, go);
-                        if (gm) {
-                            unsigned int ok = 0, over = 0;
-                            if (lane == 0) {
-                                const unsigned int tail2 = ld_volatile_u32(pc + 4), head2 = ld_volatile_u32(pc + 5);
-                                const unsigned int infl = ld_volatile_u32(pc + 6);
-                                over = ld_volatile_u32(pc + 3) >= total_warps ? 1u : 0u;
-                                ok = (!over && (tail2 - head2) + infl + __popc(gm) <= rp.express_lanes &&
-                                      tail2 + 32u <= rp.xqueue_soft_cap) ? 1u : 0u;
-                            }
-                            ok = __shfl_sync(0xffffffffu, ok, 0);
-                            bulk_over = __shfl_sync(0xffffffffu, over, 0) != 0u;
-                            if (ok) {
-                                if (rp.timeline && go) timeline_event(slot.pix, slot.steps, 102);
-                                queue_push(slot, go, rp.xqueue, pc + 4, rp, st);
-                            }
-                        }
-                    }
                     const bool popped = fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
                     if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 101);
                     // leftovers of the express queue once its lanes may have gone
@@ -314,7 +317,9 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
         if (__popc(act) == 1 && (exhausted || hold)) {
             const int owner = __ffs(act) - 1;
             if (__shfl_sync(0xffffffffu, slot.mode, owner) == 0) {
-                lone_ray_march(slot, owner, s_w, rp.n_sq, abuf, rp, st, lane, use_queue ? 64 : (1 << 30));
+                // chunks end on multiples of 64 steps (the queues and the express hand-over are looked at in between)
+                const int chunk = 64 - (__shfl_sync(0xffffffffu, slot.steps, owner) & 63);
+                lone_ray_march(slot, owner, s_w, rp.n_sq, abuf, rp, st, lane, use_queue ? chunk : (1 << 30));
                 if (rp.timeline && lane == owner && (slot.steps & 255) < 64 && slot.steps >= 256) timeline_event(slot.pix, slot.steps, 1);
                 continue;
             }

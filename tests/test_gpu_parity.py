@@ -308,6 +308,28 @@ def test_frame_schedules_agree(env):
     assert outs[4]["evicted"] > 0 and outs[6]["evicted"] > 0 and outs[0]["evicted"] == 0
 
 
+def test_express_lanes_bit_exact(env, monkeypatch):
+    """The cooperative tracer's express lanes (full grids only, so a frame larger than 296 CTAs x 128 ray slots): default
+    thresholds, a threshold that sends nearly every ray through the express queue from the producing warps, the consumer-only
+    hand-over behind quiet SMs, and express lanes off -- same bytes as the oracle, same query count."""
+    W, H = 256, 192
+    ref = None
+    for knobs in ({}, {"NSDF_COOP_EXPRESS_STEPS": "16"}, {"NSDF_COOP_EXPRESS_STEPS": "32", "NSDF_COOP_EXPRESS_PERIOD": "37"},
+                  {"NSDF_COOP_EXPRESS_STEPS": "48", "NSDF_COOP_EXPRESS_FROM_BULK": "0", "NSDF_COOP_QUIET_PERIOD": "16",
+                   "NSDF_COOP_EVICT": "16", "NSDF_COOP_POP_MAX": "4"},
+                  {"NSDF_COOP_EXPRESS_PERIOD": "0", "NSDF_COOP_QUIET_PERIOD": "16", "NSDF_COOP_EVICT": "64"},
+                  {"NSDF_COOP_EXPRESS_PERIOD": "0"}):
+        for k, v in knobs.items():
+            monkeypatch.setenv(k, v)
+        img, stats, r = _render_both(env, "plane_1", W, H, "blue.png")
+        for k in knobs:
+            monkeypatch.delenv(k)
+        ref = ref or r
+        assert np.array_equal(img, ref["image"]), knobs
+        assert stats["queries"] == ref["queries"], knobs
+        assert stats["pixels"] == W * H
+
+
 def test_animation_net_frames_bit_exact(env, tmp_path):
     """4-input (x, y, z, t) nets, the reference's --animation mode (src/volumeRender_kernel.cu:524-545, t = frame number):
     a shipped shape with a fourth input row added to its first layer is written with nsdf_h5_write_keras, loaded through
