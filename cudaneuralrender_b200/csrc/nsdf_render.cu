@@ -315,6 +315,15 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         rp2.total_idx = 0;          // no pixels of its own: ray slots refill from the queue the first pass filled
         rp2.consumer_period = 0;
         rp2.queue_static = 1;
+        rp2.evict_steps_hi = 1 << 30;
+        rp2.express_period = (unsigned int)env_int("NSDF_COOP_EXPRESS_PERIOD", 12);   // the serial tail of this pass: express lanes
+        rp2.express_steps = env_int("NSDF_COOP_EXPRESS_STEPS", 160);
+        rp2.express_from_bulk = 1;
+        if (rp2.express_period > 0 && rp2.express_steps > 0) {
+            rp2.xqueue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);
+            rp2.xqueue_soft_cap = (unsigned int)(XQUEUE_ENTRIES / 2);
+            rp2.express_lanes = ((unsigned int)sms / rp2.express_period) * (unsigned int)occ * 4u;
+        }
         trace_coop_kernel<<<sms * occ, COOP_THREADS, coop_smem(m), stream>>>(rp2);
         return (int)cudaGetLastError();
     }

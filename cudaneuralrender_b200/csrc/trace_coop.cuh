@@ -126,7 +126,8 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     float* abuf = s_w + (rp.blob_bytes >> 2) + warp * (2 * COOP_R * WARP_ACT_STRIDE);
     const unsigned int total_warps = gridDim.x * (COOP_THREADS / 32);
     const bool from_queue = rp.queue_static != 0;
-    const bool use_queue = rp.queue != nullptr && !from_queue;
+    // second pass over a static queue: the consumer machinery runs only for the express lanes (nothing is pushed to the main queue)
+    const bool use_queue = rp.queue != nullptr && (!from_queue || rp.xqueue != nullptr);
     unsigned int n_src = rp.total_idx;
     if (from_queue) {
         n_src = rp.pixel_counter[1];

@@ -5,7 +5,7 @@ import os, sys
 import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from cudaneuralrender_b200 import host
+from cudaneuralrender_b200 import host, _capi as capi
 model, W, H = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
 settings = sys.argv[4:] or [""]
 nn = host.NeuralNetwork(); assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"))
@@ -16,12 +16,13 @@ frame = torch.zeros(W * H, dtype=torch.int32, device="cuda")
 stats = torch.zeros(6, dtype=torch.int64, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 ref = {}
+FLAGS = getattr(capi, os.environ["PROBE_FLAGS"]) if os.environ.get("PROBE_FLAGS") else 0   # e.g. RENDER_TC_FARFIELD
 for setting in settings:
     keys = []
     for kv in filter(None, setting.split(",")):
         k, v = kv.split("="); os.environ[k] = v; keys.append(k)
     for ms_cap in (int(s) for s in os.environ.get("PROBE_STEPS", "256,1024,6000").split(",")):
-        host.setSceneOptions(host.SCENE_TANH, ms_cap, 0, 0)
+        host.setSceneOptions(host.SCENE_TANH, ms_cap, FLAGS, 0)
         for _ in range(2): host.render_kernel(frame, W, H, nn, matcap)
         ts = []
         for _ in range(5):
