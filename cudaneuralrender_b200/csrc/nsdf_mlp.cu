@@ -123,6 +123,62 @@ mlp_fp32_warp16_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int 
     }
 }
 
+// Development rung (NSDF_FP32_P=40): the thread-per-point evaluator with the weights in __constant__ memory, so that they reach
+// the FFMAs through the uniform datapath / constant-bank operands instead of the shared-memory pipe (ncu: every LDS.128 costs four
+// wavefronts, which is what bounds the shared-memory forms).  One symbol per device: callers on different streams would overwrite
+// each other's weights, hence not a default.  Same arithmetic order, same bits.
+constexpr int CONST_MAX_SQ = 8;
+__constant__ float c_blob[FUSED_L0_FLOATS + CONST_MAX_SQ * FUSED_SQ_FLOATS + FUSED_LAST_FLOATS];
+
+template <int P>
+__global__ void __launch_bounds__(256, 2)
+mlp_fp32_const_kernel(int n_sq, const float* __restrict__ xin, float* __restrict__ yout, long long n, const LatticeParams lp) {
+    const long long stride = (long long)gridDim.x * 256 * P;
+    for (long long base = (long long)blockIdx.x * 256 * P; base < n; base += stride) {
+        float a[P][32];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            const long long i = base + (long long)p * 256 + threadIdx.x;
+            float x[3] = {0.0f, 0.0f, 0.0f};
+            if (i < n) {
+                if (lp.enabled) lattice_point(lp, lp.first + i, x);
+                else { x[0] = __ldg(xin + 3 * i); x[1] = __ldg(xin + 3 * i + 1); x[2] = __ldg(xin + 3 * i + 2); }
+            }
+#pragma unroll
+            for (int o = 0; o < 32; ++o)
+                a[p][o] = relu_det(fmaf(c_blob[64 + o], x[2], fmaf(c_blob[32 + o], x[1], fmaf(c_blob[o], x[0], 0.0f))) + c_blob[128 + o]);
+        }
+#pragma unroll 1
+        for (int l = 0; l < n_sq; ++l) {
+            const int wb = FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS;
+            float z[P][32];
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+#pragma unroll
+                for (int o = 0; o < 32; ++o) z[p][o] = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 32; ++k)
+#pragma unroll
+                for (int o = 0; o < 32; ++o)
+#pragma unroll
+                    for (int p = 0; p < P; ++p) z[p][o] = fmaf(c_blob[wb + k * 32 + o], a[p][k], z[p][o]);
+#pragma unroll
+            for (int p = 0; p < P; ++p)
+#pragma unroll
+                for (int o = 0; o < 32; ++o) a[p][o] = relu_det(z[p][o] + c_blob[wb + 1024 + o]);
+        }
+        const int lb = FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS;
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+            float acc = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 32; ++k) acc = fmaf(c_blob[lb + k], a[p][k], acc);
+            const long long i = base + (long long)p * 256 + threadIdx.x;
+            if (i < n) yout[i] = acc + c_blob[lb + 32];
+        }
+    }
+}
+
 // Generic dense layer (any M, K; N = 1 per batch): replaces denseLayerForward /
 // batchedDenseLayerForward (src/layers/denseLayer.cu:86-176) with the same arithmetic.
 __global__ void __launch_bounds__(256)
@@ -203,6 +259,17 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
         if (threads == 384) return go4(mlp_fp32_thread_s_kernel<4, 384, 1>, 384);
         if (threads == 128) return go4(mlp_fp32_thread_s_kernel<4, 128, 1>, 128);
         return go4(mlp_fp32_thread_s_kernel<4, 256, 1>, 256);
+    }
+    if ((P == 40 || P == 41) && m->n_sq <= CONST_MAX_SQ && m->in[0] == 3) {   // development: weights through the constant path
+        e = cudaMemcpyToSymbolAsync(c_blob, m->d_blob, m->blob_bytes, 0, cudaMemcpyDeviceToDevice, stream);
+        if (e != cudaSuccess) return (int)e;
+        const int pp = P == 40 ? 2 : 1;
+        const long long chunk = 256LL * pp;
+        long long want = (n + chunk - 1) / chunk;
+        const int grid = (int)(want < 2LL * sms ? want : 2LL * sms);
+        if (pp == 2) mlp_fp32_const_kernel<2><<<grid, 256, 0, stream>>>(m->n_sq, d_x, d_y, n, lp);
+        else mlp_fp32_const_kernel<1><<<grid, 256, 0, stream>>>(m->n_sq, d_x, d_y, n, lp);
+        return (int)cudaGetLastError();
     }
     if (P == 22) {   // development: two points per thread, activations in shared memory, the tracer's register budget
         auto go2 = [&](auto kern) -> int {

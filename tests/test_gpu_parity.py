@@ -81,7 +81,8 @@ def test_fp32_thread_evaluator_variants_bit_exact(env, monkeypatch):
         x = np.random.default_rng(n).uniform(-1, 1, (n, 3)).astype(np.float32)
         ref = oracle.mlp_forward(om, x).ravel()
         xd = torch.from_numpy(x).cuda().contiguous()
-        for p, th in (("1", None), ("2", None), ("22", None), ("4", "128"), ("4", "256"), ("4", "384"), (None, None)):
+        for p, th in (("1", None), ("2", None), ("22", None), ("4", "128"), ("4", "256"), ("4", "384"), ("40", None), ("41", None),
+                      (None, None)):
             for k, v in (("NSDF_FP32_P", p), ("NSDF_FP32_P4_THREADS", th)):
                 if v is None:
                     monkeypatch.delenv(k, raising=False)

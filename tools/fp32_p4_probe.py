@@ -12,7 +12,8 @@ x = torch.from_numpy(np.random.default_rng(0).uniform(-1, 1, (n, 3)).astype(np.f
 ref = None
 for name, env in (("P2", {"NSDF_FP32_P": "2"}), ("P1", {"NSDF_FP32_P": "1"}), ("P2s/256x2", {"NSDF_FP32_P": "22"}), ("P4/128", {"NSDF_FP32_P": "4", "NSDF_FP32_P4_THREADS": "128"}),
                   ("P4/256", {"NSDF_FP32_P": "4", "NSDF_FP32_P4_THREADS": "256"}),
-                  ("P4/384", {"NSDF_FP32_P": "4", "NSDF_FP32_P4_THREADS": "384"})):
+                  ("P4/384", {"NSDF_FP32_P": "4", "NSDF_FP32_P4_THREADS": "384"}),
+                  ("const P2", {"NSDF_FP32_P": "40"}), ("const P1", {"NSDF_FP32_P": "41"})):
     os.environ.update(env)
     out = torch.zeros(n, dtype=torch.float32, device="cuda")
     for _ in range(3): nn.forward_tensor(x, host.PREC_FP32, out=out)
