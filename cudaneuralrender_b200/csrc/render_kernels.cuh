@@ -71,6 +71,8 @@ struct RenderParams {
     int express_steps;             //   a consumer's ray with this many steps moves to an express lane when one is free (0 = off)
     unsigned int express_period;   //   the warps 0..3 of every CTA on SMs with smid % express_period == express_period - 1 are express
     unsigned int express_lanes;    //   lanes: they hold ONE ray each, so that it marches at the 1-ray latency on a quiet scheduler
+    int express_warps;             //   express lanes per CTA of an express SM (warps 0..express_warps-1)
+    int express_steps_old, express_check_old;   //   rays past express_steps_old steps ask for a lane whenever steps & express_check_old == 0
     int express_from_bulk;         //   producing warps hand rays over to free express lanes too (else only the consumers do)
     int timeline;                  // development: record the timeline of long rays (trace_coop.cuh g_timeline)
     int queue_static;              // trace_coop_kernel: the queue was filled by an earlier launch and IS the ray source

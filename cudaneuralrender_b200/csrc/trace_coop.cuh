@@ -1,21 +1,29 @@
 // =====================================================================================
 // trace_coop.cuh -- the default tracer: ONE persistent launch, every warp marches up to
-// COOP_R rays with the warp-cooperative evaluator (lane = neuron, mlp32_eval_warp).
+// COOP_R = 16 rays with the warp-cooperative evaluators of mlp_fp32.cuh.
 //
 // Replaces the host loop of render_kernel (src/volumeRender_kernel.cu:608-692) and its
 // per-iteration thrust::exclusive_scan + createBatch (:504-563): a warp's idle ray slots are
 // refilled from the global pixel counter by ballot compaction, so there is no batch to build.
 //
-// Why lane = neuron rather than lane = ray: one march step of a ray is a chain of nine dependent
-// layers.  With a ray per lane a step costs the whole warp ~9k instructions (~18 us on a busy SM),
-// which turns the few rays that need thousands of steps into tens of milliseconds;
-// with a neuron per lane a layer is a 32-deep FFMA chain and a step is ~1-2.5 us, at ~80 % of the
-// ray-per-lane instruction efficiency once COOP_R rays share every weight load.  All rays take the
-// same path, so nothing is queued or handed over, and the serial tail overlaps the bulk.
-// As rays finish and the pixels run out, the warp drops to the 4-, 2- and 1-ray evaluators.
+// Why a warp per ray group rather than a ray per lane: one march step of a ray is a chain of nine
+// dependent layers.  With a ray per lane a step costs the whole warp ~9k instructions (~18 us on a
+// busy SM), which turns the few rays that need thousands of steps into tens of
+// milliseconds; cooperatively a layer is a 32-deep FFMA chain per output.  With 9..16 busy slots the
+// warp runs the register-tiled 16-ray evaluator (mlp32_eval_warp16: 4 neurons x 4 rays per lane, ~13 us
+// per step on a full SM); with fewer it drops to the lane = neuron evaluators for 8/4/2/1 rays, and a
+// warp left with one ray runs lone_ray_march (1.15 us per step when its SM is otherwise quiet).
+//
+// Serial tail: "express lanes".  Every express_period-th SM takes no pixels; warps 0..3 of its CTAs hold
+// ONE ray each, popped from the express queue.  Any other warp hands a ray that has marched
+// express_steps steps to that queue when a lane is free (three L2 counters), and keeps it otherwise.
+// The older scheme (quiet SMs consuming a main queue fed at evict_steps_hi steps) is still here for
+// callers that set evict_steps, for the hybrid schedule and for the second pass of the mixed-precision
+// tracer, whose source IS that queue.  When all pixels are taken every idle warp serves both queues.
+// NSDF_COOP_TIMELINE=1 records when long rays are pushed/popped and how fast they step (g_timeline).
 //
 // Per ray the arithmetic is that of render_kernels.cuh (slot_start / slot_update): frames are
-// bit-identical to the oracle.
+// bit-identical to the oracle whatever the schedule.
 // =====================================================================================
 #pragma once
 #include "render_kernels.cuh"
@@ -144,7 +152,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     // express SMs (trace timeline: a lone ray steps in 1.14 us on an SM where nothing else runs, in 3.5 us beside the crowded
     // warps of a quiet SM, in 5.5 us beside 16-ray warps): warps 0..3 of their CTAs hold ONE ray each, taken from the express queue
     const bool express_sm = use_queue && rp.xqueue && rp.express_period && (sm_id() % rp.express_period) == rp.express_period - 1;
-    const bool express_lane = express_sm && warp < 4;
+    const bool express_lane = express_sm && warp < rp.express_warps;
     bool producing = !(use_queue && (express_sm || (rp.consumer_period && (sm_id() % rp.consumer_period) == rp.consumer_period - 1) ||
                                      warp >= COOP_THREADS / 32 - rp.consumer_warps));
     bool bulk_over = false, xbusy = false;   // warp-uniform
@@ -236,7 +244,8 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
         if (rp.xqueue && rp.express_steps > 0 && (!producing || rp.express_from_bulk) && !express_sm && !bulk_over) {
             // rays that have come this far move to an express lane, if one is free
             // (looked at when a ray's step count is a multiple of 16: the counters live in L2; a lone ray comes back every 64 steps)
-            const bool go = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_steps && (slot.steps & 15) == 0;
+            const bool go = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_steps &&
+                            (slot.steps & (slot.steps >= rp.express_steps_old ? rp.express_check_old : 15)) == 0;
             const unsigned int gm = __ballot_sync(0xffffffffu, go);
             if (gm) {
                 unsigned int ok = 0, over = 0;
