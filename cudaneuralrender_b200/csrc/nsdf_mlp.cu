@@ -179,6 +179,121 @@ mlp_fp32_const_kernel(int n_sq, const float* __restrict__ xin, float* __restrict
     }
 }
 
+// Development rung (NSDF_FP32_WARP_R=77, networks with 7 hidden layers): weight-stationary warp pipeline.  Warp l < 7 keeps the
+// 4 neurons x 32 k weights of hidden layer l in registers for the life of the kernel; 16-point tiles stream through the warps via
+// shared memory, one layer per tick, one __syncthreads per tick; warp 7 feeds (layer 0) and drains (last layer).  Per tile-layer the
+// shared-memory traffic is activations only (32 LDS.128 + 4 STS.128) -- the tiled evaluator re-reads the weights for every 16 points
+// and is bound by that (profiles/r01_ncu_full_trace_coop_s26.txt).  Same k-ascending chains, same bits.
+__global__ void __launch_bounds__(256, 1)
+mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ xin, float* __restrict__ yout, long long n,
+                     const LatticeParams lp) {
+    __shared__ __align__(16) float buf[2][8][16 * WARP_ACT_STRIDE];
+    __shared__ __align__(16) float4 xs[16];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane & 7, rg = lane >> 3;
+    const long long n_tiles = (n + 15) / 16;
+    const long long T = (n_tiles + gridDim.x - 1) / gridDim.x;
+    float4 wreg[32];
+    float4 breg;
+    if (warp < 7) {
+        const float4* Wt = reinterpret_cast<const float4*>(blob + FUSED_L0_FLOATS + warp * FUSED_SQ_FLOATS) + g;
+#pragma unroll
+        for (int k = 0; k < 32; ++k) wreg[k] = __ldg(Wt + k * 8);
+        breg = __ldg(Wt + 256);
+    } else {
+        const float4* S4 = reinterpret_cast<const float4*>(blob);
+        wreg[0] = __ldg(S4 + g); wreg[1] = __ldg(S4 + 8 + g); wreg[2] = __ldg(S4 + 16 + g); breg = __ldg(S4 + 32 + g);
+        const float4* LL = reinterpret_cast<const float4*>(blob + FUSED_L0_FLOATS + 7 * FUSED_SQ_FLOATS);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) wreg[8 + k] = __ldg(LL + k);
+        wreg[16] = __ldg(LL + 8);   // .x = bias of the last layer
+    }
+    for (long long t = 0; t < T + 9; ++t) {
+        const int par = (int)(t & 1);
+        if (warp < 7) {
+            const long long tile = t - 1 - warp;
+            if (tile >= 0 && tile < T) {
+                const float* in = &buf[par][warp][0] + rg * WARP_ACT_STRIDE;
+                float z[4][4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) z[i][j] = 0.0f;
+#pragma unroll
+                for (int kc = 0; kc < 8; ++kc) {
+                    float a[4][4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 av = *reinterpret_cast<const float4*>(in + 4 * j * WARP_ACT_STRIDE + 4 * kc);
+                        a[j][0] = av.x; a[j][1] = av.y; a[j][2] = av.z; a[j][3] = av.w;
+                    }
+#pragma unroll
+                    for (int kk = 0; kk < 4; ++kk) {
+                        const float4 w = wreg[4 * kc + kk];
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            z[0][j] = fmaf(w.x, a[j][kk], z[0][j]);
+                            z[1][j] = fmaf(w.y, a[j][kk], z[1][j]);
+                            z[2][j] = fmaf(w.z, a[j][kk], z[2][j]);
+                            z[3][j] = fmaf(w.w, a[j][kk], z[3][j]);
+                        }
+                    }
+                }
+                float* out = &buf[par ^ 1][warp + 1][0];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float4 o;
+                    o.x = relu_det(z[0][j] + breg.x); o.y = relu_det(z[1][j] + breg.y);
+                    o.z = relu_det(z[2][j] + breg.z); o.w = relu_det(z[3][j] + breg.w);
+                    *reinterpret_cast<float4*>(out + (rg + 4 * j) * WARP_ACT_STRIDE + 4 * g) = o;
+                }
+            }
+        } else {
+            if (t < T) {                                   // feed: layer 0 of tile t
+                const long long i = ((long long)blockIdx.x + t * gridDim.x) * 16 + lane;
+                if (lane < 16) {
+                    float x[3] = {0.0f, 0.0f, 0.0f};
+                    if (i < n) {
+                        if (lp.enabled) lattice_point(lp, lp.first + i, x);
+                        else { x[0] = __ldg(xin + 3 * i); x[1] = __ldg(xin + 3 * i + 1); x[2] = __ldg(xin + 3 * i + 2); }
+                    }
+                    xs[lane] = make_float4(x[0], x[1], x[2], 0.0f);
+                }
+                __syncwarp();
+                float* out = &buf[par ^ 1][0][0];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 x = xs[rg + 4 * j];
+                    float4 o;
+                    o.x = relu_det(fmaf(wreg[2].x, x.z, fmaf(wreg[1].x, x.y, fmaf(wreg[0].x, x.x, 0.0f))) + breg.x);
+                    o.y = relu_det(fmaf(wreg[2].y, x.z, fmaf(wreg[1].y, x.y, fmaf(wreg[0].y, x.x, 0.0f))) + breg.y);
+                    o.z = relu_det(fmaf(wreg[2].z, x.z, fmaf(wreg[1].z, x.y, fmaf(wreg[0].z, x.x, 0.0f))) + breg.z);
+                    o.w = relu_det(fmaf(wreg[2].w, x.z, fmaf(wreg[1].w, x.y, fmaf(wreg[0].w, x.x, 0.0f))) + breg.w);
+                    *reinterpret_cast<float4*>(out + (rg + 4 * j) * WARP_ACT_STRIDE + 4 * g) = o;
+                }
+                __syncwarp();
+            }
+            const long long to = t - 8;                    // drain: last layer of tile t - 8
+            if (to >= 0 && to < T) {
+                const float* in = &buf[par][7][0] + (lane & 15) * WARP_ACT_STRIDE;
+                float acc = 0.0f;
+#pragma unroll
+                for (int kc = 0; kc < 8; ++kc) {
+                    const float4 w = wreg[8 + kc];
+                    const float4 av = *reinterpret_cast<const float4*>(in + 4 * kc);
+                    acc = fmaf(w.x, av.x, acc);
+                    acc = fmaf(w.y, av.y, acc);
+                    acc = fmaf(w.z, av.z, acc);
+                    acc = fmaf(w.w, av.w, acc);
+                }
+                const long long i = ((long long)blockIdx.x + to * gridDim.x) * 16 + lane;
+                if (lane < 16 && i < n) yout[i] = acc + wreg[16].x;
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // Generic dense layer (any M, K; N = 1 per batch): replaces denseLayerForward /
 // batchedDenseLayerForward (src/layers/denseLayer.cu:86-176) with the same arithmetic.
 __global__ void __launch_bounds__(256)
@@ -224,6 +339,13 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
             kern<<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         };
+        if (R == 77 && m->n_sq == 7 && m->in[0] == 3) {   // development: weight-stationary warp pipeline
+            const long long n_tiles = (n + 15) / 16;
+            const int occ = env_int("NSDF_FP32_PIPE_CTAS", 1);
+            const int grid = (int)(n_tiles < (long long)sms * occ ? n_tiles : (long long)sms * occ);
+            mlp_fp32_pipe_kernel<<<grid, 256, 0, stream>>>(m->d_blob, d_x, d_y, n, lp);
+            return (int)cudaGetLastError();
+        }
         if (R == 16) {
             const size_t smem = m->blob_bytes + 8 * 2 * 16 * WARP_ACT_STRIDE * sizeof(float);
             cudaError_t e2 = cudaFuncSetAttribute(mlp_fp32_warp16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);

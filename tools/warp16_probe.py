@@ -12,7 +12,7 @@ n = (1 << 23) + 12345
 x = torch.from_numpy(np.random.default_rng(0).uniform(-1, 1, (n, 3)).astype(np.float32)).cuda()
 os.environ["NSDF_FP32_P"] = "2"
 ref = nn.forward_tensor(x, host.PREC_FP32).clone()
-for r in ("8", "16"):
+for r in ("8", "16", "77"):
     os.environ["NSDF_FP32_WARP_R"] = r
     out = torch.zeros(n, dtype=torch.float32, device="cuda")
     for _ in range(3): nn.forward_tensor(x, host.PREC_FP32_WARP, out=out)
@@ -25,6 +25,7 @@ for r in ("8", "16"):
     same = bool(torch.equal(out.view(torch.int32), ref.view(torch.int32)))
     print("warp R", r, "ms", round(min(ts), 4), "Gq/s", round(n / min(ts) / 1e6, 3), "bit-equal to thread P2:", same, flush=True)
 del os.environ["NSDF_FP32_P"]
+if os.environ.get("PROBE_DENSE_ONLY"): sys.exit(0)
 
 matcap = oracle.load_matcap_png(os.path.join(ROOT, "data", "matcaps", "blue.png"))
 iv, nm = oracle.view_matrices()
