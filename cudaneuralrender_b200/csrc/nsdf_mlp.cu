@@ -184,14 +184,17 @@ mlp_fp32_const_kernel(int n_sq, const float* __restrict__ xin, float* __restrict
 // shared memory, one layer per tick, one __syncthreads per tick; warp 7 feeds (layer 0) and drains (last layer).  Per tile-layer the
 // shared-memory traffic is activations only (32 LDS.128 + 4 STS.128) -- the tiled evaluator re-reads the weights for every 16 points
 // and is bound by that (profiles/r01_ncu_full_trace_coop_s26.txt).  Same k-ascending chains, same bits.
+template <int NT>   // NT 16-point tiles per tick (NT * 4 points per lane)
 __global__ void __launch_bounds__(256, 1)
 mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ xin, float* __restrict__ yout, long long n,
                      const LatticeParams lp) {
-    __shared__ __align__(16) float buf[2][8][16 * WARP_ACT_STRIDE];
-    __shared__ __align__(16) float4 xs[16];
+    constexpr int RAYS = 16 * NT, NJ = 4 * NT;
+    extern __shared__ __align__(16) float pipe_smem[];
+    float* const buf = pipe_smem;                                   // [2][8][RAYS * WARP_ACT_STRIDE]
+    float4* const xs = reinterpret_cast<float4*>(pipe_smem + 2 * 8 * RAYS * WARP_ACT_STRIDE);   // [RAYS]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane & 7, rg = lane >> 3;
-    const long long n_tiles = (n + 15) / 16;
+    const long long n_tiles = (n + RAYS - 1) / RAYS;
     const long long T = (n_tiles + gridDim.x - 1) / gridDim.x;
     float4 wreg[32];
     float4 breg;
@@ -208,22 +211,23 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
         for (int k = 0; k < 8; ++k) wreg[8 + k] = __ldg(LL + k);
         wreg[16] = __ldg(LL + 8);   // .x = bias of the last layer
     }
+    auto stage = [&](int par, int st) -> float* { return buf + ((par * 8 + st) * RAYS) * WARP_ACT_STRIDE; };
     for (long long t = 0; t < T + 9; ++t) {
         const int par = (int)(t & 1);
         if (warp < 7) {
             const long long tile = t - 1 - warp;
             if (tile >= 0 && tile < T) {
-                const float* in = &buf[par][warp][0] + rg * WARP_ACT_STRIDE;
-                float z[4][4];
+                const float* in = stage(par, warp) + rg * WARP_ACT_STRIDE;
+                float z[4][NJ];
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) z[i][j] = 0.0f;
+                    for (int j = 0; j < NJ; ++j) z[i][j] = 0.0f;
 #pragma unroll
                 for (int kc = 0; kc < 8; ++kc) {
-                    float a[4][4];
+                    float a[NJ][4];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
+                    for (int j = 0; j < NJ; ++j) {
                         const float4 av = *reinterpret_cast<const float4*>(in + 4 * j * WARP_ACT_STRIDE + 4 * kc);
                         a[j][0] = av.x; a[j][1] = av.y; a[j][2] = av.z; a[j][3] = av.w;
                     }
@@ -231,7 +235,7 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                     for (int kk = 0; kk < 4; ++kk) {
                         const float4 w = wreg[4 * kc + kk];
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
+                        for (int j = 0; j < NJ; ++j) {
                             z[0][j] = fmaf(w.x, a[j][kk], z[0][j]);
                             z[1][j] = fmaf(w.y, a[j][kk], z[1][j]);
                             z[2][j] = fmaf(w.z, a[j][kk], z[2][j]);
@@ -239,9 +243,9 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                         }
                     }
                 }
-                float* out = &buf[par ^ 1][warp + 1][0];
+                float* out = stage(par ^ 1, warp + 1);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < NJ; ++j) {
                     float4 o;
                     o.x = relu_det(z[0][j] + breg.x); o.y = relu_det(z[1][j] + breg.y);
                     o.z = relu_det(z[2][j] + breg.z); o.w = relu_det(z[3][j] + breg.w);
@@ -250,8 +254,8 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
             }
         } else {
             if (t < T) {                                   // feed: layer 0 of tile t
-                const long long i = ((long long)blockIdx.x + t * gridDim.x) * 16 + lane;
-                if (lane < 16) {
+                if (lane < RAYS) {
+                    const long long i = ((long long)blockIdx.x + t * gridDim.x) * RAYS + lane;
                     float x[3] = {0.0f, 0.0f, 0.0f};
                     if (i < n) {
                         if (lp.enabled) lattice_point(lp, lp.first + i, x);
@@ -260,9 +264,9 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                     xs[lane] = make_float4(x[0], x[1], x[2], 0.0f);
                 }
                 __syncwarp();
-                float* out = &buf[par ^ 1][0][0];
+                float* out = stage(par ^ 1, 0);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < NJ; ++j) {
                     const float4 x = xs[rg + 4 * j];
                     float4 o;
                     o.x = relu_det(fmaf(wreg[2].x, x.z, fmaf(wreg[1].x, x.y, fmaf(wreg[0].x, x.x, 0.0f))) + breg.x);
@@ -274,8 +278,8 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                 __syncwarp();
             }
             const long long to = t - 8;                    // drain: last layer of tile t - 8
-            if (to >= 0 && to < T) {
-                const float* in = &buf[par][7][0] + (lane & 15) * WARP_ACT_STRIDE;
+            if (to >= 0 && to < T && lane < RAYS) {
+                const float* in = stage(par, 7) + lane * WARP_ACT_STRIDE;
                 float acc = 0.0f;
 #pragma unroll
                 for (int kc = 0; kc < 8; ++kc) {
@@ -286,8 +290,8 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                     acc = fmaf(w.z, av.z, acc);
                     acc = fmaf(w.w, av.w, acc);
                 }
-                const long long i = ((long long)blockIdx.x + to * gridDim.x) * 16 + lane;
-                if (lane < 16 && i < n) yout[i] = acc + wreg[16].x;
+                const long long i = ((long long)blockIdx.x + to * gridDim.x) * RAYS + lane;
+                if (i < n) yout[i] = acc + wreg[16].x;
             }
         }
         __syncthreads();
@@ -339,11 +343,15 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
             kern<<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         };
-        if (R == 77 && m->n_sq == 7 && m->in[0] == 3) {   // development: weight-stationary warp pipeline
-            const long long n_tiles = (n + 15) / 16;
-            const int occ = env_int("NSDF_FP32_PIPE_CTAS", 1);
-            const int grid = (int)(n_tiles < (long long)sms * occ ? n_tiles : (long long)sms * occ);
-            mlp_fp32_pipe_kernel<<<grid, 256, 0, stream>>>(m->d_blob, d_x, d_y, n, lp);
+        if ((R == 77 || R == 78) && m->n_sq == 7 && m->in[0] == 3) {   // development: weight-stationary warp pipeline (1 / 2 tiles per tick)
+            const int nt = R == 77 ? 1 : 2;
+            const long long n_tiles = (n + 16 * nt - 1) / (16 * nt);
+            const int grid = (int)(n_tiles < (long long)sms ? n_tiles : (long long)sms);
+            const size_t smem = (size_t)(2 * 8 * 16 * nt * WARP_ACT_STRIDE) * sizeof(float) + 16 * nt * sizeof(float4);
+            cudaError_t e2 = cudaFuncSetAttribute(mlp_fp32_pipe_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+            if (e2 != cudaSuccess) return (int)e2;
+            if (nt == 1) mlp_fp32_pipe_kernel<1><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
+            else mlp_fp32_pipe_kernel<2><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         }
         if (R == 16) {
