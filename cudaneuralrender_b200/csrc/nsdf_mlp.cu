@@ -254,14 +254,14 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
             }
         } else {
             if (t < T) {                                   // feed: layer 0 of tile t
-                if (lane < RAYS) {
-                    const long long i = ((long long)blockIdx.x + t * gridDim.x) * RAYS + lane;
+                for (int r = lane; r < RAYS; r += 32) {
+                    const long long i = ((long long)blockIdx.x + t * gridDim.x) * RAYS + r;
                     float x[3] = {0.0f, 0.0f, 0.0f};
                     if (i < n) {
                         if (lp.enabled) lattice_point(lp, lp.first + i, x);
                         else { x[0] = __ldg(xin + 3 * i); x[1] = __ldg(xin + 3 * i + 1); x[2] = __ldg(xin + 3 * i + 2); }
                     }
-                    xs[lane] = make_float4(x[0], x[1], x[2], 0.0f);
+                    xs[r] = make_float4(x[0], x[1], x[2], 0.0f);
                 }
                 __syncwarp();
                 float* out = stage(par ^ 1, 0);
@@ -278,8 +278,9 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                 __syncwarp();
             }
             const long long to = t - 8;                    // drain: last layer of tile t - 8
-            if (to >= 0 && to < T && lane < RAYS) {
-                const float* in = stage(par, 7) + lane * WARP_ACT_STRIDE;
+            if (to >= 0 && to < T) {
+              for (int r = lane; r < RAYS; r += 32) {
+                const float* in = stage(par, 7) + r * WARP_ACT_STRIDE;
                 float acc = 0.0f;
 #pragma unroll
                 for (int kc = 0; kc < 8; ++kc) {
@@ -290,8 +291,9 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
                     acc = fmaf(w.z, av.z, acc);
                     acc = fmaf(w.w, av.w, acc);
                 }
-                const long long i = ((long long)blockIdx.x + to * gridDim.x) * RAYS + lane;
+                const long long i = ((long long)blockIdx.x + to * gridDim.x) * RAYS + r;
                 if (i < n) yout[i] = acc + wreg[16].x;
+              }
             }
         }
         __syncthreads();
@@ -343,14 +345,17 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
             kern<<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         };
-        if ((R == 77 || R == 78) && m->n_sq == 7 && m->in[0] == 3) {   // development: weight-stationary warp pipeline (1 / 2 tiles per tick)
-            const int nt = R == 77 ? 1 : 2;
+        if ((R == 77 || R == 78 || R == 79) && m->n_sq == 7 && m->in[0] == 3) {   // development: weight-stationary warp pipeline (1 / 2 tiles per tick)
+            const int nt = R - 76;
             const long long n_tiles = (n + 16 * nt - 1) / (16 * nt);
             const int grid = (int)(n_tiles < (long long)sms ? n_tiles : (long long)sms);
             const size_t smem = (size_t)(2 * 8 * 16 * nt * WARP_ACT_STRIDE) * sizeof(float) + 16 * nt * sizeof(float4);
             cudaError_t e2 = cudaFuncSetAttribute(mlp_fp32_pipe_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
             if (e2 != cudaSuccess) return (int)e2;
-            if (nt == 1) mlp_fp32_pipe_kernel<1><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
+            e2 = cudaFuncSetAttribute(mlp_fp32_pipe_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 120 * 1024);
+            if (e2 != cudaSuccess) return (int)e2;
+            if (nt == 3) mlp_fp32_pipe_kernel<3><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
+            else if (nt == 1) mlp_fp32_pipe_kernel<1><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
             else mlp_fp32_pipe_kernel<2><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         }

@@ -102,7 +102,7 @@ def test_fp32_warp_evaluator_widths_bit_exact(env, monkeypatch):
             x = np.random.default_rng(n).uniform(-1, 1, (n, 3)).astype(np.float32)
             ref = oracle.mlp_forward(om, x).ravel()
             xd = torch.from_numpy(x).cuda().contiguous()
-            for r in ("78", "77", "16", "8", "4", "2", "1"):
+            for r in ("79", "78", "77", "16", "8", "4", "2", "1"):
                 monkeypatch.setenv("NSDF_FP32_WARP_R", r)
                 y = nn.forward_tensor(xd, host.PREC_FP32_WARP).cpu().numpy()
                 assert np.array_equal(_bits(y), _bits(ref)), (name, n, r)

@@ -12,7 +12,7 @@ n = (1 << 23) + 12345
 x = torch.from_numpy(np.random.default_rng(0).uniform(-1, 1, (n, 3)).astype(np.float32)).cuda()
 os.environ["NSDF_FP32_P"] = "2"
 ref = nn.forward_tensor(x, host.PREC_FP32).clone()
-for r in ("8", "16", "77", "78"):
+for r in ("8", "16", "77", "78", "79"):
     os.environ["NSDF_FP32_WARP_R"] = r
     out = torch.zeros(n, dtype=torch.float32, device="cuda")
     for _ in range(3): nn.forward_tensor(x, host.PREC_FP32_WARP, out=out)
