@@ -5,7 +5,7 @@
 // (the reference's --single path, generateSingleImage :404-468); --spin renders 360 frames with
 // viewRotation.y = i and frameNumber = i (doABarrelRoll :470-478).  Output: <prefix><basename>.png with the
 // reference's 180-degree turn (Image::savePNG), and the same frame as PPM with --ppm.
-// Extra flags: --ppm, --scene tanh|manysphere|round|displace|sphere|cylindercut|spherecut (scene programs), --max-steps N, --precision N (NSDF_PREC_*), --views N
+// Extra flags: --ppm, --scene manysphere|tanh|round|displace|sphere|cylindercut|spherecut (scene programs; default manysphere = HEAD), --math reference|deterministic, --max-steps N, --precision N (NSDF_PREC_*), --views N
 // (turntable of N views instead of 360), --gpu K (device ordinal), --stats.
 #include <chrono>
 #include <cmath>
@@ -35,7 +35,7 @@ static void usage() {
                  "\t--single one frame (default here: there is no interactive mode)\n"
                  "\t--spin 360 frames (or --views N) rotating about y\n"
                  "\t--animation 4-input (xyzt) networks\n"
-                 "\t--ppm also write <name>.ppm   --scene tanh|manysphere|round|displace|sphere|cylindercut|spherecut   --max-steps N   --precision N\n"
+                 "\t--ppm also write <name>.ppm   --scene manysphere|tanh|round|displace|sphere|cylindercut|spherecut   --math reference|deterministic   --max-steps N   --precision N\n"
                  "\t--gpu K   --stats   -h (--help)\n";
 }
 static int countDigit(int n) {
@@ -64,7 +64,10 @@ int main(int argc, char** argv) {
     const bool ppm = cmdOptionExists(argv, end, "--ppm");
     const int maxSteps = getCmdOption(argv, end, "--max-steps") ? atoi(getCmdOption(argv, end, "--max-steps")) : 6000;
     const char* sceneName = getCmdOption(argv, end, "--scene");
-    const int scene = (sceneName && std::strcmp(sceneName, "manysphere") == 0) ? NSDF_SCENE_MANYSPHERE : NSDF_SCENE_TANH;
+    // default = what the reference's HEAD build renders: sceneSDF returns manySphere(p, nSDF, true) (src/volumeRender_kernel.cu:221)
+    const int scene = (sceneName && std::strcmp(sceneName, "tanh") == 0) ? NSDF_SCENE_TANH : NSDF_SCENE_MANYSPHERE;
+    const char* mathName = getCmdOption(argv, end, "--math");
+    const int mathMode = (mathName && std::strcmp(mathName, "deterministic") == 0) ? NSDF_MATH_DETERMINISTIC : NSDF_MATH_REFERENCE;
     // the scenes sceneSDF (src/volumeRender_kernel.cu:217-230) holds commented out, as scene programs
     nsdf_scene_op prog[2] = {};
     int progOps = 0;
@@ -103,6 +106,7 @@ int main(int argc, char** argv) {
     }
     copyStaticSettings(colorType, numInputs);
     setRenderOptions(scene, maxSteps, 0);
+    setMathMode(mathMode);
     if (progOps) setSceneProgram(prog, progOps);
 
     uint* d_output = nullptr;

@@ -2,14 +2,21 @@
 """bench.py -- headline benchmark of the neural-SDF hot path (BASELINE.json metric).
 
   python bench.py --gpus N --steps K --warmup W            # product arm (libnsdf.so on B200)
-  python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on the host cores
+  python bench.py --impl reference --gpus N --steps K ...  # reference arm: the reference's OWN CUDA (oracle/_ref/ref_driver)
 
-A "step" is one 1920x1080 sphere-traced frame of plane_1.h5 with tetrahedron normals and matcap
-shading (BASELINE config 2), inputs resident in HBM.  N > 1: one process per GPU (torchrun), every
-rank renders its own view of the turntable (rank r: ry = r * 5.625 degrees) -- whole views per GPU,
-no data-path collective, weak scaling.  Prints ONE JSON line on rank 0.
+A "step" is one pass over a FIXED view set: the 64-view turntable (ry = k * 5.625 degrees) of plane_1.h5
+at 1920x1080 with tetrahedron normals and matcap shading (BASELINE config 2), rendered with what the unmodified reference
+renders at HEAD (sceneSDF = manySphere, reference math) -- the same frames, the same config string in both arms.
+N > 1: one process per GPU (torchrun); view v goes to rank v % N, so every N renders the SAME 64 frames per step
+(strong scaling, no data-path collective).  `value` = frames/s of the whole job.
+
+Every line also carries the other BASELINE configs as legs: `frame4k_tiles` (C4: one 3840x2160 frame, 64x64 tiles round-robin
+over the N GPUs, peer stores into GPU 0 over NVLink), `turntable_c5` (C5: 64 views x 5 shapes), and at N = 1 `c1` (car_1
+512x512 frame, 1 000 000-point batch from an HBM B x 3 buffer), `dense_256cubed` (C3), `tanh_scene`, `mixed_precision`,
+`parity_vs_oracle`, `parity_vs_reference`, `cpu_baseline`.  Prints ONE JSON line on rank 0.
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -21,10 +28,21 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLOP_PER_QUERY = 14592            # 2 * (3*32 + 7*32*32 + 32*1), SURVEY 8(d)
+FP32_ALU_TFLOPS = 74.4            # 148 SMs x 128 FMA lanes x 2 x 1.965 GHz: the ceiling of the bit-exact fp32 rung
 MODEL = "plane_1"
 W, H = 1920, 1080
 MATCAP = "blue.png"
+N_VIEWS = 64
 VIEW_STEP_DEG = 5.625
+SHAPES = ["car_1", "plane_1", "plane_2", "plane_3", "3a3d4a90a2db90b4203936772104a82d.obj"]
+WORKLOAD = (f"{MODEL}.h5 {W}x{H} sphere-traced frames, {N_VIEWS}-view turntable ry=k*{VIEW_STEP_DEG}deg per step, FD normals + "
+            f"matcap {MATCAP}, scene=manySphere (reference HEAD), max_steps=6000")
+METRIC = "1080p frames/sec (plane_1, FD normals + matcap)"
+REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+
+
+def geom(name):
+    return os.path.join(ROOT, "data", "neuralGeometries", name + ".h5")
 
 
 def peaks():
@@ -34,6 +52,18 @@ def peaks():
         return {"hbm_gbs": d["hbm_gbs"], "tflops_burst": d["bf16_tflops"], "tflops_sustained": d["bf16_tflops_sustained"],
                 "source": "measured"}
     return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def tracer_source_sha():
+    """sha of the tracer's sources: profiles/ncu_traffic.json is only quoted when it was captured from these bytes."""
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "cudaneuralrender_b200", "csrc")
+    for f in ("trace_coop.cuh", "render_kernels.cuh", "mlp_fp32.cuh", "device_math.cuh", "nsdf_render.cu"):
+        try:
+            h.update(open(os.path.join(d, f), "rb").read())
+        except OSError:
+            pass
+    return h.hexdigest()[:16]
 
 
 class ClockSampler:
@@ -73,164 +103,299 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_oracle_frame(rows=None, nthreads=0, ry=0.0):
-    """One (sampled) frame of the workload on the host cores through the CPU oracle."""
+# ---- checker / baseline legs (the only places that touch oracle/) -------------------------------------------------------
+def cpu_oracle_frame(rows=None, nthreads=0, ry=0.0, scene=None, model=MODEL, w=W, h=H):
+    """One (sampled) frame on the host cores through the CPU oracle (deterministic arithmetic)."""
     from oracle import oracle
-    m = oracle.Model.from_h5(os.path.join(ROOT, "data", "neuralGeometries", MODEL + ".h5"))
+    m = oracle.Model.from_h5(geom(model))
     mc = oracle.load_matcap_png(os.path.join(ROOT, "data", "matcaps", MATCAP))
     iv, nm = oracle.view_matrices(0.0, ry)
     t0 = time.perf_counter()
-    r = oracle.render(m, iv, nm, W, H, matcap=mc, want_stats=False, rows=rows, nthreads=nthreads)
-    return time.perf_counter() - t0, r["queries"], oracle.hardware_threads()
+    r = oracle.render(m, iv, nm, w, h, matcap=mc, want_stats=False, rows=rows, nthreads=nthreads,
+                      scene=oracle.SCENE_MANYSPHERE if scene is None else scene)
+    return time.perf_counter() - t0, r, oracle.hardware_threads()
 
 
-REF_DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
-
-
-def reference_cuda_frame(frames, model=MODEL, w=W, h=H, ry=0.0, timeout=900):
-    """The UNMODIFIED reference's own CUDA render_kernel (oracle/_ref/ref_driver = the reference's translation units
-    compiled from /root/reference by oracle/build_ref.sh + a headless main) on this box's GPU 0: `frames` timed frames
-    after one warm-up call.  Returns the driver's JSON or None when it is not built / there is no GPU."""
-    import tempfile
-    import numpy as np
+def reference_cuda(args_list, timeout=900):
+    """oracle/_ref/ref_driver = the UNMODIFIED reference's CUDA translation units (compiled from /root/reference by
+    oracle/build_ref.sh) + a headless main.  Returns its JSON line, or None when it is not built / fails / there is no GPU."""
     if not os.path.exists(REF_DRIVER):
         return None
+    try:
+        r = subprocess.run([REF_DRIVER] + args_list, capture_output=True, text=True, timeout=timeout)
+    except (OSError, subprocess.TimeoutExpired):
+        return None
+    if r.returncode != 0:
+        return None
+    for ln in r.stdout.splitlines():
+        if ln.startswith("{"):
+            return json.loads(ln)
+    return None
+
+
+def reference_cuda_frame(frames, model=MODEL, w=W, h=H, ry=0.0, td=None):
+    import tempfile
+    import numpy as np
     from oracle import oracle
     iv, nm = oracle.view_matrices(0.0, ry)
-    with tempfile.TemporaryDirectory() as td:
-        cam = os.path.join(td, "cam.f32")
+    with tempfile.TemporaryDirectory() as tmp:
+        cam = os.path.join(tmp, "cam.f32")
         np.concatenate([np.asarray(iv, np.float32).ravel(), np.asarray(nm, np.float32).ravel()]).tofile(cam)
-        cmd = [REF_DRIVER, "render", os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"), str(w), str(h),
-               os.path.join(ROOT, "data", "matcaps", MATCAP), cam, "0", os.path.join(td, "out.u32"), str(frames)]
-        try:
-            r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
-        except (OSError, subprocess.TimeoutExpired):
-            return None
-        if r.returncode != 0:
-            return None
-        for ln in r.stdout.splitlines():
-            if ln.startswith("{"):
-                return json.loads(ln)
-    return None
+        return reference_cuda(["render", geom(model), str(w), str(h), os.path.join(ROOT, "data", "matcaps", MATCAP), cam, "0",
+                               os.path.join(tmp, "out.u32"), str(frames)])
 
 
 def run_reference(args):
     """--impl reference.  The reference (daviesthomas/cudaNeuralRender) has NO CPU implementation of this path: its
-    implementation IS CUDA.  When oracle/_ref/ref_driver exists (the reference's own, unmodified CUDA translation units,
-    built by oracle/build_ref.sh) and a GPU is present, this arm times THAT on the same box: whole 1080p plane_1 frames
-    through the reference's render_kernel (host loop of <= 6000 iterations x {thrust scan, D2H, createBatch, 9 CUTLASS
-    GemmBatched, singleMarch}).  Its sceneSDF is what HEAD evaluates (manySphere); the native arm reports the same scene
-    as `head_scene`.  Otherwise it times the CPU oracle (a line-by-line port) with all host threads on 1/8 of the rows."""
+    implementation IS CUDA.  This arm times THAT on the same box: whole 1080p plane_1 frames of the same view set through the
+    reference's own render_kernel (host loop of <= 6000 iterations x {thrust scan, D2H, createBatch, 9 CUTLASS GemmBatched,
+    singleMarch}).  One view per step, cycling through the set in order (a frame takes > 1 s).  Without the built driver or a
+    GPU it times the CPU oracle port (all host threads, 1/8 of the rows of each view)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cfg = {"workload": f"{MODEL}.h5 {W}x{H} sphere-traced frame, FD normals + matcap {MATCAP}, max_steps=6000"}
-    base = {"impl": "reference", "metric": "1080p frames/sec (plane_1, FD normals + matcap)", "unit": "frames/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "gpu_launches": 0}
+    cfg = {"workload": WORKLOAD}
+    base = {"impl": "reference", "metric": METRIC, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "gpu_launches": 0}
     have_gpu = False
     try:
         import torch
         have_gpu = torch.cuda.is_available()
     except Exception:
         pass
-    ref = reference_cuda_frame(max(1, args.steps)) if (have_gpu and not args.cpu_port) else None
-    if ref is not None:
-        fps = 1e3 / ref["mean_ms"]
-        cfg["note"] = "reference's own CUDA kernels (unmodified, sm_100 build), scene = manySphere as at HEAD, one process, GPU 0"
-        line = dict(base, value=fps, ms_per_step=ref["mean_ms"], config=cfg,
-                    cpu_baseline={"value": fps, "unit": "frames/s", "cores": 1, "kind": "reference",
-                                  "sample": f"{ref['frames']} whole {W}x{H} frames through the reference's render_kernel on this "
-                                            f"box's GPU 0 after one warm-up frame (best {ref['best_ms']:.1f} ms, first {ref['first_call_ms']:.1f} ms)"},
-                    e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
-        print(json.dumps(line), flush=True)
-        return
+    if have_gpu and not args.cpu_port and os.path.exists(REF_DRIVER):
+        times, first = [], None
+        for _ in range(max(0, args.warmup - 1)):     # the driver's own first call inside each process is a warm-up frame already
+            reference_cuda_frame(1, ry=0.0)
+        for k in range(max(1, args.steps)):
+            r = reference_cuda_frame(1, ry=(k % N_VIEWS) * VIEW_STEP_DEG)
+            if r is None:
+                times = []
+                break
+            times.append(r["mean_ms"])
+            first = first or r["first_call_ms"]
+        if times:
+            ms = sum(times) / len(times)
+            fps = 1e3 / ms
+            cfg["note"] = ("reference's own CUDA kernels (unmodified, sm_100 build) on this box's GPU 0, one process; one view of the "
+                           "set per step (views 0.." + str(len(times) - 1) + "), each timed after a warm-up frame of the same view")
+            line = dict(base, value=fps, ms_per_step=ms, config=cfg,
+                        cpu_baseline={"value": fps, "unit": "frames/s", "cores": 1, "kind": "reference",
+                                      "sample": f"{len(times)} whole {W}x{H} frames (views 0..{len(times) - 1} of the set) through the "
+                                                f"reference's render_kernel on GPU 0 (min {min(times):.1f} ms, max {max(times):.1f} ms)"},
+                        e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
+            print(json.dumps(line), flush=True)
+            return
     stride = 8
     for _ in range(args.warmup):
         cpu_oracle_frame(rows=(0, H, stride))
     ts, qs, cores = [], 0, 0
-    for _ in range(args.steps):
-        dt, q, cores = cpu_oracle_frame(rows=(0, H, stride))
+    for k in range(args.steps):
+        dt, r, cores = cpu_oracle_frame(rows=(0, H, stride), ry=(k % N_VIEWS) * VIEW_STEP_DEG)
         ts.append(dt)
-        qs += q
+        qs += r["queries"]
     total = sum(ts)
     fps = args.steps / (total * stride)
-    sample = f"rows y%{stride}==0 of the {W}x{H} frame per step (1/{stride} of the rays), scaled by {stride}"
-    cfg["note"] = "reference has no CPU path and its CUDA build is not available here; oracle port (scene = tanh) timed"
+    cfg["note"] = "the reference's CUDA build is not available here (no GPU or oracle/_ref missing): CPU oracle port timed"
     line = dict(base, value=fps, ms_per_step=1e3 * total / args.steps * stride, config=cfg, queries_per_s=qs / total,
-                cpu_baseline={"value": fps, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+                cpu_baseline={"value": fps, "unit": "frames/s", "cores": cores, "kind": "port",
+                              "sample": f"rows y%{stride}==0 of one view per step (1/{stride} of the rays), scaled by {stride}"},
                 e2e={"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
     print(json.dumps(line), flush=True)
+
+
+def compare_frames(mine, ref):
+    import numpy as np
+    hm, hr = mine != 0, ref != 0
+    mism = hm != hr
+    mism[-1, -1] = False           # the reference reads a stale SDF slot for the last pixel (SURVEY App. E-6)
+    both = hm & hr
+    both[-1, -1] = False
+    ch = lambda v: np.stack([(v >> s) & 255 for s in (0, 8, 16)], -1).astype(np.int32)  # noqa: E731
+    diff = np.abs(ch(mine) - ch(ref))[both]
+    neq = mine != ref
+    neq[-1, -1] = False
+    return {"mask_mismatches": int(mism.sum()), "differing_pixels": int(neq.sum()), "hit_pixels": int(both.sum()),
+            "frac_within_1_255": float((diff.max(1) <= 1).mean()) if diff.size else 1.0}
+
+
+# ---- product arm ------------------------------------------------------------------------------------------------------
+class Dist:
+    def __init__(self):
+        import torch
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            import torch.distributed as dist
+            self.dist = dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, x, op="max"):
+        if self.world == 1:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op={"max": self.dist.ReduceOp.MAX, "min": self.dist.ReduceOp.MIN, "sum": self.dist.ReduceOp.SUM}[op])
+        return float(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+
+
+def timed(torch, fn, reps, flush=None):
+    """Device time of fn() in ms, per repetition (events on the current stream, L2 flushed outside the events)."""
+    out = []
+    for _ in range(reps):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        out.append((a, b))
+    torch.cuda.synchronize()
+    return [a.elapsed_time(b) for a, b in out]
+
+
+def tiles_leg(D, args, host, multigpu, flush, steps):
+    """BASELINE config 4: one 3840x2160 frame of 3a3d4a90....obj.h5 (reference HEAD scene), 64x64 tiles round-robin over the
+    ranks, every rank's tracer storing its tiles straight into rank 0's frame buffer over NVLink (peer-mapped d_out)."""
+    import numpy as np
+    torch = D.torch
+    model, Wt, Ht = SHAPES[4], 3840, 2160
+    nn = host.NeuralNetwork()
+    assert nn.load(geom(model))
+    matcap = host.Image()
+    assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.updateViewMatrices((0.0, 0.0, 0.0), (0.0, 0.0, -2.0), 0)
+    host.setSceneOptions(host.SCENE_MANYSPHERE, args.max_steps, 0, 0, host.MATH_REFERENCE)
+    frame = multigpu.PeerFrame(Wt, Ht, D.rank, D.world, root=0)
+    stats = torch.zeros(6, dtype=torch.int64, device="cuda")
+    for _ in range(2):
+        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
+    multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame, stats=stats)
+    D.barrier()
+    my_q = float(stats[0].item())
+    q_frame, q_max = D.reduce(my_q, "sum"), D.reduce(my_q, "max")
+    equal = None
+    if D.rank == 0:
+        gathered = frame.to_numpy()
+        single = torch.zeros(Wt * Ht, dtype=torch.int32, device="cuda")
+        host.render_kernel(single, Wt, Ht, nn, matcap)
+        torch.cuda.synchronize()
+        equal = bool(np.array_equal(gathered.ravel(), single.cpu().numpy().view(np.uint32)))
+        del single
+    D.barrier()
+    ms = timed(torch, lambda: multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame), steps, flush)
+    D.barrier()
+    mine = sum(ms)
+    total, tmin = D.reduce(mine, "max"), D.reduce(mine, "min")     # a frame is done when its slowest rank is
+    D.barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):                                          # end to end: the frame on rank 0's HOST every step
+        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
+        D.barrier()
+        if D.rank == 0:
+            frame.to_numpy()
+    D.barrier()
+    e2e_s = D.reduce(time.perf_counter() - t0, "max")
+    frame.close()
+    return {"workload": f"{model}.h5 {Wt}x{Ht} frame, scene=manySphere (reference HEAD), 64x64 tiles round-robin over {D.world} GPU(s), "
+                        "peer stores into GPU 0 over NVLink", "scaling": "strong",
+            "ms_per_frame": total / steps, "frames_per_s": steps / (total * 1e-3), "e2e_frames_per_s": steps / e2e_s,
+            "queries_per_frame": q_frame, "tile_balance_queries": (q_frame / D.world / q_max) if q_max else None,
+            "rank_time_min_over_max": (tmin / total) if total else None, "tiles_equal_single_gpu": equal, "steps": steps}
+
+
+def turntable_c5_leg(D, args, host, flush, size):
+    """BASELINE config 5: 64 views x the five shipped shapes, view v of shape s -> rank (s*64 + v) % N; one pass."""
+    torch = D.torch
+    matcap = host.Image()
+    assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.setSceneOptions(host.SCENE_MANYSPHERE, args.max_steps, 0, 0, host.MATH_REFERENCE)
+    nets = []
+    for s in SHAPES:
+        nn = host.NeuralNetwork()
+        assert nn.load(geom(s))
+        nets.append(nn)
+    Wc, Hc = size
+    frame = torch.zeros(Wc * Hc, dtype=torch.int32, device="cuda")
+    jobs = [(s, v) for s in range(len(SHAPES)) for v in range(N_VIEWS)]
+    mine = [j for i, j in enumerate(jobs) if i % D.world == D.rank]
+
+    def one_pass():
+        for s, v in mine:
+            host.updateViewMatrices((0.0, v * VIEW_STEP_DEG, 0.0), (0.0, 0.0, -2.0), 0)
+            host.render_kernel(frame, Wc, Hc, nets[s], matcap)
+    one_pass()
+    D.barrier()
+    ms = timed(torch, one_pass, 1, flush)[0]
+    D.barrier()
+    total = D.reduce(ms, "max")
+    return {"workload": f"64 views (ry=k*{VIEW_STEP_DEG}deg) x 5 shapes at {Wc}x{Hc}, scene=manySphere (reference HEAD), view-parallel over "
+                        f"{D.world} GPU(s)", "frames": len(jobs), "ms_total": total, "frames_per_s": len(jobs) / (total * 1e-3)}
 
 
 def run_native(args):
     import ctypes as C
     import numpy as np
-    import torch
-    import torch.distributed as dist
-    from cudaneuralrender_b200 import host
+    from cudaneuralrender_b200 import host, multigpu
     from cudaneuralrender_b200 import _capi as capi
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
+    D = Dist()
+    torch = D.torch
+    world, rank = D.world, D.rank
     L = capi.lib()
     nn = host.NeuralNetwork()
-    assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", MODEL + ".h5"))
+    assert nn.load(geom(MODEL))
     matcap = host.Image()
     assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
     host.copyStaticSettings(host.COLOR_MATCAP, 3)
-    host.updateViewMatrices((0.0, rank * VIEW_STEP_DEG, 0.0), (0.0, 0.0, -2.0), 0)
-    host.setSceneOptions(host.SCENE_TANH, args.max_steps, 0, 0)
+    head = dict(scene=host.SCENE_MANYSPHERE, max_steps=args.max_steps, flags=0, evict_steps=0, math=host.MATH_REFERENCE)
+    host.setSceneOptions(**head)
 
     frame = torch.zeros(W * H, dtype=torch.int32, device="cuda")
     stats = torch.zeros(6, dtype=torch.int64, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     K, Wm = args.steps, args.warmup
+    my_views = multigpu.views_of_rank(N_VIEWS, rank, world)
 
-    def step(flags=0):
-        host._state.flags = flags
-        host.render_kernel(frame, W, H, nn, matcap)
+    def set_view(v):
+        host.updateViewMatrices((0.0, v * VIEW_STEP_DEG, 0.0), (0.0, 0.0, -2.0), 0)
+
+    def step(st=None):
+        for v in my_views:
+            set_view(v)
+            host.render_kernel(frame, W, H, nn, matcap, stats=st)
 
     for _ in range(Wm):
         step()
-    # ---- untimed accounting pass: Q_frame, hits, rays handed to the latency warps
+    # ---- untimed accounting pass: queries, hits of this rank's views
     stats.zero_()
-    host._state.flags = 0
-    host.render_kernel(frame, W, H, nn, matcap, stats=stats)
+    step(stats)
     torch.cuda.synchronize()
-    sAB = stats.cpu().numpy().copy()
-    q_frame, hits, evicted = int(sAB[0]), int(sAB[1]), int(sAB[3])
+    sA = stats.cpu().numpy().copy()
+    q_set = D.reduce(float(sA[0]), "sum")
+    hits_set = D.reduce(float(sA[1]), "sum")
 
     # ---- timed region: K steps, device time per step, L2 flushed between steps
-    sampler = ClockSampler(local)
+    sampler = ClockSampler(D.local)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    barrier()
+    D.barrier()
     if rank == 0:
         sampler.start()
     t_wall0 = time.perf_counter()
@@ -239,107 +404,141 @@ def run_native(args):
         ev[i][0].record()
         step()
         ev[i][1].record()
-    barrier()
+    D.barrier()
     t_wall = time.perf_counter() - t_wall0
     clocks = sampler.stop() if rank == 0 else None
-    per_step_ms = [a.elapsed_time(b) for a, b in ev]
-    my_ms = sum(per_step_ms)
-    total_ms = max_over_ranks(my_ms)
+    my_ms = sum(a.elapsed_time(b) for a, b in ev)
+    total_ms = D.reduce(my_ms, "max")
+    min_ms = D.reduce(my_ms, "min")
     ms_per_step = total_ms / K
-    fps = world * K / (total_ms * 1e-3)
-    q_total = sum_over_ranks(float(q_frame))
+    fps = N_VIEWS * K / (total_ms * 1e-3)
 
-    # ---- A/B: the earlier two-launch schedule (throughput kernel, then latency kernel), same frame
-    evp = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(min(K, 5))]
-    for e in evp:
-        flush.zero_()
-        e[0].record()
-        step(capi.RENDER_TWO_KERNELS)
-        e[1].record()
-    torch.cuda.synchronize()
-    host._state.flags = 0
-    t_two = sum(e[0].elapsed_time(e[1]) for e in evp) / len(evp)
-
-    # ---- mixed-precision tracer (opt-in NSDF_RENDER_TC_FARFIELD): far field on the tensor cores (fp16x3 rung), fp32 near
-    # the surface.  Same frame, timed the same way, parity against the bit-exact frame measured here.
-    mixed = None
-    if args.mixed:
-        exact_img = frame.cpu().numpy().view(np.uint32).copy()
-        st_m = torch.zeros(6, dtype=torch.int64, device="cuda")
-        host._state.flags = capi.RENDER_TC_FARFIELD
-        host.render_kernel(frame, W, H, nn, matcap, stats=st_m)
-        for _ in range(2):
-            host.render_kernel(frame, W, H, nn, matcap)
-        evm = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(min(K, 10))]
-        for e in evm:
-            flush.zero_()
-            e[0].record()
-            host.render_kernel(frame, W, H, nn, matcap)
-            e[1].record()
-        torch.cuda.synchronize()
-        host._state.flags = 0
-        mixed_img = frame.cpu().numpy().view(np.uint32)
-        t_mixed = sum(e[0].elapsed_time(e[1]) for e in evm) / len(evm)
-        h0, h1 = exact_img != 0, mixed_img != 0
-        both = h0 & h1
-        dch = np.max(np.stack([np.abs(((exact_img >> s) & 255).astype(np.int32) - ((mixed_img >> s) & 255).astype(np.int32))
-                               for s in (0, 8, 16)]), axis=0)
-        sm = st_m.cpu().numpy()
-        mixed = {"ms_per_frame": t_mixed, "frames_per_s": 1e3 / t_mixed, "queries": int(sm[0]), "rays_finished_in_fp32": int(sm[3]),
-                 "tflops_algorithmic": int(sm[0]) * FLOP_PER_QUERY / (t_mixed * 1e-3) / 1e12,
-                 "hit_mask_mismatches": int((h0 != h1).sum()), "hit_pixels": int(h0.sum()),
-                 "hit_px_within_1_255": float((dch[both] <= 1).mean()) if both.any() else 1.0,
-                 "note": "far field (t >= 1e-4) on tcgen05 fp16x3 (|SDF err| <= 1e-4), accept test / normals / shading fp32; "
-                         "not bit-identical, so not the headline"}
-        host.render_kernel(frame, W, H, nn, matcap)   # leave the exact frame behind
-        torch.cuda.synchronize()
-
-    # ---- the scene the reference evaluates at HEAD (manySphere), for a like-for-like ratio against --impl reference
-    host.setSceneOptions(host.SCENE_MANYSPHERE, args.max_steps, 0, 0)
-    st_h = torch.zeros(6, dtype=torch.int64, device="cuda")
-    host.render_kernel(frame, W, H, nn, matcap, stats=st_h)
-    evh = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(min(K, 5))]
-    for e in evh:
-        flush.zero_()
-        e[0].record()
-        host.render_kernel(frame, W, H, nn, matcap)
-        e[1].record()
-    torch.cuda.synchronize()
-    t_head = sum(e[0].elapsed_time(e[1]) for e in evh) / len(evh)
-    head_scene = {"ms_per_frame": t_head, "frames_per_s": 1e3 / t_head, "queries": int(st_h[0].item()), "hit_pixels": int(st_h[1].item()),
-                  "note": "scene = manySphere (src/volumeRender_kernel.cu:221), what the reference's HEAD renders; bit-exact path"}
-    host.setSceneOptions(host.SCENE_TANH, args.max_steps, 0, 0)
-    host.render_kernel(frame, W, H, nn, matcap)
-    torch.cuda.synchronize()
-
-    # ---- end to end through the C ABI with host buffers (pinned): matcap H2D + frame D2H every step
+    # ---- end to end through the C ABI with HOST buffers (pinned): matcap H2D + frame D2H every frame
     mc_host = torch.from_numpy(matcap.hostData.view(np.int32)).pin_memory()
     out_host = torch.empty(W * H, dtype=torch.int32).pin_memory()
     st = capi.RenderStats()
-    opts = capi.RenderOpts(host.COLOR_MATCAP, host.SCENE_TANH, args.max_steps, 0, 1, 0, 0)
+    opts = host._opts()
 
     def e2e_step():
-        capi.check(L.nsdf_render_host(nn.handle(), C.byref(host._state.cam), mc_host.data_ptr(), matcap.shape.x,
-                                      matcap.shape.y, C.byref(opts), out_host.data_ptr(), W, H, C.byref(st)),
-                   "nsdf_render_host")
-    for _ in range(max(1, Wm)):
-        e2e_step()
-    barrier()
+        for v in my_views:
+            set_view(v)
+            capi.check(L.nsdf_render_host(nn.handle(), C.byref(host._state.cam), mc_host.data_ptr(), matcap.shape.x,
+                                          matcap.shape.y, C.byref(opts), out_host.data_ptr(), W, H, C.byref(st)), "nsdf_render_host")
+    Ke = min(K, args.e2e_steps) if args.e2e_steps > 0 else K
+    e2e_step()
+    D.barrier()
     t0 = time.perf_counter()
-    for _ in range(K):
+    for _ in range(Ke):
         e2e_step()
     torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    e2e_fps = world * K / e2e_s
-    h2d = matcap.size() * 4 + 116 + 28
-    d2h = W * H * 4 + 48
-    assert int(st.queries) == q_frame, "e2e call rendered a different frame"
+    e2e_s = D.reduce(time.perf_counter() - t0, "max")
+    e2e_fps = N_VIEWS * Ke / e2e_s
+    h2d = (matcap.size() * 4 + 116 + 48) * N_VIEWS
+    d2h = (W * H * 4 + 48) * N_VIEWS
 
-    # ---- dense sweep (BASELINE config 3): 256^3 lattice through car_1, points generated in-kernel
-    dense = None
+    # ---- legs every N carries: C4 (one 4K frame, tile-partitioned) and C5 (64 views x 5 shapes)
+    tiles = tiles_leg(D, args, host, multigpu, flush, max(3, min(K, 5))) if args.tiles else None
+    c5 = turntable_c5_leg(D, args, host, flush, (512, 512)) if args.c5 else None
+
+    if rank != 0:
+        D.close()
+        return
+
+    # ================= rank 0 only from here: single-GPU legs =================
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.setSceneOptions(**head)
+    set_view(0)
+    pk = peaks()
+    line_extra = {}
+
+    def frame_leg(net, w, h, reps=5, **opts_kw):
+        buf = torch.zeros(w * h, dtype=torch.int32, device="cuda")
+        s = torch.zeros(6, dtype=torch.int64, device="cuda")
+        host.setSceneOptions(**dict(head, **opts_kw))
+        host.render_kernel(buf, w, h, net, matcap, stats=s)
+        host.render_kernel(buf, w, h, net, matcap)
+        ms = timed(torch, lambda: host.render_kernel(buf, w, h, net, matcap), reps, flush)
+        img = buf.cpu().numpy().view(np.uint32).reshape(h, w).copy()
+        host.setSceneOptions(**head)
+        sv = s.cpu().numpy()
+        m = sum(ms) / len(ms)
+        return {"ms_per_frame": m, "ms_min": min(ms), "frames_per_s": 1e3 / m, "queries": int(sv[0]), "hit_pixels": int(sv[1]),
+                "queries_per_s": int(sv[0]) / (m * 1e-3)}, img
+
+    # view 0 alone (the frame of BASELINE config 2 as round 1 quoted it), both scenes, both math modes
+    single, img_ref_math = frame_leg(nn, W, H)
+    single["note"] = "view 0 (rx=ry=0) alone, scene=manySphere, reference math"
+    tanh_scene, _ = frame_leg(nn, W, H, scene=host.SCENE_TANH, math=host.MATH_DETERMINISTIC)
+    tanh_scene["note"] = "view 0, scene=tanh(nSDF) (the shipped renders' variant; round 1's headline), deterministic math"
+    line_extra["single_view"] = single
+    line_extra["tanh_scene"] = tanh_scene
+
+    # parity of the frame this bench times: against the reference binary's frame (golden, recorded on a B200 by
+    # tools/make_ref_golden.py) and, in the deterministic arithmetic, against the CPU oracle's frame rendered below
+    try:
+        gmeta = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_cuda_meta.json")))["frames"]
+        gf = np.load(os.path.join(ROOT, "tests", "golden", "ref_cuda_frames.npz"))
+        key = [k for k, m in gmeta.items() if m["model"] == MODEL and m["W"] == W and m["H"] == H and m["ry"] == 0.0 and m["frame"] == 0]
+        if key:
+            line_extra["parity_vs_reference"] = dict(compare_frames(img_ref_math, gf[key[0] + "/image"]),
+                                                     golden=f"tests/golden/ref_cuda_frames.npz:{key[0]} (reference's own render_kernel on a B200)")
+    except Exception as e:   # noqa: BLE001
+        line_extra["parity_vs_reference"] = {"unavailable": str(e)[:120]}
+
+    # ---- mixed-precision tracer (opt-in NSDF_RENDER_TC_FARFIELD; tanh scene only): reported, not the headline
+    if args.mixed:
+        try:
+            exact, img_e = frame_leg(nn, W, H, scene=host.SCENE_TANH, math=host.MATH_DETERMINISTIC)
+            mixed, img_m = frame_leg(nn, W, H, scene=host.SCENE_TANH, math=host.MATH_DETERMINISTIC, flags=capi.RENDER_TC_FARFIELD)
+            cmpm = compare_frames(img_m, img_e)
+            line_extra["mixed_precision"] = dict(mixed, exact_ms_per_frame=exact["ms_per_frame"], **cmpm,
+                                                 note="tanh scene; far field (t >= 1e-4) on tcgen05 fp16x3, accept test / normals / shading "
+                                                      "fp32; not bit-identical and outside the RGB tolerance on part of the hit pixels")
+        except capi.NsdfError as e:
+            line_extra["mixed_precision"] = {"unavailable": str(e)}
+
+    # ---- C1: car_1 512x512 frame, and the simpleInfer shape: 1 000 000 points from an HBM B x 3 buffer (variant A)
+    if args.c1:
+        car = host.NeuralNetwork()
+        assert car.load(geom("car_1"))
+        c1, _ = frame_leg(car, 512, 512)
+        c1 = {"frame_512": dict(c1, note="car_1.h5 512x512, scene=manySphere (reference HEAD), matcap blue.png")}
+        x = torch.from_numpy(np.random.default_rng(0).uniform(-1, 1, (1000000, 3)).astype(np.float32)).cuda().contiguous()
+        y = torch.empty(1000000, dtype=torch.float32, device="cuda")
+        for label, prec in (("fp32", host.PREC_FP32), ("tc_fp16x3", host.PREC_TC_FP16X3), ("tc_fp16", host.PREC_TC_FP16)):
+            try:
+                for _ in range(2):
+                    car.forward_tensor(x, prec, out=y)
+                ms = min(timed(torch, lambda: car.forward_tensor(x, prec, out=y), 5, flush))
+                c1[f"batch_1M_{label}"] = {"ms": ms, "queries_per_s": 1e6 / (ms * 1e-3), "tflops": 1e6 * FLOP_PER_QUERY / (ms * 1e-3) / 1e12,
+                                           "hbm_bytes": 16 * 1000000}
+            except capi.NsdfError:
+                pass
+        xh = x.cpu().numpy()
+        yh = car.forward_host(xh[:4096])
+        t0 = time.perf_counter()
+        yh = car.forward_host(xh)
+        c1["batch_1M_fp32_host_buffers"] = {"ms": 1e3 * (time.perf_counter() - t0), "note": "nsdf_mlp_forward_host: H2D 12 MB + kernel + D2H 4 MB"}
+        if args.ref_cuda and os.path.exists(REF_DRIVER):
+            import tempfile
+            with tempfile.TemporaryDirectory() as tmp:
+                px, py = os.path.join(tmp, "x.f32"), os.path.join(tmp, "y.f32")
+                xh.tofile(px)
+                rc = reference_cuda(["mlp", geom("car_1"), px, py, "3"])
+                if rc is not None:
+                    yr = np.fromfile(py, dtype=np.float32)
+                    c1["batch_1M_reference_cuda"] = {"ms": rc["best_ms"], "queries_per_s": rc["queries_per_s"], "first_call_ms": rc["first_call_ms"],
+                                                     "bit_equal_to_product_fp32": bool(np.array_equal(yr.view(np.uint32), yh.view(np.uint32))),
+                                                     "note": "the reference's nn.forward (9 CUTLASS GemmBatched launches) on the same points, same GPU"}
+            rf = reference_cuda_frame(1, model="car_1", w=512, h=512)
+            if rf is not None:
+                c1["frame_512_reference_cuda"] = {"ms_per_frame": rf["mean_ms"], "frames_per_s": 1e3 / rf["mean_ms"]}
+        line_extra["c1"] = c1
+
+    # ---- C3: 256^3 lattice through car_1, points generated in-kernel (variant B), all rungs
     if args.dense:
         nd = host.NeuralNetwork()
-        assert nd.load(os.path.join(ROOT, "data", "neuralGeometries", "car_1.h5"))
+        assert nd.load(geom("car_1"))
         res = 256
         yb = torch.empty(res ** 3, dtype=torch.float32, device="cuda")
         dense = {}
@@ -349,225 +548,124 @@ def run_native(args):
                     nd.forward_lattice(res, out=yb, precision=prec)
             except capi.NsdfError:
                 continue
-            torch.cuda.synchronize()
-            es = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(5)]
-            for a, b in es:
-                flush.zero_()
-                a.record()
-                nd.forward_lattice(res, out=yb, precision=prec)
-                b.record()
-            torch.cuda.synchronize()
-            ms = min(a.elapsed_time(b) for a, b in es)
-            dense[label] = {"queries_per_s": res ** 3 / (ms * 1e-3), "ms": ms,
-                            "tflops": res ** 3 * FLOP_PER_QUERY / (ms * 1e-3) / 1e12}
+            ms = timed(torch, lambda: nd.forward_lattice(res, out=yb, precision=prec), 5, flush)
+            m = sum(ms) / len(ms)
+            dense[label] = {"queries_per_s": res ** 3 / (m * 1e-3), "ms": m, "ms_min": min(ms),
+                            "tflops": res ** 3 * FLOP_PER_QUERY / (m * 1e-3) / 1e12,
+                            "frac_of_tensor_peak": res ** 3 * FLOP_PER_QUERY / (m * 1e-3) / 1e12 / pk["tflops_burst"]}
+        line_extra["dense_256cubed"] = dense
 
-    if world > 1:
-        dist.barrier()
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+    # ---- the reference's own CUDA on the same box, same frame (view 0)
+    if args.ref_cuda:
+        rc = reference_cuda_frame(1)
+        if rc is not None:
+            line_extra["reference_cuda_same_box"] = {"ms_per_frame": rc["mean_ms"], "frames_per_s": 1e3 / rc["mean_ms"],
+                                                     "speedup_view0_device_timed": rc["mean_ms"] / single["ms_per_frame"],
+                                                     "note": "the reference's unmodified CUDA kernels (oracle/_ref/ref_driver), view 0, same GPU"}
 
-    pk = peaks()
-    traffic = None
-    try:   # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, from the committed ncu --set full capture
-        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["trace_coop_kernel"]
-        traffic = tj["dram_bytes_read"] + tj["dram_bytes_write"]
+    # ---- CPU baseline + oracle parity: one full frame (view 0, HEAD scene) through the oracle port on all host threads
+    if not args.no_cpu:
+        dt, r, cores = cpu_oracle_frame()
+        line_extra["cpu_baseline"] = {"value": 1.0 / dt, "unit": "frames/s", "cores": cores, "kind": "port",
+                                      "sample": f"one full {W}x{H} frame (view 0, scene=manySphere, {r['queries']} queries) through "
+                                                "oracle/nsdf_oracle.cpp, all host threads",
+                                      "queries_per_s": r["queries"] / dt}
+        det, img_det = frame_leg(nn, W, H, reps=1, math=host.MATH_DETERMINISTIC)
+        line_extra["parity_vs_oracle"] = {"equal": bool(np.array_equal(img_det, r["image"].reshape(H, W))),
+                                          "queries_equal": bool(det["queries"] == r["queries"]), "queries": det["queries"],
+                                          "note": "the timed frame's view 0 in NSDF_MATH_DETERMINISTIC against the CPU oracle's frame, all pixels"}
+
+    traffic, traffic_note = None, "no capture of the current tracer sources under profiles/ncu_traffic.json"
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if tj.get("tracer_source_sha") == tracer_source_sha():
+            k = tj["trace_coop_kernel"]
+            traffic = k["dram_bytes_read"] + k["dram_bytes_write"]
+            traffic_note = f"dram bytes per launch from the ncu --set full capture {tj.get('capture', '')} of these tracer sources"
+        else:
+            traffic_note = "profiles/ncu_traffic.json was captured from other tracer sources than the ones running: not quoted"
     except Exception:
         pass
-    achieved = q_frame * FLOP_PER_QUERY / (ms_per_step * 1e-3) / 1e12
-    hbm_bytes = 4 * W * H + 4 * hits + nn.getNumWeightParams() * 4 + nn.getNumBiasParams() * 4
+    q_frame = q_set / N_VIEWS
+    achieved = q_set * FLOP_PER_QUERY / (ms_per_step * 1e-3) / 1e12 / world     # per GPU
+    hbm_bytes = 4 * W * H + 4 * hits_set / N_VIEWS + nn.getNumWeightParams() * 4 + nn.getNumBiasParams() * 4
+    ms_per_frame = ms_per_step * world / N_VIEWS
     line = {
-        "metric": "1080p frames/sec (plane_1, FD normals + matcap)", "value": fps, "unit": "frames/s", "n_gpus": world,
-        "steps": K, "warmup": Wm, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{MODEL}.h5 {W}x{H} sphere-traced frame, FD normals + matcap {MATCAP}, scene=tanh, "
-                               f"max_steps={args.max_steps}",
-                   "parallelism": f"views{world}" if world > 1 else "single", "views_per_step": world,
-                   "l2": "256 MiB memset between timed steps (outside the per-step events)",
-                   "precision": "fp32 FFMA rung (bit-exact vs oracle)"},
-        "queries_per_s": q_total * K / (total_ms * 1e-3), "queries_per_frame": q_frame, "hit_pixels": hits,
-        "evicted_rays": evicted,
-        "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
-        "gpu_launches": 3 * K,   # per step: tile_probe_kernel, tile_sort_kernel, trace_coop_kernel (+ one 16-byte memset)
-        "kernels": {"trace_coop_kernel (+ tile_probe_kernel, tile_sort_kernel)": {"ms": ms_per_step, "queries": q_frame},
-                    "two_launch_schedule_ms": t_two},
-        "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved,
-                     "peak": pk["tflops_burst"], "unit": "TFLOP/s", "frac": achieved / pk["tflops_burst"],
-                     "traffic": traffic, "peak_source": pk["source"],
-                     "note": "algorithmic FLOP = queries x 14592 against the measured bf16 tensor peak; this is the bit-exact fp32 FFMA "
-                             "rung, whose own ceiling is 74.4 TFLOP/s (frac_of_fp32_alu below); traffic = DRAM bytes per launch from "
-                             "profiles/ncu_traffic.json (the frame stays in L2 within the launch)",
-                     "frac_of_fp32_alu": achieved / 74.4,
-                     "hbm": {"algorithmic_bytes": hbm_bytes, "achieved_gbs": hbm_bytes / (ms_per_step * 1e-3) / 1e9,
+        "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "parallelism": f"views{world}: view v -> rank v % {world}" if world > 1 else "single",
+                   "frames_per_step": N_VIEWS, "l2": "256 MiB memset between timed steps (outside the per-step events)",
+                   "precision": "fp32 FFMA rung, reference arithmetic order; NSDF_MATH_REFERENCE (rsqrtf / __saturatef as the reference)"},
+        "ms_per_frame_per_gpu": ms_per_frame, "queries_per_s": q_set * K / (total_ms * 1e-3), "queries_per_frame_mean": q_frame,
+        "hit_pixels_per_frame_mean": hits_set / N_VIEWS, "rank_time_min_over_max": min_ms / total_ms if total_ms else None,
+        "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": Ke},
+        "gpu_launches": 3 * N_VIEWS * K,   # per frame: tile_probe_kernel, tile_sort_kernel, trace_coop_kernel (+ one 32-byte memset)
+        "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tflops_burst"],
+                     "unit": "TFLOP/s", "frac": achieved / pk["tflops_burst"], "traffic": traffic, "traffic_note": traffic_note,
+                     "peak_source": pk["source"], "frac_of_fp32_alu": achieved / FP32_ALU_TFLOPS,
+                     "note": "per GPU; algorithmic FLOP = MLP evaluations (counted on the device) x 14592 over the step's device time, against "
+                             "the measured bf16 tensor peak as SURVEY 8(d) prescribes; the kernel is the bit-exact fp32 FFMA rung whose own "
+                             f"ceiling is {FP32_ALU_TFLOPS} TFLOP/s (frac_of_fp32_alu); HBM is not the bound (hbm below)",
+                     "hbm": {"algorithmic_bytes_per_frame": hbm_bytes, "achieved_gbs": hbm_bytes / (ms_per_frame * 1e-3) / 1e9,
                              "peak_gbs": pk["hbm_gbs"]}},
         "clocks": clocks, "wall_s": t_wall,
     }
-    line["head_scene"] = head_scene
-    if mixed:
-        line["mixed_precision"] = mixed
-    if world == 1 and args.ref_cuda:
-        rc = reference_cuda_frame(2)
-        if rc is not None:
-            line["reference_cuda_same_box"] = {"ms_per_frame": rc["mean_ms"], "frames_per_s": 1e3 / rc["mean_ms"],
-                                               "speedup_vs_head_scene": rc["mean_ms"] / t_head,
-                                               "note": "the reference's own unmodified CUDA kernels (oracle/_ref/ref_driver), same frame, "
-                                                       "same GPU, 2 frames after a warm-up"}
-    if dense:
-        line["dense_256cubed"] = dense
-    if world == 1 and not args.no_cpu:
-        dt, q, cores = cpu_oracle_frame()
-        line["cpu_baseline"] = {"value": 1.0 / dt, "unit": "frames/s", "cores": cores, "kind": "port",
-                                "sample": f"one full {W}x{H} frame ({q} queries) through oracle/nsdf_oracle.cpp, all host threads",
-                                "queries_per_s": q / dt}
+    if tiles:
+        line["frame4k_tiles"] = tiles
+    if c5:
+        line["turntable_c5"] = c5
+    line.update(line_extra)
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    D.close()
 
 
 def run_tiles(args):
-    """BASELINE config 4: one 3840x2160 frame of 3a3d4a90....obj.h5, 64x64 tiles round-robin over the ranks,
-    every rank's tracer storing its tiles straight into rank 0's frame buffer over NVLink (peer-mapped d_out).
-    Strong scaling: value = frames/s of the whole job."""
-    import numpy as np
-    import torch
-    import torch.distributed as dist
+    """--workload frame4k_tiles: BASELINE config 4 as the headline of the line (strong scaling over the N GPUs)."""
     from cudaneuralrender_b200 import host, multigpu
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def reduce(x, op):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=op)
-        return float(t.item())
-
-    model, Wt, Ht = "3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160
-    nn = host.NeuralNetwork()
-    assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"))
-    matcap = host.Image()
-    assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
-    host.copyStaticSettings(host.COLOR_MATCAP, 3)
-    host.updateViewMatrices((0.0, 0.0, 0.0), (0.0, 0.0, -2.0), 0)
-    from cudaneuralrender_b200 import _capi as capi
-    mixed = os.environ.get("NSDF_BENCH_TILES_MIXED", "0") == "1"   # opt-in: the mixed-precision tracer on every rank
-    host.setSceneOptions(host.SCENE_TANH, args.max_steps, capi.RENDER_TC_FARFIELD if mixed else 0, 0)
-    frame = multigpu.PeerFrame(Wt, Ht, rank, world, root=0)
-    stats = torch.zeros(6, dtype=torch.int64, device="cuda")
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    K, Wm = args.steps, args.warmup
-
-    for _ in range(Wm):
-        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
-    stats.zero_()
-    multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame, stats=stats)
-    barrier()
-    my_q = float(stats[0].item())
-    q_frame = reduce(my_q, dist.ReduceOp.SUM if world > 1 else None)
-    q_max = reduce(my_q, dist.ReduceOp.MAX if world > 1 else None)
-    hits = reduce(float(stats[1].item()), dist.ReduceOp.SUM if world > 1 else None)
-
-    # parity of the partition: the gathered frame must equal a single-GPU render of the same frame, bytewise
-    equal = None
-    if rank == 0:
-        gathered = frame.to_numpy()
-        single = torch.zeros(Wt * Ht, dtype=torch.int32, device="cuda")
-        host.render_kernel(single, Wt, Ht, nn, matcap)
-        torch.cuda.synchronize()
-        equal = bool(np.array_equal(gathered.ravel(), single.cpu().numpy().view(np.uint32)))
-        if mixed:   # the mixed mode is not schedule-independent bit for bit: report the hit-mask agreement instead
-            equal = bool(np.array_equal(gathered.ravel() != 0, single.cpu().numpy().view(np.uint32) != 0))
-
-    sampler = ClockSampler(local)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    barrier()
-    if rank == 0:
+    D = Dist()
+    flush = D.torch.empty(256 << 20, dtype=D.torch.uint8, device="cuda")
+    sampler = ClockSampler(D.local)
+    if D.rank == 0:
         sampler.start()
-    t0 = time.perf_counter()
-    for i in range(K):
-        flush.zero_()
-        ev[i][0].record()
-        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
-        ev[i][1].record()
-    barrier()
-    wall = time.perf_counter() - t0
-    clocks = sampler.stop() if rank == 0 else None
-    my_ms = sum(a.elapsed_time(b) for a, b in ev)
-    total_ms = reduce(my_ms, dist.ReduceOp.MAX if world > 1 else None)   # a frame is done when its slowest rank is
-    min_ms = reduce(my_ms, dist.ReduceOp.MIN if world > 1 else None)
-
-    # end to end: frame on the HOST of rank 0 every step (render -> barrier -> D2H on the root)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(K):
-        multigpu.render_frame_tiled(nn, matcap, Wt, Ht, frame)
-        barrier()
-        if rank == 0:
-            frame.to_numpy()
-    barrier()
-    e2e_s = reduce(time.perf_counter() - t0, dist.ReduceOp.MAX if world > 1 else None)
-
-    if rank == 0:
+    leg = tiles_leg(D, args, host, multigpu, flush, args.steps)
+    clocks = sampler.stop() if D.rank == 0 else None
+    if D.rank == 0:
         pk = peaks()
-        ms = total_ms / K
-        achieved = q_frame * FLOP_PER_QUERY / (ms * 1e-3) / 1e12
-        line = {"metric": "4K frames/sec (3a3d4a90.obj, FD normals + matcap), tile-partitioned", "value": K / (total_ms * 1e-3),
-                "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": Wm, "ms_per_step": ms, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": f"{model}.h5 {Wt}x{Ht} sphere-traced frame, FD normals + matcap {MATCAP}, scene=tanh, "
-                                       f"max_steps={args.max_steps}",
-                           "parallelism": f"tiles{world}: 64x64 tiles round-robin, peer stores into GPU 0 over NVLink",
-                           "l2": "256 MiB memset between timed steps (outside the per-step events)",
-                           "precision": "mixed: tcgen05 fp16x3 far field + fp32 near surface (hit masks compared)" if mixed
-                                        else "fp32 FFMA rung (bit-exact vs oracle)"},
-                "queries_per_frame": q_frame, "queries_per_s": q_frame * K / (total_ms * 1e-3), "hit_pixels": hits,
-                "tile_balance_queries": q_frame / world / q_max if q_max else None,
-                "rank_time_min_over_max": min_ms / total_ms if total_ms else None,
-                "tiles_equal_single_gpu": equal,
-                "e2e": {"value": K / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": Wt * Ht * 4},
-                "gpu_launches": K * world,
-                "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved,
-                             "peak": pk["tflops_burst"] * world, "unit": "TFLOP/s",
-                             "frac": achieved / (pk["tflops_burst"] * world), "traffic": None, "peak_source": pk["source"],
-                             "note": "whole job; peak = N x one GPU's measured bf16 peak; fp32 ALU rung (own ceiling 74 TFLOP/s per GPU)"},
-                "clocks": clocks, "wall_s": wall}
+        achieved = leg["queries_per_frame"] * FLOP_PER_QUERY / (leg["ms_per_frame"] * 1e-3) / 1e12
+        line = {"metric": "4K frames/sec (3a3d4a90.obj, FD normals + matcap), tile-partitioned", "value": leg["frames_per_s"],
+                "unit": "frames/s", "n_gpus": D.world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": leg["ms_per_frame"],
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": leg["workload"], "l2": "256 MiB memset between timed steps (outside the per-step events)"},
+                "e2e": {"value": leg["e2e_frames_per_s"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 3840 * 2160 * 4},
+                "gpu_launches": 3 * args.steps * D.world,
+                "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tflops_burst"] * D.world,
+                             "unit": "TFLOP/s", "frac": achieved / (pk["tflops_burst"] * D.world), "traffic": None,
+                             "peak_source": pk["source"], "frac_of_fp32_alu": achieved / (FP32_ALU_TFLOPS * D.world)},
+                "clocks": clocks, "frame4k_tiles": leg}
         print(json.dumps(line), flush=True)
-    frame.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    D.close()
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--max-steps", type=int, default=6000, dest="max_steps")
+    ap.add_argument("--e2e-steps", type=int, default=0, dest="e2e_steps", help="0 = as many as --steps")
     ap.add_argument("--no-dense", action="store_false", dest="dense")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-mixed", action="store_false", dest="mixed")
+    ap.add_argument("--no-c1", action="store_false", dest="c1")
+    ap.add_argument("--no-c5", action="store_false", dest="c5")
+    ap.add_argument("--no-tiles", action="store_false", dest="tiles")
     ap.add_argument("--cpu-port", action="store_true", help="--impl reference: time the CPU oracle port even if the reference's "
                                                             "CUDA build (oracle/_ref) is present")
     ap.add_argument("--no-ref-cuda", action="store_false", dest="ref_cuda")
-    ap.add_argument("--workload", default="frame1080", choices=["frame1080", "frame4k_tiles"],
-                    help="frame1080: BASELINE config 2 (default; N>1 = one view per GPU, weak scaling).  "
-                         "frame4k_tiles: BASELINE config 4, ONE 3840x2160 frame tile-partitioned over the N GPUs, "
-                         "gathered on GPU 0 over NVLink (strong scaling)")
+    ap.add_argument("--workload", default="turntable1080", choices=["turntable1080", "frame4k_tiles"],
+                    help="turntable1080: BASELINE config 2 over the fixed 64-view set (default).  frame4k_tiles: BASELINE config 4 "
+                         "alone, ONE 3840x2160 frame tile-partitioned over the N GPUs (also a leg of every default line)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
     args.dense_tc = (("tc_fp16", 1), ("tc_bf16", 2), ("tc_fp16x3", 3), ("tc_fp16_acc16", 5))

@@ -28,10 +28,11 @@ class SceneOp(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("color_type", C.c_int), ("scene", C.c_int), ("max_steps", C.c_int), ("tile_rank", C.c_int),
                 ("tile_world", C.c_int), ("evict_steps", C.c_int), ("flags", C.c_int), ("program", C.POINTER(SceneOp)),
-                ("n_ops", C.c_int)]
+                ("n_ops", C.c_int), ("math", C.c_int)]
 
 
 SCENE_TANH, SCENE_MANYSPHERE, SCENE_PROGRAM = 0, 1, 2
+MATH_REFERENCE, MATH_DETERMINISTIC = 0, 1   # nsdf_render_opts.math
 PRIM_NSDF, PRIM_TANH, PRIM_SPHERE, PRIM_BOX, PRIM_PLANE, PRIM_CYLINDER = range(6)
 MOD_DISPLACE, MOD_ROUND, MOD_ONION, MOD_MANY_SPHERE, MOD_MANY_CYLINDER_CUT = range(16, 21)
 (COMB_SET, COMB_UNION, COMB_INTERSECT, COMB_SUBTRACT, COMB_SUBTRACT_FROM, COMB_SMOOTH_UNION, COMB_SMOOTH_SUBTRACT,
@@ -83,7 +84,7 @@ PROTOTYPES = {
     "nsdf_mlp_forward_lattice": (_i, [_vp, _vp, _i, _f, _f, _i64, _i64, _i, _vp]),
     "nsdf_dense_layer_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "nsdf_render_opts_default": (None, [C.POINTER(RenderOpts)]),
-    "nsdf_scene_eval": (_i, [C.POINTER(SceneOp), _i, _vp, _vp, _i, _vp, _i64, _vp]),
+    "nsdf_scene_eval": (_i, [C.POINTER(SceneOp), _i, _vp, _vp, _i, _i, _vp, _i64, _vp]),
     "nsdf_camera_from_view": (None, [_f, _f, _f, _f, _f, _i, C.POINTER(Camera)]),
     "nsdf_render": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
     "nsdf_render_host": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i,

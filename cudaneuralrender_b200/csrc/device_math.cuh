@@ -6,6 +6,17 @@
 // fused multiply-adds are the explicit fmaf()/fma() below; their placement is the
 // "arithmetic contract" of DESIGN.md (the contraction pattern nvcc -fmad=true produces
 // for the reference's expressions), which makes every result reproducible bit for bit.
+//
+// Two math modes (nsdf_render_opts.math), selected by the warp-uniform `ref` argument:
+//   ref == true   NSDF_MATH_REFERENCE: the three operations the reference's device code takes from
+//                 the SFU / libdevice are taken from the same place -- rsqrtf (rsqrt.approx.f32 =
+//                 MUFU.RSQ with the denormal pre-scale, what helper_math.h:1309-1313 compiles to),
+//                 libdevice tanhf (:229) and __saturatef (:140,146,268-271).  On the GPU family the
+//                 reference binary runs on, frames equal the reference's frames.
+//   ref == false  NSDF_MATH_DETERMINISTIC: IEEE-only forms of the same three, which a CPU can
+//                 reproduce bit for bit -- the mode the oracle tests run in.
+// libdevice's tanhf / sinf / rsqrtf compile to the same SASS under -fmad=false and -fmad=true
+// (checked with cuobjdump), so calling them from this translation unit is exact.
 // =====================================================================================
 #pragma once
 #include <cstdint>
@@ -21,8 +32,9 @@ __device__ __forceinline__ float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a
 // helper_math.h:1309-1313 normalize = v * rsqrtf(dot(v,v)).  MUFU.RSQ is replaced by the
 // correctly rounded 1/sqrt (the header's own host fallback, helper_math.h:62-65).
 __device__ __forceinline__ float rsqrt_det(float x) { return __fdiv_rn(1.0f, __fsqrt_rn(x)); }
-__device__ __forceinline__ f3 normalize3(f3 v) {
-    const float r = rsqrt_det(dot3(v, v));
+__device__ __forceinline__ float rsqrt_sel(float x, bool ref) { return ref ? rsqrtf(x) : rsqrt_det(x); }
+__device__ __forceinline__ f3 normalize3(f3 v, bool ref) {
+    const float r = rsqrt_sel(dot3(v, v), ref);
     return f3{v.x * r, v.y * r, v.z * r};
 }
 
@@ -31,6 +43,7 @@ __device__ __forceinline__ float saturate_det(float x) {
     if (!(x > 0.0f)) return 0.0f;
     return x > 1.0f ? 1.0f : x;
 }
+__device__ __forceinline__ float saturate_sel(float x, bool ref) { return ref ? __saturatef(x) : saturate_det(x); }
 
 // tanh of the network output (volumeRender_kernel.cu:229; simpleInfer.cpp:109).  libdevice
 // tanhf goes through MUFU.EX2/RCP; this polynomial/Cody-Waite form is < 1.5 ulp and uses only
@@ -69,12 +82,18 @@ __device__ __forceinline__ float tanhf_det(float x) {
     if (ax != ax) return x + x;
     return copysignf(r, x);
 }
+__device__ __forceinline__ float tanh_sel(float x, bool ref) { return ref ? tanhf(x) : tanhf_det(x); }
 
 // sdfOpSmoothUnion (volumeRender_kernel.cu:144-149) with its double promotions.
-__device__ __forceinline__ float smooth_union(float d1, float d2, float k) {
+// Outside the blend band the double arithmetic collapses exactly: d2 - d1 >= k gives h == 1 and the value d1, d2 - d1 <= -k
+// gives h == 0 and the value d2 (every product with the zero weight is a signed zero that the final roundings absorb, which
+// is why zero operands and non-finite differences take the long way).  Same bits, no division on the march's critical path.
+__device__ __forceinline__ float smooth_union(float d1, float d2, float k, bool ref) {
     const float diff = d2 - d1;
+    if (diff >= k && diff <= 1.0e30f && d1 != 0.0f) return d1;
+    if (diff <= -k && diff >= -1.0e30f && d2 != 0.0f) return d2;
     const double hd = __dadd_rn(__ddiv_rn(__dmul_rn((double)diff, 0.5), (double)k), 0.5);
-    const float h = saturate_det((float)hd);
+    const float h = saturate_sel((float)hd, ref);
     const double omh = __dsub_rn(1.0, (double)h);
     const float d1h = d1 * h;
     const float mix = (float)fma(omh, (double)d2, (double)d1h);
@@ -83,34 +102,58 @@ __device__ __forceinline__ float smooth_union(float d1, float d2, float k) {
 }
 
 // manySphere(p, nSDF, true) (volumeRender_kernel.cu:176-196): what sceneSDF (:217-222)
-// evaluates at the reference's HEAD.
-__device__ __forceinline__ float many_sphere_union(f3 p, float nsdf, int frame) {
-    float s = nsdf;
+// evaluates at the reference's HEAD.  The nine sphere distances depend on the point alone, so they are computed first (nine
+// independent square roots instead of a serial loop) and their minimum decides, with one compare, whether the whole chain of
+// smooth unions is the identity on nSDF (every union then takes smooth_union's d2 - d1 >= k exit; rounding is monotonic, so
+// fl(d_i - s) >= fl(dmin - s)).  A marching warp can take the minimum before the network answers (many_sphere_dmin).
+__device__ __forceinline__ void many_sphere_dists(f3 p, int frame, float (&d)[9]) {
     float cx = p.x;
     float cy = (float)__dsub_rn((double)p.y, 0.6);
     const double zoff = __dadd_rn(-0.7, __ddiv_rn(__dmul_rn((double)(frame * 2), 0.7), 360.0));
     const float cz = (float)__dadd_rn((double)p.z, zoff);
     const float zz = cz * cz;
-#pragma unroll 1
+#pragma unroll
     for (int i = 0; i < 9; ++i) {
         if (i % 3 == 0) {
             cy = (float)__dadd_rn((double)cy, 0.4);
             cx = p.x + 0.5f;
         }
         const float len2 = zz + fmaf(cx, cx, cy * cy);
-        const float d = __fsqrt_rn(len2) + (-0.1f);
-        s = smooth_union(s, d, 0.01f);
+        d[i] = __fsqrt_rn(len2) + (-0.1f);
         cx = (float)__dsub_rn((double)cx, 0.4);
     }
+}
+__device__ __forceinline__ float many_sphere_dmin(f3 p, int frame) {
+    float d[9];
+    many_sphere_dists(p, frame, d);
+    float m = d[0];
+#pragma unroll
+    for (int i = 1; i < 9; ++i) m = fminf(m, d[i]);   // a NaN distance yields a NaN-free minimum that can only be too small
+    return (d[0] == d[0] && d[1] == d[1] && d[2] == d[2] && d[3] == d[3] && d[4] == d[4] && d[5] == d[5] && d[6] == d[6] &&
+            d[7] == d[7] && d[8] == d[8]) ? m : -3.0e38f;
+}
+__device__ __forceinline__ float many_sphere_union(f3 p, float nsdf, int frame, bool ref, float dmin) {
+    const float k = 0.01f;
+    const float gap = dmin - nsdf;
+    if (gap >= k && gap <= 1.0e30f && nsdf != 0.0f) return nsdf;
+    float d[9];
+    many_sphere_dists(p, frame, d);
+    float s = nsdf;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) s = smooth_union(s, d[i], k, ref);
     return s;
 }
 
 enum { SCENE_TANH = 0, SCENE_MANYSPHERE = 1 };
 
+// The part of sceneSDF that depends on the point alone (nothing for the tanh scene).
+__device__ __forceinline__ float scene_pre(int scene, f3 p, int frame) {
+    return scene == SCENE_MANYSPHERE ? many_sphere_dmin(p, frame) : 0.0f;
+}
 // sceneSDF (volumeRender_kernel.cu:217-230): scene 1 = HEAD, scene 0 = `tanh(nSDF)` (:229).
-__device__ __forceinline__ float scene_sdf(int scene, f3 p, float nsdf, int frame) {
-    if (scene == SCENE_MANYSPHERE) return many_sphere_union(p, nsdf, frame);
-    return tanhf_det(nsdf);
+__device__ __forceinline__ float scene_sdf(int scene, f3 p, float nsdf, int frame, bool ref, float pre) {
+    if (scene == SCENE_MANYSPHERE) return many_sphere_union(p, nsdf, frame, ref, pre);
+    return tanh_sel(nsdf, ref);
 }
 
 #define NSDF_NORMAL_EPSILON 0.00001f     // volumeRender_kernel.cu:59
@@ -140,7 +183,7 @@ struct Camera {
 struct RayInit { f3 o, d, p; float tfar; bool hit; };
 
 // initMarcher (volumeRender_kernel.cu:293-358) + intersectSphere (:200-215), sphere (0, 1.2).
-__device__ __forceinline__ RayInit init_ray(const Camera& c, int x, int y, int W, int H) {
+__device__ __forceinline__ RayInit init_ray(const Camera& c, int x, int y, int W, int H, bool ref) {
     RayInit r;
     const float u = fmaf(__fdiv_rn((float)x, (float)W), 2.0f, -1.0f);
     const float v = fmaf(__fdiv_rn((float)y, (float)H), 2.0f, -1.0f);
@@ -148,7 +191,7 @@ __device__ __forceinline__ RayInit init_ray(const Camera& c, int x, int y, int W
     r.o = f3{M[3] + fmaf(M[2], 0.0f, fmaf(M[0], 0.0f, M[1] * 0.0f)),
              M[7] + fmaf(M[6], 0.0f, fmaf(M[4], 0.0f, M[5] * 0.0f)),
              M[11] + fmaf(M[10], 0.0f, fmaf(M[8], 0.0f, M[9] * 0.0f))};
-    const float rs = rsqrt_det(fmaf(u, u, v * v) + 4.0f);
+    const float rs = rsqrt_sel(fmaf(u, u, v * v) + 4.0f, ref);
     const f3 d0{u * rs, v * rs, rs * -2.0f};
     r.d = f3{dot3(d0, f3{M[0], M[1], M[2]}), dot3(d0, f3{M[4], M[5], M[6]}), dot3(d0, f3{M[8], M[9], M[10]})};
     const float a = dot3(r.d, r.d);
@@ -170,25 +213,25 @@ __device__ __forceinline__ RayInit init_ray(const Camera& c, int x, int y, int W
 }
 
 // rgbaFloatToInt (volumeRender_kernel.cu:266-274)
-__device__ __forceinline__ uint32_t rgba_float_to_int(float r, float g, float b, float a) {
-    r = saturate_det(r); g = saturate_det(g); b = saturate_det(b); a = saturate_det(a);
+__device__ __forceinline__ uint32_t rgba_float_to_int(float r, float g, float b, float a, bool ref) {
+    r = saturate_sel(r, ref); g = saturate_sel(g, ref); b = saturate_sel(b, ref); a = saturate_sel(a, ref);
     return (f2u_rz(a * 255.0f) << 24) | (f2u_rz(b * 255.0f) << 16) | (f2u_rz(g * 255.0f) << 8) | f2u_rz(r * 255.0f);
 }
 
 // facingColor (volumeRender_kernel.cu:380-384)
-__device__ __forceinline__ uint32_t facing_color(f3 n, f3 ray) {
+__device__ __forceinline__ uint32_t facing_color(f3 n, f3 ray, bool ref) {
     float t = ray.x * n.x;
     t = fmaf(-ray.y, n.y, -t);
     t = fmaf(-ray.z, n.z, t);
     double rd = (double)t;
     rd = (rd > 0.0) ? rd : 0.0;
     const float ratio = (float)rd;
-    return rgba_float_to_int(ratio, ratio, ratio, 1.0f);
+    return rgba_float_to_int(ratio, ratio, ratio, 1.0f, ref);
 }
 
 // matCapColor (volumeRender_kernel.cu:387-413): nearest texel, truncating, texel returned as is.
 __device__ __forceinline__ uint32_t matcap_color(const Camera& c, f3 n, const uint32_t* __restrict__ matcap, int mw,
-                                                 int mh) {
+                                                 int mh, bool ref) {
     const float* N = c.normal;
     float e[3];
 #pragma unroll
@@ -200,7 +243,7 @@ __device__ __forceinline__ uint32_t matcap_color(const Camera& c, f3 n, const ui
         t = fmaf(row[3], 0.0f, t);
         e[i] = t;
     }
-    const f3 ne = normalize3(f3{e[0], e[1], e[2]});
+    const f3 ne = normalize3(f3{e[0], e[1], e[2]}, ref);
     const float fu = (float)fma((double)ne.x, 0.5, 0.5);
     const float fv = (float)fma((double)ne.y, 0.5, 0.5);
     const int ux = f2i_rz(fu * (float)(mw - 1));
@@ -211,13 +254,13 @@ __device__ __forceinline__ uint32_t matcap_color(const Camera& c, f3 n, const ui
 }
 
 // surfaceNormal (volumeRender_kernel.cu:361-377): p0+p1+p2+p3 as contracted by nvcc.
-__device__ __forceinline__ f3 tet_normal(const float (&s)[4]) {
+__device__ __forceinline__ f3 tet_normal(const float (&s)[4], bool ref) {
     f3 nn;
     const f3 t0 = tet_vertex(0), t1 = tet_vertex(1), t2 = tet_vertex(2), t3 = tet_vertex(3);
     nn.x = fmaf(t3.x, s[3], fmaf(t2.x, s[2], fmaf(t0.x, s[0], t1.x * s[1])));
     nn.y = fmaf(t3.y, s[3], fmaf(t2.y, s[2], fmaf(t0.y, s[0], t1.y * s[1])));
     nn.z = fmaf(t3.z, s[3], fmaf(t2.z, s[2], fmaf(t0.z, s[0], t1.z * s[1])));
-    return normalize3(nn);
+    return normalize3(nn, ref);
 }
 
 }  // namespace nsdf

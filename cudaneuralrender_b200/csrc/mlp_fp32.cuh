@@ -361,6 +361,79 @@ __device__ __forceinline__ void mlp32_eval_warp(const float* __restrict__ sw, in
     __syncwarp();   // abuf may be rewritten by the caller's next evaluation
 }
 
+// ---- one point per warp, latency form ---------------------------------------------------------------
+// The serial tail of a frame is ONE ray's chain of dependent evaluations, so what counts here is the
+// latency of a single evaluation, whose floor is the dependent FFMA chain 3 + n_sq*32 + 32 (4 clocks each).
+// mlp32_eval_warp<1> pays ~140 clocks per layer on top of the 128-clock chain: its 32 weight loads are issued after the
+// __syncwarp() that publishes the previous layer (a barrier orders memory operations, so the compiler cannot hoist them),
+// then wait out the shared-memory latency before the chain can start.  Weights do not depend on activations: here lane o
+// loads the column W[o][0..31] of layer l+1 into registers BEFORE layer l's chain (two register buffers, layers unrolled
+// in pairs), so that after the barrier only the eight activation loads stand between one chain and the next; the last
+// layer's weights are fetched the same way.  Same arithmetic, same bits (ascending-k fmaf chain from 0, + bias, relu).
+// x is warp-uniform, the result is returned in every lane.  abuf: 2 * WARP_ACT_STRIDE floats of per-warp scratch.
+__device__ __forceinline__ void lone_load_col(const float* __restrict__ Wt, int lane, float (&w)[32], float& bias) {
+#pragma unroll
+    for (int k = 0; k < 32; ++k) w[k] = Wt[k * 32 + lane];
+    bias = Wt[1024 + lane];
+}
+__device__ __forceinline__ void lone_load_last(const float* __restrict__ LL, float (&w)[32], float& bias) {
+#pragma unroll
+    for (int kc = 0; kc < 8; ++kc) {
+        const float4 v = *reinterpret_cast<const float4*>(LL + 4 * kc);
+        w[4 * kc + 0] = v.x; w[4 * kc + 1] = v.y; w[4 * kc + 2] = v.z; w[4 * kc + 3] = v.w;
+    }
+    bias = LL[32];
+}
+__device__ __forceinline__ float lone_chain(const float (&w)[32], const float* __restrict__ act) {
+    float acc = 0.0f;
+#pragma unroll
+    for (int kc = 0; kc < 8; ++kc) {
+        const float4 av = *reinterpret_cast<const float4*>(act + 4 * kc);
+        acc = fmaf(w[4 * kc + 0], av.x, acc);
+        acc = fmaf(w[4 * kc + 1], av.y, acc);
+        acc = fmaf(w[4 * kc + 2], av.z, acc);
+        acc = fmaf(w[4 * kc + 3], av.w, acc);
+    }
+    return acc;
+}
+__device__ __forceinline__ float mlp32_eval_lone(const float* __restrict__ sw, int n_sq, float* __restrict__ abuf, float x0,
+                                                 float x1, float x2, int lane, float t4 = 0.0f, bool in4 = false) {
+    float* cur = abuf;
+    float* nxt = abuf + WARP_ACT_STRIDE;
+    float wA[32], wB[32], bA, bB;
+    const float* H = sw + FUSED_L0_FLOATS;
+    const float* LL = H + n_sq * FUSED_SQ_FLOATS;
+    {
+        const float w0 = sw[lane], w1 = sw[32 + lane], w2 = sw[64 + lane], bb = sw[128 + lane];
+        if (n_sq > 0) lone_load_col(H, lane, wA, bA); else lone_load_last(LL, wA, bA);
+        float c = fmaf(w2, x2, fmaf(w1, x1, fmaf(w0, x0, 0.0f)));
+        if (in4) c = fmaf(sw[96 + lane], t4, c);
+        cur[lane] = relu_det(c + bb);
+    }
+    __syncwarp();
+    int l = 0;
+#pragma unroll 1
+    for (; l + 1 < n_sq; l += 2) {
+        lone_load_col(H + (l + 1) * FUSED_SQ_FLOATS, lane, wB, bB);
+        nxt[lane] = relu_det(lone_chain(wA, cur) + bA);
+        __syncwarp();
+        if (l + 2 < n_sq) lone_load_col(H + (l + 2) * FUSED_SQ_FLOATS, lane, wA, bA); else lone_load_last(LL, wA, bA);
+        cur[lane] = relu_det(lone_chain(wB, nxt) + bB);
+        __syncwarp();
+    }
+    float out;
+    if (l < n_sq) {   // odd number of hidden layers: wA holds the last hidden one
+        lone_load_last(LL, wB, bB);
+        nxt[lane] = relu_det(lone_chain(wA, cur) + bA);
+        __syncwarp();
+        out = lone_chain(wB, nxt) + bB;
+    } else {
+        out = lone_chain(wA, cur) + bA;
+    }
+    __syncwarp();   // abuf may be rewritten by the caller's next evaluation
+    return out;
+}
+
 // ---- warp-cooperative evaluator, 16 points, register-tiled ------------------------------------------
 // One warp evaluates 16 points; lane = (g = lane & 7, rg = lane >> 3) owns the 4 x 4 tile
 // {neurons 4g..4g+3} x {points rg, rg+4, rg+8, rg+12}.  A hidden layer is still a 32-deep FFMA chain per output

@@ -392,7 +392,7 @@ int nsdf_dense_layer_forward(const float* d_W, const float* d_A, float* d_Z, con
 void nsdf_render_opts_default(nsdf_render_opts* o) {
     if (!o) return;
     o->color_type = NSDF_COLOR_FACING;
-    o->scene = NSDF_SCENE_TANH;
+    o->scene = NSDF_SCENE_MANYSPHERE;   // what sceneSDF returns at the reference's HEAD (src/volumeRender_kernel.cu:221)
     o->max_steps = 6000;
     o->tile_rank = 0;
     o->tile_world = 1;
@@ -400,12 +400,14 @@ void nsdf_render_opts_default(nsdf_render_opts* o) {
     o->flags = 0;
     o->program = nullptr;
     o->n_ops = 0;
+    o->math = NSDF_MATH_REFERENCE;
 }
 
-int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,
                     float* d_out, int64_t n, void* stream) {
     if (n < 0 || (n > 0 && (!d_xyz || !d_nsdf || !d_out))) return NSDF_EINVAL;
-    return nsdf::scene_eval_launch(program, n_ops, d_xyz, d_nsdf, frame, d_out, n, (cudaStream_t)stream);
+    if (math != NSDF_MATH_REFERENCE && math != NSDF_MATH_DETERMINISTIC) return NSDF_EINVAL;
+    return nsdf::scene_eval_launch(program, n_ops, d_xyz, d_nsdf, frame, math, d_out, n, (cudaStream_t)stream);
 }
 
 // updateViewMatrices, src/main.cpp:207-222.  Eigen composes AngleAxis(-rx, X) * AngleAxis(-ry, Y)

@@ -54,7 +54,7 @@ int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const flo
                        int64_t num_batches, int activation, cudaStream_t stream);
 
 // renderer (nsdf_render.cu)
-int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,
                       float* d_out, int64_t n, cudaStream_t stream);
 int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,

@@ -94,20 +94,21 @@ int scene_program_pack(const nsdf_scene_op* program, int n_ops, SceneProgram* ou
 }
 
 __global__ void __launch_bounds__(256) scene_eval_kernel(const __grid_constant__ SceneProgram prog, const float* __restrict__ xyz,
-                                                         const float* __restrict__ nsdf, int frame, float* __restrict__ out,
-                                                         int64_t n) {
+                                                         const float* __restrict__ nsdf, int frame, int refmath,
+                                                         float* __restrict__ out, int64_t n) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = scene_program_eval(prog, f3{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}, nsdf[i], frame);
+    out[i] = scene_program_eval(prog, f3{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}, nsdf[i], frame, refmath != 0);
 }
 
-int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,
                       float* d_out, int64_t n, cudaStream_t stream) {
     SceneProgram prog;
     const int rc = scene_program_pack(program, n_ops, &prog);
     if (rc) return rc;
     if (n <= 0) return NSDF_OK;
-    scene_eval_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, stream>>>(prog, d_xyz, d_nsdf, frame, d_out, n);
+    scene_eval_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, stream>>>(prog, d_xyz, d_nsdf, frame,
+                                                                           math == NSDF_MATH_REFERENCE ? 1 : 0, d_out, n);
     return (int)cudaGetLastError();
 }
 
@@ -168,6 +169,8 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.pop_max = env_int("NSDF_COOP_POP_MAX", 0);
     rp.n_in = m->in[0];
     rp.t4 = (float)cam->frame;
+    if (opts->math != NSDF_MATH_REFERENCE && opts->math != NSDF_MATH_DETERMINISTIC) return NSDF_EINVAL;
+    rp.refmath = opts->math == NSDF_MATH_REFERENCE ? 1 : 0;
     rp.tile_order = nullptr;
     rp.stats = d_stats;
 

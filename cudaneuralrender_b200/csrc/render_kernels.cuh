@@ -80,6 +80,8 @@ struct RenderParams {
     SceneProgram prog;             // scene == NSDF_SCENE_PROGRAM: the op list (scene_program.cuh)
     int n_in;                      // network inputs: 3 (x, y, z) or 4 (x, y, z, t) -- animation nets, volumeRender_kernel.cu:524-545
     float t4;                      // the fourth input of every query of this call: (float)frame number (c_frameNumber)
+    int refmath;                   // nsdf_render_opts.math == NSDF_MATH_REFERENCE: rsqrtf / libdevice tanhf / __saturatef as the
+                                   // reference's device code calls them (device_math.cuh); 0 = the IEEE-only forms the oracle restates
     int hybrid;                    // trace_coop_kernel: producing warps march one ray per LANE (mlp32_eval_thread, 32 rays per warp,
                                    // a third of the shared-memory wavefronts per query) and hand rays that reach evict_steps_hi
                                    // steps to the cooperative consumers on the quiet SMs; out of pixels they become consumers
@@ -87,9 +89,16 @@ struct RenderParams {
 };
 
 // sceneSDF (volumeRender_kernel.cu:217-230) of this call: one of the two compiled scenes, or the op list
+// scene_pre_eval is the part that depends on the point alone: a marching warp takes it while the network is still evaluating.
+__device__ __forceinline__ float scene_pre_eval(const RenderParams& rp, f3 p) {
+    return scene_pre(rp.scene, p, rp.cam.frame);
+}
+__device__ __forceinline__ float scene_eval(const RenderParams& rp, f3 p, float nsdf, float pre) {
+    if (rp.scene == NSDF_SCENE_PROGRAM) return scene_program_eval(rp.prog, p, nsdf, rp.cam.frame, rp.refmath != 0);
+    return scene_sdf(rp.scene, p, nsdf, rp.cam.frame, rp.refmath != 0, pre);
+}
 __device__ __forceinline__ float scene_eval(const RenderParams& rp, f3 p, float nsdf) {
-    if (rp.scene == NSDF_SCENE_PROGRAM) return scene_program_eval(rp.prog, p, nsdf, rp.cam.frame);
-    return scene_sdf(rp.scene, p, nsdf, rp.cam.frame);
+    return scene_eval(rp, p, nsdf, scene_pre_eval(rp, p));
 }
 
 struct RaySlot {
@@ -124,25 +133,25 @@ __device__ __forceinline__ f3 slot_query_point(const RaySlot& s) {
 // singleMarch (volumeRender_kernel.cu:416-477) for one slot whose request returned `nsdf`.
 __device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const RenderParams& rp, LocalStats& st) {
     ++st.queries;
+#ifdef NSDF_DEBUG_TSCALE   // development: every ray crawls and runs to max_steps (per-step latency probe)
+    const float sv = s.mode > 0 ? scene_eval(rp, q, nsdf) : scene_eval(rp, q, nsdf) * NSDF_DEBUG_TSCALE + 2e-6f;
+#else
+    const float sv = scene_eval(rp, q, nsdf);   // q == s.p while marching
+#endif
     if (s.mode > 0) {
-        const float sv = scene_eval(rp, q, nsdf);
         if (s.mode == 1) s.s0 = sv;
         else if (s.mode == 2) s.s1 = sv;
         else if (s.mode == 3) s.s2 = sv;
         if (s.mode < 4) { ++s.mode; return; }
         const float sarr[4] = {s.s0, s.s1, s.s2, sv};
-        const f3 n = tet_normal(sarr);
-        rp.out[s.pix] = (rp.color_type == NSDF_COLOR_FACING) ? facing_color(n, s.d)
-                                                             : matcap_color(rp.cam, n, rp.matcap, rp.mw, rp.mh);
+        const f3 n = tet_normal(sarr, rp.refmath != 0);
+        rp.out[s.pix] = (rp.color_type == NSDF_COLOR_FACING) ? facing_color(n, s.d, rp.refmath != 0)
+                                                             : matcap_color(rp.cam, n, rp.matcap, rp.mw, rp.mh, rp.refmath != 0);
         ++st.hits;
         s.mode = -1;
         return;
     }
-#ifdef NSDF_DEBUG_TSCALE   // development: every ray crawls and runs to max_steps (per-step latency probe)
-    const float t = scene_eval(rp, s.p, nsdf) * NSDF_DEBUG_TSCALE + 2e-6f;
-#else
-    const float t = scene_eval(rp, s.p, nsdf);
-#endif
+    const float t = sv;
     s.tfar = s.tfar - t;
     ++s.steps;
     if (s.tfar <= 0.0f) {             // left the march budget: background (:463-467)
@@ -166,7 +175,7 @@ __device__ __forceinline__ void slot_start(RaySlot& s, unsigned int idx, const R
     s.mode = -1;
     if (!decode_pixel(rp, idx, x, y)) return;
     ++st.pixels;
-    const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H);
+    const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H, rp.refmath != 0);
     const int pix = y * rp.W + x;
     if (!r.hit || rp.max_steps <= 0) { rp.out[pix] = 0u; return; }
     ++st.rays;

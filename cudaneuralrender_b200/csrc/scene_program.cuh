@@ -50,10 +50,14 @@ __device__ __forceinline__ float sinf_det(float x) {
 }
 
 // sdfOpSmoothSubtraction (volumeRender_kernel.cu:138-142) with its double promotions.
-__device__ __forceinline__ float smooth_subtract(float d1, float d2, float k) {
+// Outside the blend band it collapses exactly like smooth_union: d1 + d2 >= k gives h == 0 and the value d1, d1 + d2 <= -k gives
+// h == 1 and the value -d2 (manyCylinderCut applies 300 of these per query; almost all take one of the two exits).
+__device__ __forceinline__ float smooth_subtract(float d1, float d2, float k, bool ref) {
     const float sum = d1 + d2;
+    if (sum >= k && sum <= 1.0e30f && d1 != 0.0f && fabsf(d2) <= 1.0e30f) return d1;
+    if (sum <= -k && sum >= -1.0e30f && d2 != 0.0f && fabsf(d1) <= 1.0e30f) return -d2;
     const double hd = __dsub_rn(0.5, __ddiv_rn(__dmul_rn((double)sum, 0.5), (double)k));
-    const float h = saturate_det((float)hd);
+    const float h = saturate_sel((float)hd, ref);
     const double omh = __dsub_rn(1.0, (double)h);
     const float d2h = d2 * h;
     const float mix = (float)fma(omh, (double)d1, -(double)d2h);
@@ -79,8 +83,8 @@ __device__ __forceinline__ float sdf_cylinder(f3 p, f3 c) {
 }
 
 // manySphere(p, nSDF, doUnion) (:176-196); the union form is many_sphere_union of device_math.cuh, bit for bit.
-__device__ __forceinline__ float many_sphere(f3 p, float nsdf, int frame, bool do_union) {
-    if (do_union) return many_sphere_union(p, nsdf, frame);
+__device__ __forceinline__ float many_sphere(f3 p, float nsdf, int frame, bool do_union, bool ref) {
+    if (do_union) return many_sphere_union(p, nsdf, frame, ref, many_sphere_dmin(p, frame));
     float s = nsdf;
     float cx = p.x;
     float cy = (float)__dsub_rn((double)p.y, 0.6);
@@ -95,14 +99,14 @@ __device__ __forceinline__ float many_sphere(f3 p, float nsdf, int frame, bool d
         }
         const float len2 = zz + fmaf(cx, cx, cy * cy);
         const float d = __fsqrt_rn(len2) + (-0.1f);
-        s = smooth_subtract(s, d, 0.01f);
+        s = smooth_subtract(s, d, 0.01f, ref);
         cx = (float)__dsub_rn((double)cx, 0.4);
     }
     return s;
 }
 
 // manyCylinderCut (:156-174): 300 cylinders of radius 0.02 carved out smoothly, 15 rows of 20
-__device__ __forceinline__ float many_cylinder_cut(f3 p, float nsdf) {
+__device__ __forceinline__ float many_cylinder_cut(f3 p, float nsdf, bool ref) {
     float s = nsdf;
     const f3 c = f3{0.02f, 0.02f, 0.02f};
     f3 cp = p;
@@ -113,13 +117,17 @@ __device__ __forceinline__ float many_cylinder_cut(f3 p, float nsdf) {
             cp.y = (float)__dadd_rn((double)cp.y, 0.1);
             cp.x = (float)__dadd_rn((double)p.x, 0.9);
         }
-        s = smooth_subtract(s, sdf_cylinder(cp, c), 0.01f);
+        // sdfCylinder as nvcc contracts it inside this loop of the reference (ref_sdf_probe SASS: FMUL dx,dx ; FFMA dy,dy,.):
+        // fma(dy, dy, dx*dx), not the stand-alone function's fma(dx, dx, dy*dy)
+        const float dx = cp.x - c.x, dy = cp.y - c.z;
+        const float cyl = __fsqrt_rn(fmaf(dy, dy, dx * dx)) - c.y;
+        s = smooth_subtract(s, cyl, 0.01f, ref);
         cp.x = (float)__dsub_rn((double)cp.x, 0.1);
     }
     return s;
 }
 
-__device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p, float nsdf, int frame) {
+__device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p, float nsdf, int frame, bool ref) {
     float s = 0.0f;
     const int n = prog.n_ops < SCENE_MAX_OPS ? prog.n_ops : SCENE_MAX_OPS;
 #pragma unroll 1
@@ -129,14 +137,18 @@ __device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p,
         if (op.prim >= MOD_DISPLACE) {
             switch (op.prim) {
                 case MOD_DISPLACE: {
-                    const float w = (sinf_det(a[0] * p.x) * sinf_det(a[0] * p.y)) * sinf_det(a[0] * p.z);
-                    s = (float)fma((double)w, (double)a[1], (double)s);
+                    const float sx = ref ? sinf(a[0] * p.x) : sinf_det(a[0] * p.x), sy = ref ? sinf(a[0] * p.y) : sinf_det(a[0] * p.y),
+                                sz = ref ? sinf(a[0] * p.z) : sinf_det(a[0] * p.z);
+                    const float w = (sx * sy) * sz;
+                    // the reference's amplitude is the DOUBLE literal 0.05 (:107); a float parameter equal to 0.05f means that literal
+                    const double amp = a[1] == 0.05f ? 0.05 : (double)a[1];
+                    s = (float)fma((double)w, amp, (double)s);
                     break;
                 }
                 case MOD_ROUND: s = s - a[0]; break;
                 case MOD_ONION: s = fabsf(s) - a[0]; break;
-                case MOD_MANY_SPHERE: s = many_sphere(p, s, frame, a[0] != 0.0f); break;
-                case MOD_MANY_CYLINDER_CUT: s = many_cylinder_cut(p, s); break;
+                case MOD_MANY_SPHERE: s = many_sphere(p, s, frame, a[0] != 0.0f, ref); break;
+                case MOD_MANY_CYLINDER_CUT: s = many_cylinder_cut(p, s, ref); break;
                 default: break;
             }
             continue;
@@ -145,7 +157,7 @@ __device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p,
         const f3 q = f3{p.x - a[0], p.y - a[1], p.z - a[2]};
         switch (op.prim) {
             case PRIM_NSDF: d = nsdf; break;
-            case PRIM_TANH: d = tanhf_det(nsdf); break;
+            case PRIM_TANH: d = tanh_sel(nsdf, ref); break;
             case PRIM_SPHERE: d = length3_det(q) - a[3]; break;
             case PRIM_BOX: d = sdf_box(q, f3{a[3], a[4], a[5]}, a[6]); break;
             case PRIM_PLANE: d = p.y - a[0]; break;
@@ -157,9 +169,9 @@ __device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p,
             case COMB_INTERSECT: s = max_det(s, d); break;
             case COMB_SUBTRACT: s = max_det(s, -d); break;
             case COMB_SUBTRACT_FROM: s = max_det(d, -s); break;
-            case COMB_SMOOTH_UNION: s = smooth_union(s, d, a[7]); break;
-            case COMB_SMOOTH_SUBTRACT: s = smooth_subtract(s, d, a[7]); break;
-            case COMB_SMOOTH_SUBTRACT_FROM: s = smooth_subtract(d, s, a[7]); break;
+            case COMB_SMOOTH_UNION: s = smooth_union(s, d, a[7], ref); break;
+            case COMB_SMOOTH_SUBTRACT: s = smooth_subtract(s, d, a[7], ref); break;
+            case COMB_SMOOTH_SUBTRACT_FROM: s = smooth_subtract(d, s, a[7], ref); break;
             default: s = d; break;
         }
     }

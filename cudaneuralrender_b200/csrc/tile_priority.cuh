@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__
         const int x = tx * TILE + (s % (TILE / PROBE_STRIDE)) * PROBE_STRIDE + PROBE_STRIDE / 2 - 1;
         const int y = ty * TILE + (s / (TILE / PROBE_STRIDE)) * PROBE_STRIDE + PROBE_STRIDE / 2 - 1;
         if (x < rp.W && y < rp.H) {
-            const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H);
+            const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H, rp.refmath != 0);
             if (r.hit) { marching = true; p = r.p; d = r.d; tfar = r.tfar; }
         }
     }

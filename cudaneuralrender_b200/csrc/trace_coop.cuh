@@ -88,14 +88,14 @@ __device__ __forceinline__ void lone_ray_march(RaySlot& slot, int owner, const f
     unsigned int q = 0;
 #pragma unroll 1
     for (int it = 0; it < max_iter; ++it) {
-        const float x[1][3] = {{p.x, p.y, p.z}};
         float y[1];
-        mlp32_eval_warp<1>(s_w, n_sq, abuf, x, y, lane, rp.t4, rp.n_in == 4);
+        const float pre = scene_pre_eval(rp, p);   // point-only part of sceneSDF: off the dependent chain
+        y[0] = mlp32_eval_lone(s_w, n_sq, abuf, p.x, p.y, p.z, lane, rp.t4, rp.n_in == 4);
         ++q;
 #ifdef NSDF_DEBUG_TSCALE
-        const float t = scene_eval(rp, p, y[0]) * NSDF_DEBUG_TSCALE + 2e-6f;
+        const float t = scene_eval(rp, p, y[0], pre) * NSDF_DEBUG_TSCALE + 2e-6f;
 #else
-        const float t = scene_eval(rp, p, y[0]);
+        const float t = scene_eval(rp, p, y[0], pre);
 #endif
         tfar = tfar - t;
         ++steps;

@@ -19,7 +19,8 @@ import torch
 
 from . import _capi as capi
 from ._capi import (ACT_RELU, ACT_TANH_LINEAR, COLOR_FACING, COLOR_MATCAP, PREC_FP32, PREC_FP32_WARP, PREC_TC_BF16,
-                    PREC_TC_FP16, PREC_TC_FP16_ACC16, PREC_TC_FP16X3, SCENE_MANYSPHERE, SCENE_PROGRAM, SCENE_TANH, Camera, RenderOpts, RenderStats)
+                    PREC_TC_FP16, PREC_TC_FP16_ACC16, PREC_TC_FP16X3, SCENE_MANYSPHERE, SCENE_PROGRAM, SCENE_TANH, MATH_REFERENCE,
+                    MATH_DETERMINISTIC, Camera, RenderOpts, RenderStats)
 
 ReLU, Tanh = ACT_RELU, ACT_TANH_LINEAR  # enum Activation, src/layers/denseLayer.hh:6-9
 
@@ -355,15 +356,19 @@ def write_keras_h5(path: str, layers) -> None:
 
 # ---- renderer: the three extern "C" entry points of src/volumeRender_kernel.cu ------------------
 class _RenderState:
+    """What the reference keeps in __constant__ symbols and compile-time constants.  Starts as nsdf_render_opts_default does:
+    the reference's HEAD build (sceneSDF = manySphere, reference math)."""
+
     def __init__(self):
         self.cam = Camera()
         self.color_type = COLOR_FACING
         self.num_inputs = 3
-        self.scene = SCENE_TANH
+        self.scene = SCENE_MANYSPHERE
         self.program = None     # (SceneOp * n) for SCENE_PROGRAM
         self.max_steps = 6000
         self.flags = 0
         self.evict_steps = 0
+        self.math = MATH_REFERENCE
 
 
 _state = _RenderState()
@@ -397,17 +402,21 @@ def updateViewMatrices(viewRotation=(0.0, 0.0, 0.0), viewTranslation=(0.0, 0.0, 
     return (np.array(_state.cam.inv_view[:], dtype=np.float32), np.array(_state.cam.normal[:], dtype=np.float32))
 
 
-def setSceneOptions(scene: int = SCENE_TANH, max_steps: int = 6000, flags: int = 0, evict_steps: int = 0):
-    """Compile-time settings of the reference (sceneSDF variant, MAX_STEPS) as run-time options."""
+def setSceneOptions(scene: int = SCENE_TANH, max_steps: int = 6000, flags: int = 0, evict_steps: int = 0,
+                    math: int = MATH_DETERMINISTIC):
+    """Compile-time settings of the reference (sceneSDF variant, MAX_STEPS) as run-time options.  This is the switch the
+    oracle-facing tests use, so `math` defaults to the deterministic forms the CPU oracle restates; pass
+    math=MATH_REFERENCE (the library's own default) to get the reference binary's frames."""
     _state.scene, _state.max_steps, _state.flags, _state.evict_steps = int(scene), int(max_steps), int(flags), int(evict_steps)
+    _state.math = int(math)
     if _state.scene != SCENE_PROGRAM:
         _state.program = None
 
 
-def setSceneProgram(ops, max_steps: int = 6000, flags: int = 0, evict_steps: int = 0):
+def setSceneProgram(ops, max_steps: int = 6000, flags: int = 0, evict_steps: int = 0, math: int = MATH_DETERMINISTIC):
     """Run-time form of editing sceneSDF (src/volumeRender_kernel.cu:217-230): ops = [(prim, combine, [params]) ...] over the
     reference's analytic SDF library (:67-196), see include/nsdf.h nsdf_scene_op."""
-    setSceneOptions(SCENE_PROGRAM, max_steps, flags, evict_steps)
+    setSceneOptions(SCENE_PROGRAM, max_steps, flags, evict_steps, math)
     _state.program = ops if not isinstance(ops, (list, tuple)) else capi.scene_ops(ops)
 
 
@@ -416,15 +425,16 @@ def _opts(tile_rank: int = 0, tile_world: int = 1) -> RenderOpts:
     if _state.program is not None:
         o.program = C.cast(_state.program, C.POINTER(capi.SceneOp))
         o.n_ops = len(_state.program)
+    o.math = _state.math
     return o
 
 
-def scene_eval(ops, xyz: torch.Tensor, nsdf: torch.Tensor, frame: int = 0) -> torch.Tensor:
+def scene_eval(ops, xyz: torch.Tensor, nsdf: torch.Tensor, frame: int = 0, math: int = MATH_DETERMINISTIC) -> torch.Tensor:
     """nsdf_scene_eval: the program's sceneSDF at n device points with given network outputs."""
     prog = ops if not isinstance(ops, (list, tuple)) else capi.scene_ops(ops)
     out = torch.empty_like(nsdf)
     capi.check(capi.lib().nsdf_scene_eval(C.cast(prog, C.POINTER(capi.SceneOp)), len(prog), xyz.data_ptr(), nsdf.data_ptr(),
-                                          frame, out.data_ptr(), nsdf.numel(), _stream_ptr()), "nsdf_scene_eval")
+                                          frame, math, out.data_ptr(), nsdf.numel(), _stream_ptr()), "nsdf_scene_eval")
     return out
 
 

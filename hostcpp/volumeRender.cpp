@@ -59,6 +59,11 @@ extern "C" void setRenderOptions(int scene, int maxSteps, int flags) {
     g.opts.flags = flags;
 }
 
+extern "C" void setMathMode(int math) {
+    ensure_init();
+    g.opts.math = math;
+}
+
 extern "C" void setSceneProgram(const nsdf_scene_op* ops, int nOps) {
     ensure_init();
     static nsdf_scene_op program[NSDF_SCENE_MAX_OPS];

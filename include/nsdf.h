@@ -86,6 +86,16 @@ typedef struct nsdf_scene_op {
 #define NSDF_COMB_SMOOTH_SUBTRACT 6  /* sdfOpSmoothSubtraction(s, d, k = a[7])                      (:138-142)    */
 #define NSDF_COMB_SMOOTH_SUBTRACT_FROM 7 /* sdfOpSmoothSubtraction(d, s, k = a[7])  (the commented scene of :225-227) */
 
+/* Arithmetic of the three operations the reference's device code takes from the SFU / libdevice: normalize's rsqrtf
+ * (src/common/helper_math.h:1309-1313), tanh (src/volumeRender_kernel.cu:229) and __saturatef (:140,146,268-271).
+ *   NSDF_MATH_REFERENCE      the same instructions the reference compiles to (rsqrt.approx.f32, libdevice tanhf, .sat): on the
+ *                            GPU family the reference binary runs on, frames are the reference's frames.  The drop-in default.
+ *   NSDF_MATH_DETERMINISTIC  IEEE-only forms (1/sqrt correctly rounded, a polynomial tanh, compare/select) that a CPU reproduces
+ *                            bit for bit: the mode the oracle tests run in.  Frames differ from the reference's in the last bits
+ *                            of ray directions and normals (0 hit-mask mismatches, 97.7-99.98 % of hit pixels within 1/255).   */
+#define NSDF_MATH_REFERENCE 0
+#define NSDF_MATH_DETERMINISTIC 1
+
 /* c_coloringType, src/volumeRender_kernel.cu:33 */
 #define NSDF_COLOR_FACING 0
 #define NSDF_COLOR_MATCAP 1
@@ -187,6 +197,7 @@ typedef struct nsdf_render_opts {
     int flags;        /* NSDF_RENDER_* bits                                                */
     const nsdf_scene_op* program; /* HOST array, read during the call; used when scene == NSDF_SCENE_PROGRAM */
     int n_ops;        /* 1..NSDF_SCENE_MAX_OPS                                             */
+    int math;         /* NSDF_MATH_*                                                       */
 } nsdf_render_opts;
 
 #define NSDF_RENDER_SIMPLE 1u      /* one-thread-per-pixel kernel without refill (debug / A-B testing) */
@@ -218,11 +229,13 @@ typedef struct nsdf_render_stats {
     unsigned long long pixels;     /* pixels this call covered                                          */
 } nsdf_render_stats;
 
-/* Fills opts with the reference's compile-time settings (tanh scene, 6000 steps, whole frame). */
+/* Fills opts with what the reference's HEAD build does: sceneSDF = manySphere(p, nSDF, true) (src/volumeRender_kernel.cu:221),
+ * MAX_STEPS 6000, facing-ratio colouring until copyStaticSettings says otherwise (src/main.cpp:655-662), reference math,
+ * whole frame. */
 void nsdf_render_opts_default(nsdf_render_opts* opts);
 /* sceneSDF for n points on the device: d_out[i] = program(d_xyz[3i..3i+2], d_nsdf[i]) with c_frameNumber = frame
  * (what singleMarch :459 and surfaceNormal :361-377 evaluate per query).  program is a HOST array. */
-int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame,
+int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,
                     float* d_out, int64_t n, void* stream);
 
 /* updateViewMatrices (src/main.cpp:207-222): modelView from viewRotation (degrees) and

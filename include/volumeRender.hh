@@ -6,7 +6,8 @@
 //                      (the reference's by-value declaration destroys the caller's layers).
 //   copyViewMatrices   c_invViewMatrix (3x4) and c_normalMatrix (4x4) + frame number, as cudaMemcpyToSymbol did.
 //   copyStaticSettings c_coloringType / c_numInputs.
-// Extensions: setRenderOptions (scene function, MAX_STEPS, NSDF_RENDER_* flags), setSceneProgram, getLastRenderStats,
+// Defaults are those of the reference's HEAD build (sceneSDF = manySphere, reference math; nsdf_render_opts_default).
+// Extensions: setRenderOptions (scene function, MAX_STEPS, NSDF_RENDER_* flags), setMathMode, setSceneProgram, getLastRenderStats,
 // updateViewMatrices (src/main.cpp:207-222 without Eigen).
 #pragma once
 #include <cstddef>
@@ -32,6 +33,8 @@ extern "C" void copyViewMatrices(float* invViewMatrix, size_t sizeofInvModelView
 extern "C" void copyStaticSettings(int colorType, int numInputs);
 
 extern "C" void setRenderOptions(int scene, int maxSteps, int flags);
+// NSDF_MATH_REFERENCE (default: the reference binary's frames) or NSDF_MATH_DETERMINISTIC (the CPU oracle's frames)
+extern "C" void setMathMode(int math);
 // sceneSDF (volumeRender_kernel.cu:217-230) as data: the op list is copied; selects NSDF_SCENE_PROGRAM (include/nsdf.h)
 extern "C" void setSceneProgram(const nsdf_scene_op* ops, int nOps);
 extern "C" void getLastRenderStats(nsdf_render_stats* out);

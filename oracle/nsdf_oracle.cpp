@@ -288,7 +288,12 @@ inline float many_cylinder_cut(f3 p, float nsdf) {
             cp.y = (float)((double)cp.y + 0.1);
             cp.x = (float)((double)p.x + 0.9);
         }
-        s = smooth_subtract(s, sdf_cylinder(cp, c), 0.01f);
+        // sdfCylinder (:96-101) as nvcc contracts it INSIDE this loop: dy is loop-invariant per row, and the compiled reference
+        // (oracle/_ref/ref_sdf_probe SASS: FMUL dx,dx ; FFMA dy,dy,.) forms fma(dy, dy, dx*dx) here, not the stand-alone
+        // function's fma(dx, dx, dy*dy)
+        const float dx = cp.x - c.x, dy = cp.y - c.z;
+        const float cyl = sqrtf(fmaf(dy, dy, dx * dx)) - c.y;
+        s = smooth_subtract(s, cyl, 0.01f);
         cp.x = (float)((double)cp.x - 0.1);
     }
     return s;
@@ -307,7 +312,9 @@ inline float scene_program_eval(const SceneOp* ops, int n, f3 p, float nsdf, int
             switch (op.prim) {
                 case 16: {   // sdfOpDisplace :103-110 (frequency 5 and amplitude 0.05 there; float parameters here)
                     const float w = (sinf_det(a[0] * p.x) * sinf_det(a[0] * p.y)) * sinf_det(a[0] * p.z);
-                    s = (float)fma((double)w, (double)a[1], (double)s);
+                    // :107 multiplies by the DOUBLE literal 0.05; a float parameter equal to 0.05f stands for that literal
+                    const double amp = a[1] == 0.05f ? 0.05 : (double)a[1];
+                    s = (float)fma((double)w, amp, (double)s);
                     break;
                 }
                 case 17: s = s - a[0]; break;                              // sdfOpRound :112-115

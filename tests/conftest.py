@@ -37,3 +37,17 @@ def gpu(built):
         pytest.skip("no CUDA device")
     torch.cuda.set_device(0)
     return torch.device("cuda:0")
+
+
+@pytest.fixture(autouse=True)
+def _oracle_facing_render_state():
+    """host.py starts like the library (the reference's HEAD build: manySphere scene, reference math).  The tests compare with the
+    CPU oracle unless they say otherwise, so every test starts from the tanh scene in the deterministic arithmetic."""
+    try:
+        from cudaneuralrender_b200 import host
+    except Exception:
+        yield
+        return
+    host.setSceneOptions(host.SCENE_TANH, 6000, 0, 0, host.MATH_DETERMINISTIC)
+    yield
+    host.setSceneOptions(host.SCENE_TANH, 6000, 0, 0, host.MATH_DETERMINISTIC)

@@ -31,7 +31,7 @@ def test_renderer_app_single_frame(gpu, tmp_path, matcap):
     W, H = 112, 80
     prefix = str(tmp_path) + "/"
     cmd = [os.path.join(ROOT, "apps", "neuralSDFRenderer"), "-i", model_path("car_1"), "-o", prefix, "-W", str(W), "-H", str(H),
-           "-ry", "30", "--single", "--ppm", "--stats"]
+           "-ry", "30", "--single", "--ppm", "--stats", "--scene", "tanh", "--math", "deterministic"]   # the oracle's arithmetic
     if matcap:
         cmd += ["-M", os.path.join(MATCAPS, matcap)]
     out = subprocess.run(cmd, capture_output=True, text=True)
@@ -61,7 +61,7 @@ def test_renderer_app_scene_program(gpu, tmp_path):
     W, H = 96, 64
     prefix = str(tmp_path) + "/"
     cmd = [os.path.join(ROOT, "apps", "neuralSDFRenderer"), "-i", model_path("plane_1"), "-o", prefix, "-W", str(W), "-H", str(H),
-           "-ry", "15", "--single", "--stats", "--scene", "displace", "-M", os.path.join(MATCAPS, "blue.png")]
+           "-ry", "15", "--single", "--stats", "--math", "deterministic", "--scene", "displace", "-M", os.path.join(MATCAPS, "blue.png")]
     out = subprocess.run(cmd, capture_output=True, text=True)
     assert out.returncode == 0, out.stdout + out.stderr
     om = oracle.Model.from_h5(model_path("plane_1"))

@@ -566,8 +566,9 @@ def test_frame_determinism_and_tiles(env):
 
 
 def test_full_size_frame_properties(env):
-    """BASELINE config 2 size (1920x1080 plane_1): size-independent checks -- determinism across
-    schedules, query accounting, and a 64-row band compared with the oracle."""
+    """BASELINE config 2 size (1920x1080 plane_1, the configuration the numbers are quoted on, where tile priority and the
+    express lanes are fully engaged): determinism across schedules, query accounting, and -- in both scenes -- rows 508..571
+    of the frame compared with the oracle pixel for pixel."""
     torch, host, oracle = env["torch"], env["host"], env["oracle"]
     nn, om = _load(env, "plane_1")
     W, H = 1920, 1080
@@ -580,7 +581,7 @@ def test_full_size_frame_properties(env):
     host.copyStaticSettings(host.COLOR_MATCAP, 3)
     host.copyViewMatrices(iv, nm, 0, 3)
     outs = []
-    for flags in (0, host.capi.RENDER_NO_STRAGGLER):
+    for flags in (0, host.capi.RENDER_SIMPLE):
         host.setSceneOptions(host.SCENE_TANH, 6000, flags)
         out = torch.zeros(W * H, dtype=torch.int32, device="cuda")
         st = torch.zeros(6, dtype=torch.int64, device="cuda")
@@ -594,6 +595,45 @@ def test_full_size_frame_properties(env):
     assert rays == W * H and abs(q - 25034278) / 25034278 < 5e-3 and abs(hits - 70375) < 300
     img = outs[0][0].cpu().numpy().view(np.uint32).reshape(H, W)
     assert int((img != 0).sum()) == hits
+    band = (508, 572, 1)
+    ref = oracle.render(om, iv, nm, W, H, matcap=matcap_np, rows=band)
+    assert np.array_equal(img[508:572], ref["image"][508:572])
+    assert int((ref["image"][508:572] != 0).sum()) > 1000          # the band crosses the shape
+    # the scene the reference renders at HEAD, same band
+    host.setSceneOptions(host.SCENE_MANYSPHERE, 6000)
+    out = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    host.render_kernel(out, W, H, nn, mc)
+    host.setSceneOptions()
+    ref = oracle.render(om, iv, nm, W, H, matcap=matcap_np, rows=band, scene=oracle.SCENE_MANYSPHERE)
+    assert np.array_equal(out.cpu().numpy().view(np.uint32).reshape(H, W)[508:572], ref["image"][508:572])
+
+
+def test_full_size_4k_band_against_oracle(env):
+    """BASELINE config 4 size (3840x2160, 3a3d4a90....obj): one 64-row band of the frame and of its 3-way tile partition
+    against the oracle, pixel for pixel."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "3a3d4a90a2db90b4203936772104a82d.obj")
+    W, H = 3840, 2160
+    matcap_np = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    mc = host.Image(host.Shape(matcap_np.shape[1], matcap_np.shape[0]))
+    mc.allocateMemory()
+    mc.hostData[:] = matcap_np.ravel()
+    mc.copyHostToDevice()
+    iv, nm = oracle.view_matrices()
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.copyViewMatrices(iv, nm, 0, 3)
+    host.setSceneOptions(host.SCENE_TANH, 6000)
+    a = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    host.render_kernel(a, W, H, nn, mc)
+    c = torch.full_like(a, 0x55)
+    for r in range(3):
+        host.render_kernel(c, W, H, nn, mc, tile_rank=r, tile_world=3)
+    assert torch.equal(a, c)
+    band = (1024, 1088, 1)
+    ref = oracle.render(om, iv, nm, W, H, matcap=matcap_np, rows=band)
+    img = a.cpu().numpy().view(np.uint32).reshape(H, W)
+    assert np.array_equal(img[1024:1088], ref["image"][1024:1088])
+    assert int((ref["image"][1024:1088] != 0).sum()) > 1000
 
 
 def test_error_behaviour(env):
