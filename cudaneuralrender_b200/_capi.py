@@ -13,6 +13,7 @@ ACT_RELU, ACT_TANH_LINEAR = 0, 1
 PREC_FP32, PREC_TC_FP16, PREC_TC_BF16, PREC_TC_FP16X3, PREC_FP32_WARP, PREC_TC_FP16_ACC16 = 0, 1, 2, 3, 4, 5
 COLOR_FACING, COLOR_MATCAP = 0, 1
 RENDER_SIMPLE, RENDER_NO_STRAGGLER, RENDER_PHASE_THROUGHPUT, RENDER_PHASE_LATENCY, RENDER_TWO_KERNELS, RENDER_QUEUE, RENDER_NO_QUIET_SMS, RENDER_TC_FARFIELD, RENDER_TWO_PASS, RENDER_HYBRID = 1, 2, 4, 8, 16, 32, 64, 128, 256, 512
+RENDER_STAGED_STORES = 1024
 IPC_HANDLE_BYTES = 64
 
 
@@ -87,6 +88,9 @@ PROTOTYPES = {
     "nsdf_scene_eval": (_i, [C.POINTER(SceneOp), _i, _vp, _vp, _i, _i, _vp, _i64, _vp]),
     "nsdf_camera_from_view": (None, [_f, _f, _f, _f, _f, _i, C.POINTER(Camera)]),
     "nsdf_render": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
+    "nsdf_render_views": (_i, [_vp, C.POINTER(Camera), _i, _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
+    "nsdf_render_views_host": (_i, [_vp, C.POINTER(Camera), _i, _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i,
+                                    C.POINTER(RenderStats)]),
     "nsdf_render_host": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i,
                               C.POINTER(RenderStats)]),
     "nsdf_ipc_export": (_i, [_vp, C.c_char_p]),

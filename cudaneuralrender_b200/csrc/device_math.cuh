@@ -101,15 +101,27 @@ __device__ __forceinline__ float smooth_union(float d1, float d2, float k, bool 
     return (float)fma(-omh, (double)kh, (double)mix);
 }
 
-// manySphere(p, nSDF, true) (volumeRender_kernel.cu:176-196): what sceneSDF (:217-222)
-// evaluates at the reference's HEAD.  The nine sphere distances depend on the point alone, so they are computed first (nine
-// independent square roots instead of a serial loop) and their minimum decides, with one compare, whether the whole chain of
-// smooth unions is the identity on nSDF (every union then takes smooth_union's d2 - d1 >= k exit; rounding is monotonic, so
-// fl(d_i - s) >= fl(dmin - s)).  A marching warp can take the minimum before the network answers (many_sphere_dmin).
-__device__ __forceinline__ void many_sphere_dists(f3 p, int frame, float (&d)[9]) {
+// manySphere(p, nSDF, true) (volumeRender_kernel.cu:176-196): what sceneSDF (:217-222) evaluates at the reference's HEAD.
+//
+// The nine sphere centres depend on the point alone, and almost every query is nowhere near a sphere: then every one of the
+// nine smooth unions takes smooth_union's d2 - d1 >= k exit and the function is the identity on nSDF.  That case is decided
+// WITHOUT the nine square roots and without the chain: with m = min_i |p - c_i|^2 (computed exactly as the chain computes
+// each len2), sqrt(len2_i) >= nSDF + 0.11001 for every i  =>  d_i = fl(fl(sqrt) - 0.1f) >= nSDF + 0.0100097 > nSDF + k
+// =>  fl(d_i - s) >= k (rounding is monotonic; the 1e-5 in the constant and the 1e-6 in the factor are far above the
+// roundings involved), so m >= (nSDF + 0.11001)^2 proves it.  m is the "pre" value: a marching warp takes it before the
+// network answers, off the dependent chain (~160 clocks of double adds instead of ~2000 clocks of square roots with their
+// slow-path branches on every march step: measured 2.35 us per dependent step against 1.35 us for the tanh scene).
+// zoff = -0.7 + (c_frameNumber*2*0.7/360) (:182) depends on the frame number alone: many_sphere_zoff computes it once per
+// call on the host in the same IEEE double operations (a device-side double division of 0 by 360 -- frame 0 -- takes the
+// slow path of the division routine on every step of every ray).
+__host__ __device__ inline double many_sphere_zoff(int frame) {
+    volatile double num = (double)(frame * 2) * 0.7;
+    volatile double q = num / 360.0;
+    return -0.7 + q;
+}
+__device__ __forceinline__ void many_sphere_len2(f3 p, double zoff, float (&len2)[9]) {
     float cx = p.x;
     float cy = (float)__dsub_rn((double)p.y, 0.6);
-    const double zoff = __dadd_rn(-0.7, __ddiv_rn(__dmul_rn((double)(frame * 2), 0.7), 360.0));
     const float cz = (float)__dadd_rn((double)p.z, zoff);
     const float zz = cz * cz;
 #pragma unroll
@@ -118,41 +130,73 @@ __device__ __forceinline__ void many_sphere_dists(f3 p, int frame, float (&d)[9]
             cy = (float)__dadd_rn((double)cy, 0.4);
             cx = p.x + 0.5f;
         }
-        const float len2 = zz + fmaf(cx, cx, cy * cy);
-        d[i] = __fsqrt_rn(len2) + (-0.1f);
+        len2[i] = zz + fmaf(cx, cx, cy * cy);
         cx = (float)__dsub_rn((double)cx, 0.4);
     }
 }
-__device__ __forceinline__ float many_sphere_dmin(f3 p, int frame) {
-    float d[9];
-    many_sphere_dists(p, frame, d);
-    float m = d[0];
+__device__ __forceinline__ float many_sphere_pre(f3 p, double zoff) {
+    float l[9];
+    many_sphere_len2(p, zoff, l);
+    float m = l[0];
 #pragma unroll
-    for (int i = 1; i < 9; ++i) m = fminf(m, d[i]);   // a NaN distance yields a NaN-free minimum that can only be too small
-    return (d[0] == d[0] && d[1] == d[1] && d[2] == d[2] && d[3] == d[3] && d[4] == d[4] && d[5] == d[5] && d[6] == d[6] &&
-            d[7] == d[7] && d[8] == d[8]) ? m : -3.0e38f;
+    for (int i = 1; i < 9; ++i) m = (l[i] < m) ? l[i] : m;
+    bool ok = true;       // a NaN anywhere (a NaN point) sends the query the long way
+#pragma unroll
+    for (int i = 0; i < 9; ++i) ok = ok && (l[i] == l[i]);
+    return ok ? m : -1.0f;
 }
-__device__ __forceinline__ float many_sphere_union(f3 p, float nsdf, int frame, bool ref, float dmin) {
-    const float k = 0.01f;
-    const float gap = dmin - nsdf;
-    if (gap >= k && gap <= 1.0e30f && nsdf != 0.0f) return nsdf;
-    float d[9];
-    many_sphere_dists(p, frame, d);
+// The chain itself for a point that IS near a sphere (rays grazing a sphere stay in this case for thousands of steps, so it
+// is the frame's critical path: measured 2.7 us per dependent step with the reference's loop against 1.3 us elsewhere).
+// Same nine smooth unions in the same order, but a sphere whose squared distance proves d_i - s >= k for every value s can
+// take along the chain (the running s never exceeds nSDF: a smooth union is <= min(d1, d2) up to an ulp, covered by the
+// margin) is the identity and is skipped without its square root or its double-precision blend; typically one sphere is left.
+__device__ __noinline__ float many_sphere_union_chain(f3 p, float nsdf, double zoff, bool ref) {
+    const bool plain = nsdf != 0.0f && fabsf(nsdf) <= 1.0e30f;
+    const float thr = nsdf + 0.11002f;
+    const float thr2 = (thr * thr) * 1.000001f;
     float s = nsdf;
-#pragma unroll
-    for (int i = 0; i < 9; ++i) s = smooth_union(s, d[i], k, ref);
+    float cx = p.x;
+    float cy = (float)__dsub_rn((double)p.y, 0.6);
+    const float cz = (float)__dadd_rn((double)p.z, zoff);
+    const float zz = cz * cz;
+#pragma unroll 1      // rolled on purpose: one copy of the blend keeps this function (and the registers its callers must save) small
+    for (int i = 0; i < 9; ++i) {
+        if (i % 3 == 0) {
+            cy = (float)__dadd_rn((double)cy, 0.4);
+            cx = p.x + 0.5f;
+        }
+        const float len2 = zz + fmaf(cx, cx, cy * cy);
+        const bool far = plain && len2 <= 1.0e30f && (thr <= 0.0f || len2 >= thr2);
+        if (!far) s = smooth_union(s, __fsqrt_rn(len2) + (-0.1f), 0.01f, ref);
+        cx = (float)__dsub_rn((double)cx, 0.4);
+    }
     return s;
+}
+// Clearance tracking.  `rem` is a lower bound of min_i sqrt(len2_i) at the ray's current point (negative = unknown), carried
+// from step to step: a march step moves the point by at most |t| (|d| = 1 up to rounding), so the clearance shrinks by at most
+// that; the caller subtracts clearance_step(t) after every step.  While rem >= nSDF + 0.11002 the union is the identity (see
+// above) and a march step costs one compare -- no double arithmetic, no square root; when the bound is exhausted it is
+// refreshed from the exact minimum at the current point.  Slack: the computed centre offsets are within ~4e-7 of the true
+// ones and a step's rounding moves the point by < 3e-7, hence the 3e-6 at refresh and the 5e-7 per step.
+__device__ __forceinline__ float clearance_step(float t) { return fmaf(fabsf(t), 1.000002f, 5.0e-7f); }
+__device__ __forceinline__ float many_sphere_union(f3 p, float nsdf, double zoff, bool ref, float& rem) {
+    const bool plain = nsdf != 0.0f && fabsf(nsdf) <= 1.0e30f;
+    const float thr = nsdf + 0.11002f;
+    if (plain && rem >= 0.0f && (thr <= 0.0f || rem >= thr)) return nsdf;
+    const float m = many_sphere_pre(p, zoff);
+    const bool valid = m >= 0.0f && m <= 1.0e30f;
+    rem = valid ? __fsqrt_rd(m) - 3.0e-6f : -1.0f;
+    const float thr2 = nsdf + 0.11001f;
+    if (plain && valid && (thr2 <= 0.0f || m >= (thr2 * thr2) * 1.000001f)) return nsdf;
+    return many_sphere_union_chain(p, nsdf, zoff, ref);
 }
 
 enum { SCENE_TANH = 0, SCENE_MANYSPHERE = 1 };
 
-// The part of sceneSDF that depends on the point alone (nothing for the tanh scene).
-__device__ __forceinline__ float scene_pre(int scene, f3 p, int frame) {
-    return scene == SCENE_MANYSPHERE ? many_sphere_dmin(p, frame) : 0.0f;
-}
-// sceneSDF (volumeRender_kernel.cu:217-230): scene 1 = HEAD, scene 0 = `tanh(nSDF)` (:229).
-__device__ __forceinline__ float scene_sdf(int scene, f3 p, float nsdf, int frame, bool ref, float pre) {
-    if (scene == SCENE_MANYSPHERE) return many_sphere_union(p, nsdf, frame, ref, pre);
+// sceneSDF (volumeRender_kernel.cu:217-230): scene 1 = HEAD, scene 0 = `tanh(nSDF)` (:229).  rem: clearance state of the ray
+// (many_sphere_union), untouched by the tanh scene.
+__device__ __forceinline__ float scene_sdf(int scene, f3 p, float nsdf, double zoff, bool ref, float& rem) {
+    if (scene == SCENE_MANYSPHERE) return many_sphere_union(p, nsdf, zoff, ref, rem);
     return tanh_sel(nsdf, ref);
 }
 
@@ -178,6 +222,7 @@ struct Camera {
     float inv_view[12];  // c_invViewMatrix rows 0..2 (volumeRender_kernel.cu:31)
     float normal[16];    // c_normalMatrix (:32)
     int frame;           // c_frameNumber (:35)
+    double zoff;         // many_sphere_zoff(frame), filled by the host side of the launch
 };
 
 struct RayInit { f3 o, d, p; float tfar; bool hit; };

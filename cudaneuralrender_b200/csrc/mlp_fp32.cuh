@@ -361,79 +361,6 @@ __device__ __forceinline__ void mlp32_eval_warp(const float* __restrict__ sw, in
     __syncwarp();   // abuf may be rewritten by the caller's next evaluation
 }
 
-// ---- one point per warp, latency form ---------------------------------------------------------------
-// The serial tail of a frame is ONE ray's chain of dependent evaluations, so what counts here is the
-// latency of a single evaluation, whose floor is the dependent FFMA chain 3 + n_sq*32 + 32 (4 clocks each).
-// mlp32_eval_warp<1> pays ~140 clocks per layer on top of the 128-clock chain: its 32 weight loads are issued after the
-// __syncwarp() that publishes the previous layer (a barrier orders memory operations, so the compiler cannot hoist them),
-// then wait out the shared-memory latency before the chain can start.  Weights do not depend on activations: here lane o
-// loads the column W[o][0..31] of layer l+1 into registers BEFORE layer l's chain (two register buffers, layers unrolled
-// in pairs), so that after the barrier only the eight activation loads stand between one chain and the next; the last
-// layer's weights are fetched the same way.  Same arithmetic, same bits (ascending-k fmaf chain from 0, + bias, relu).
-// x is warp-uniform, the result is returned in every lane.  abuf: 2 * WARP_ACT_STRIDE floats of per-warp scratch.
-__device__ __forceinline__ void lone_load_col(const float* __restrict__ Wt, int lane, float (&w)[32], float& bias) {
-#pragma unroll
-    for (int k = 0; k < 32; ++k) w[k] = Wt[k * 32 + lane];
-    bias = Wt[1024 + lane];
-}
-__device__ __forceinline__ void lone_load_last(const float* __restrict__ LL, float (&w)[32], float& bias) {
-#pragma unroll
-    for (int kc = 0; kc < 8; ++kc) {
-        const float4 v = *reinterpret_cast<const float4*>(LL + 4 * kc);
-        w[4 * kc + 0] = v.x; w[4 * kc + 1] = v.y; w[4 * kc + 2] = v.z; w[4 * kc + 3] = v.w;
-    }
-    bias = LL[32];
-}
-__device__ __forceinline__ float lone_chain(const float (&w)[32], const float* __restrict__ act) {
-    float acc = 0.0f;
-#pragma unroll
-    for (int kc = 0; kc < 8; ++kc) {
-        const float4 av = *reinterpret_cast<const float4*>(act + 4 * kc);
-        acc = fmaf(w[4 * kc + 0], av.x, acc);
-        acc = fmaf(w[4 * kc + 1], av.y, acc);
-        acc = fmaf(w[4 * kc + 2], av.z, acc);
-        acc = fmaf(w[4 * kc + 3], av.w, acc);
-    }
-    return acc;
-}
-__device__ __forceinline__ float mlp32_eval_lone(const float* __restrict__ sw, int n_sq, float* __restrict__ abuf, float x0,
-                                                 float x1, float x2, int lane, float t4 = 0.0f, bool in4 = false) {
-    float* cur = abuf;
-    float* nxt = abuf + WARP_ACT_STRIDE;
-    float wA[32], wB[32], bA, bB;
-    const float* H = sw + FUSED_L0_FLOATS;
-    const float* LL = H + n_sq * FUSED_SQ_FLOATS;
-    {
-        const float w0 = sw[lane], w1 = sw[32 + lane], w2 = sw[64 + lane], bb = sw[128 + lane];
-        if (n_sq > 0) lone_load_col(H, lane, wA, bA); else lone_load_last(LL, wA, bA);
-        float c = fmaf(w2, x2, fmaf(w1, x1, fmaf(w0, x0, 0.0f)));
-        if (in4) c = fmaf(sw[96 + lane], t4, c);
-        cur[lane] = relu_det(c + bb);
-    }
-    __syncwarp();
-    int l = 0;
-#pragma unroll 1
-    for (; l + 1 < n_sq; l += 2) {
-        lone_load_col(H + (l + 1) * FUSED_SQ_FLOATS, lane, wB, bB);
-        nxt[lane] = relu_det(lone_chain(wA, cur) + bA);
-        __syncwarp();
-        if (l + 2 < n_sq) lone_load_col(H + (l + 2) * FUSED_SQ_FLOATS, lane, wA, bA); else lone_load_last(LL, wA, bA);
-        cur[lane] = relu_det(lone_chain(wB, nxt) + bB);
-        __syncwarp();
-    }
-    float out;
-    if (l < n_sq) {   // odd number of hidden layers: wA holds the last hidden one
-        lone_load_last(LL, wB, bB);
-        nxt[lane] = relu_det(lone_chain(wA, cur) + bA);
-        __syncwarp();
-        out = lone_chain(wB, nxt) + bB;
-    } else {
-        out = lone_chain(wA, cur) + bA;
-    }
-    __syncwarp();   // abuf may be rewritten by the caller's next evaluation
-    return out;
-}
-
 // ---- warp-cooperative evaluator, 16 points, register-tiled ------------------------------------------
 // One warp evaluates 16 points; lane = (g = lane & 7, rg = lane >> 3) owns the 4 x 4 tile
 // {neurons 4g..4g+3} x {points rg, rg+4, rg+8, rg+12}.  A hidden layer is still a 32-deep FFMA chain per output
@@ -532,6 +459,125 @@ __device__ __forceinline__ float mlp32_eval_warp16(const float* __restrict__ sw,
     }
     __syncwarp();   // abuf may be rewritten by the caller's next evaluation
     return out;
+}
+
+// ---- warp-cooperative evaluator, 8 neurons x RJ points per lane ---------------------------------------------
+// One warp evaluates 8*RJ points (RJ = 4: 32 points, RJ = 8: 64 points); lane (g = lane & 3, rg = lane >> 2) owns the tile
+// {neurons 8g..8g+7} x {points rg + 8j, j < RJ}.  Why: shared memory fills registers at 128 B per clock per SM whatever the
+// access pattern (only a warp-uniform load is cheaper), so an evaluator is bound by that pipe unless a loaded byte feeds at
+// least one FFMA of its lane.  Per k the tile loads 8 weights + RJ activations for 8*RJ FFMA: 1.5 B per FFMA at RJ = 4 and
+// 1 B at RJ = 8, against 2 B for the 4 x 4 tile of mlp32_eval_warp16 (ncu: LSU wavefronts 88 % busy, FMA pipe 53 %).
+// Bank layout: weights Wt[k][8g..8g+7] are two float4 per lane, four distinct addresses per warp, conflict-free; activations
+// live point-major with the WARP_ACT_STRIDE = 36 row stride, the eight rows rg + 8j of one load start four banks apart, and
+// the two float4 stores per point of a quarter warp cover all 32 banks.
+// xin: abuf + 8*RJ*WARP_ACT_STRIDE (the second activation buffer) holds the points as float4 {x, y, z, -}, written by the
+// caller (a __syncwarp() is issued here).  Returns the value of point `lane` in y[0] (and of point lane + 32 in y[1] for
+// RJ = 8).  Same bits as every other evaluator (ascending-k fmaf chain from 0, + bias, relu).
+template <int RJ>
+__device__ __forceinline__ void mlp32_eval_tile(const float* __restrict__ sw, int n_sq, float* __restrict__ abuf, int lane,
+                                                float (&y)[RJ / 4], float t4 = 0.0f, bool in4 = false) {
+    constexpr int NP = 8 * RJ;
+    float* cur = abuf;
+    float* nxt = abuf + NP * WARP_ACT_STRIDE;
+    const int g = lane & 3, rg = lane >> 2;
+    __syncwarp();
+    {
+        const float4* S4 = reinterpret_cast<const float4*>(sw) + 2 * g;
+        float4 w[4][2], bb[2];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { w[k][0] = S4[8 * k]; w[k][1] = S4[8 * k + 1]; }
+        bb[0] = S4[32]; bb[1] = S4[33];
+#pragma unroll
+        for (int j = 0; j < RJ; ++j) {
+            const int r = rg + 8 * j;
+            const float4 x = *reinterpret_cast<const float4*>(nxt + 4 * r);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float4 z;
+                z.x = fmaf(w[2][h].x, x.z, fmaf(w[1][h].x, x.y, fmaf(w[0][h].x, x.x, 0.0f)));
+                z.y = fmaf(w[2][h].y, x.z, fmaf(w[1][h].y, x.y, fmaf(w[0][h].y, x.x, 0.0f)));
+                z.z = fmaf(w[2][h].z, x.z, fmaf(w[1][h].z, x.y, fmaf(w[0][h].z, x.x, 0.0f)));
+                z.w = fmaf(w[2][h].w, x.z, fmaf(w[1][h].w, x.y, fmaf(w[0][h].w, x.x, 0.0f)));
+                if (in4) {
+                    z.x = fmaf(w[3][h].x, t4, z.x); z.y = fmaf(w[3][h].y, t4, z.y);
+                    z.z = fmaf(w[3][h].z, t4, z.z); z.w = fmaf(w[3][h].w, t4, z.w);
+                }
+                z.x = relu_det(z.x + bb[h].x); z.y = relu_det(z.y + bb[h].y);
+                z.z = relu_det(z.z + bb[h].z); z.w = relu_det(z.w + bb[h].w);
+                *reinterpret_cast<float4*>(cur + r * WARP_ACT_STRIDE + 8 * g + 4 * h) = z;
+            }
+        }
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int l = 0; l < n_sq; ++l) {
+        const float4* Wt = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS) + 2 * g;
+        const float* arow = cur + rg * WARP_ACT_STRIDE;
+        float z[8][RJ];   // [neuron i][point j]
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < RJ; ++j) z[i][j] = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            float a[RJ][4];   // [point j][k within the chunk]
+#pragma unroll
+            for (int j = 0; j < RJ; ++j) {
+                const float4 av = *reinterpret_cast<const float4*>(arow + 8 * j * WARP_ACT_STRIDE + 4 * kc);
+                a[j][0] = av.x; a[j][1] = av.y; a[j][2] = av.z; a[j][3] = av.w;
+            }
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const float4 w0 = Wt[(4 * kc + kk) * 8], w1 = Wt[(4 * kc + kk) * 8 + 1];
+#pragma unroll
+                for (int j = 0; j < RJ; ++j) {
+                    z[0][j] = fmaf(w0.x, a[j][kk], z[0][j]);
+                    z[1][j] = fmaf(w0.y, a[j][kk], z[1][j]);
+                    z[2][j] = fmaf(w0.z, a[j][kk], z[2][j]);
+                    z[3][j] = fmaf(w0.w, a[j][kk], z[3][j]);
+                    z[4][j] = fmaf(w1.x, a[j][kk], z[4][j]);
+                    z[5][j] = fmaf(w1.y, a[j][kk], z[5][j]);
+                    z[6][j] = fmaf(w1.z, a[j][kk], z[6][j]);
+                    z[7][j] = fmaf(w1.w, a[j][kk], z[7][j]);
+                }
+            }
+        }
+        const float4 b0 = Wt[256], b1 = Wt[257];
+#pragma unroll
+        for (int j = 0; j < RJ; ++j) {
+            float4 o0, o1;
+            o0.x = relu_det(z[0][j] + b0.x); o0.y = relu_det(z[1][j] + b0.y);
+            o0.z = relu_det(z[2][j] + b0.z); o0.w = relu_det(z[3][j] + b0.w);
+            o1.x = relu_det(z[4][j] + b1.x); o1.y = relu_det(z[5][j] + b1.y);
+            o1.z = relu_det(z[6][j] + b1.z); o1.w = relu_det(z[7][j] + b1.w);
+            float* dst = nxt + (rg + 8 * j) * WARP_ACT_STRIDE + 8 * g;
+            *reinterpret_cast<float4*>(dst) = o0;
+            *reinterpret_cast<float4*>(dst + 4) = o1;
+        }
+        __syncwarp();
+        float* t = cur; cur = nxt; nxt = t;
+    }
+    {
+        const float* LL = sw + FUSED_L0_FLOATS + n_sq * FUSED_SQ_FLOATS;
+        float acc[RJ / 4];
+#pragma unroll
+        for (int q = 0; q < RJ / 4; ++q) acc[q] = 0.0f;
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+            const float4 w = *reinterpret_cast<const float4*>(LL + 4 * kc);
+#pragma unroll
+            for (int q = 0; q < RJ / 4; ++q) {
+                const float4 av = *reinterpret_cast<const float4*>(cur + (lane + 32 * q) * WARP_ACT_STRIDE + 4 * kc);
+                acc[q] = fmaf(w.x, av.x, acc[q]);
+                acc[q] = fmaf(w.y, av.y, acc[q]);
+                acc[q] = fmaf(w.z, av.z, acc[q]);
+                acc[q] = fmaf(w.w, av.w, acc[q]);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < RJ / 4; ++q) y[q] = acc[q] + LL[32];
+    }
+    __syncwarp();   // abuf may be rewritten by the caller's next evaluation
 }
 
 }  // namespace nsdf

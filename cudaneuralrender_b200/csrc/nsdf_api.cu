@@ -442,21 +442,26 @@ void nsdf_camera_from_view(float rx_deg, float ry_deg, float tx, float ty, float
     cam->frame = frame;
 }
 
-int nsdf_render(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
-                const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream) {
-    if (!m || !cam || !d_out || W <= 0 || H <= 0) return NSDF_EINVAL;
+int nsdf_render_views(const nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
+                      const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream) {
+    if (!m || !cams || !d_out || W <= 0 || H <= 0 || n_views < 1) return NSDF_EINVAL;
     nsdf_render_opts o;
     if (opts) o = *opts;
     else nsdf_render_opts_default(&o);
-    return nsdf::render_launch(const_cast<nsdf_model*>(m), cam, d_matcap, mw, mh, &o, d_out, W, H, d_stats,
+    return nsdf::render_launch(const_cast<nsdf_model*>(m), cams, n_views, d_matcap, mw, mh, &o, d_out, W, H, d_stats,
                                (cudaStream_t)stream);
 }
 
-int nsdf_render_host(const nsdf_model* cm, const nsdf_camera* cam, const uint32_t* h_matcap, int mw, int mh,
-                     const nsdf_render_opts* opts, uint32_t* h_out, int W, int H, nsdf_render_stats* h_stats) {
+int nsdf_render(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream) {
+    return nsdf_render_views(m, cam, 1, d_matcap, mw, mh, opts, d_out, W, H, d_stats, stream);
+}
+
+int nsdf_render_views_host(const nsdf_model* cm, const nsdf_camera* cams, int n_views, const uint32_t* h_matcap, int mw, int mh,
+                           const nsdf_render_opts* opts, uint32_t* h_out, int W, int H, nsdf_render_stats* h_stats) {
     nsdf_model* m = const_cast<nsdf_model*>(cm);
-    if (!m || !cam || !h_out || W <= 0 || H <= 0) return NSDF_EINVAL;
-    const size_t npx = (size_t)W * H;
+    if (!m || !cams || !h_out || W <= 0 || H <= 0 || n_views < 1) return NSDF_EINVAL;
+    const size_t npx = (size_t)W * H * (size_t)n_views;
     const bool have_mat = h_matcap && mw > 0 && mh > 0;
     int rc = ensure_stage(m, 0, npx * sizeof(uint32_t));
     if (rc) return rc;
@@ -469,12 +474,17 @@ int nsdf_render_host(const nsdf_model* cm, const nsdf_camera* cam, const uint32_
     // needs no device-side counterpart
     if (have_mat) NSDF_TRY(cudaMemcpyAsync(d_mat, h_matcap, (size_t)mw * mh * sizeof(uint32_t), cudaMemcpyHostToDevice, 0));
     if (d_stats) NSDF_TRY(cudaMemsetAsync(d_stats, 0, sizeof(nsdf_render_stats), 0));
-    rc = nsdf_render(m, cam, d_mat, mw, mh, opts, d_out, W, H, d_stats, nullptr);
+    rc = nsdf_render_views(m, cams, n_views, d_mat, mw, mh, opts, d_out, W, H, d_stats, nullptr);
     if (rc) return rc;
     NSDF_TRY(cudaMemcpyAsync(h_out, d_out, npx * sizeof(uint32_t), cudaMemcpyDeviceToHost, 0));
     if (d_stats) NSDF_TRY(cudaMemcpyAsync(h_stats, d_stats, sizeof(nsdf_render_stats), cudaMemcpyDeviceToHost, 0));
     NSDF_TRY(cudaStreamSynchronize(0));
     return NSDF_OK;
+}
+
+int nsdf_render_host(const nsdf_model* cm, const nsdf_camera* cam, const uint32_t* h_matcap, int mw, int mh,
+                     const nsdf_render_opts* opts, uint32_t* h_out, int W, int H, nsdf_render_stats* h_stats) {
+    return nsdf_render_views_host(cm, cam, 1, h_matcap, mw, mh, opts, h_out, W, H, h_stats);
 }
 
 int nsdf_ipc_export(void* d_ptr, unsigned char handle_out[NSDF_IPC_HANDLE_BYTES]) {

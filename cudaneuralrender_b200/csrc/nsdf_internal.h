@@ -24,7 +24,12 @@ struct nsdf_model {
     // src/volumeRender_kernel.cu:578-585); one render at a time per model handle
     unsigned int* d_counters = nullptr;   // [0] pixel counter [1] queue tail [2] queue head [3] pad
     void* d_queue = nullptr;
-    void* d_xqueue = nullptr;             // express queue of the cooperative tracer (fixed capacity, trace_coop.cuh)
+    void* d_xqueue = nullptr;             // express queue of the cooperative tracer (trace_coop.cuh), grown with the views of a call
+    size_t xqueue_capacity = 0;           // entries
+    void* d_views = nullptr;              // per-view cameras of a batched call (nsdf_render_views)
+    size_t views_capacity = 0;
+    void* d_frame_stage = nullptr;        // staged frame stores: [jobs][64 x 64] pixels, then [jobs] tile counters
+    size_t frame_stage_jobs = 0;
     size_t queue_capacity = 0;
     unsigned int frame_seq = 0;           // publication stamp of the fused tracer's queue entries
     nsdf_render_stats* d_stats_scratch = nullptr;
@@ -56,7 +61,7 @@ int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const flo
 // renderer (nsdf_render.cu)
 int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,
                       float* d_out, int64_t n, cudaStream_t stream);
-int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream);
 void render_release(nsdf_model* m);

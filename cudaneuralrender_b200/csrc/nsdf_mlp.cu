@@ -123,6 +123,39 @@ mlp_fp32_warp16_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int 
     }
 }
 
+// The 8-neuron x RJ-point register tiles (mlp32_eval_tile): 32 or 64 points per warp.
+template <int RJ>
+__global__ void __launch_bounds__(RJ == 4 ? 512 : 256, 1)
+mlp_fp32_tile_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_sq, const float* __restrict__ xin,
+                     float* __restrict__ yout, long long n, const LatticeParams lp) {
+    constexpr int NP = 8 * RJ;
+    extern __shared__ __align__(16) float s_w[];
+    __shared__ uint64_t s_bar;
+    stage_weights(s_w, blob, blob_bytes, &s_bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    float* abuf = s_w + (blob_bytes >> 2) + warp * (2 * NP * WARP_ACT_STRIDE);
+    const long long gw = (long long)blockIdx.x * wpb + warp, nw = (long long)gridDim.x * wpb;
+    for (long long base = gw * NP; base < n; base += nw * NP) {
+#pragma unroll
+        for (int q = 0; q < RJ / 4; ++q) {
+            const long long i = base + lane + 32 * q;
+            float x[3] = {0.0f, 0.0f, 0.0f};
+            if (i < n) {
+                if (lp.enabled) lattice_point(lp, lp.first + i, x);
+                else { x[0] = __ldg(xin + 3 * i); x[1] = __ldg(xin + 3 * i + 1); x[2] = __ldg(xin + 3 * i + 2); }
+            }
+            *reinterpret_cast<float4*>(abuf + NP * WARP_ACT_STRIDE + 4 * (lane + 32 * q)) = make_float4(x[0], x[1], x[2], 0.0f);
+        }
+        float y[RJ / 4];
+        mlp32_eval_tile<RJ>(s_w, n_sq, abuf, lane, y);
+#pragma unroll
+        for (int q = 0; q < RJ / 4; ++q) {
+            const long long i = base + lane + 32 * q;
+            if (i < n) yout[i] = y[q];
+        }
+    }
+}
+
 // Development rung (NSDF_FP32_P=40): the thread-per-point evaluator with the weights in __constant__ memory, so that they reach
 // the FFMAs through the uniform datapath / constant-bank operands instead of the shared-memory pipe (ncu: every LDS.128 costs four
 // wavefronts, which is what bounds the shared-memory forms).  One symbol per device: callers on different streams would overwrite
@@ -357,6 +390,21 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
             if (nt == 3) mlp_fp32_pipe_kernel<3><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
             else if (nt == 1) mlp_fp32_pipe_kernel<1><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
             else mlp_fp32_pipe_kernel<2><<<grid, 256, smem, stream>>>(m->d_blob, d_x, d_y, n, lp);
+            return (int)cudaGetLastError();
+        }
+        if (R == 32 || R == 64) {   // 8 x 4 / 8 x 8 register tiles, one CTA per SM
+            const int np = R, thr = env_int("NSDF_FP32_WARP_THREADS", R == 32 ? 512 : 256);
+            const size_t smem = m->blob_bytes + (size_t)(thr / 32) * 2 * np * WARP_ACT_STRIDE * sizeof(float);
+            cudaError_t e2 = cudaFuncSetAttribute(mlp_fp32_tile_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+            if (e2 != cudaSuccess) return (int)e2;
+            e2 = cudaFuncSetAttribute(mlp_fp32_tile_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+            if (e2 != cudaSuccess) return (int)e2;
+            if (smem > 220 * 1024) return NSDF_EINVAL;
+            const long long per_cta = (long long)(thr / 32) * np;
+            const long long want = (n + per_cta - 1) / per_cta;
+            const int grid = (int)(want < (long long)sms ? want : (long long)sms);
+            if (R == 32) mlp_fp32_tile_kernel<4><<<grid, thr, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+            else mlp_fp32_tile_kernel<8><<<grid, thr, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
             return (int)cudaGetLastError();
         }
         if (R == 16) {

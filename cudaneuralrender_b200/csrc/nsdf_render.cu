@@ -5,6 +5,7 @@
 // =====================================================================================
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "nsdf_internal.h"
 #include "render_kernels.cuh"
@@ -32,21 +33,35 @@ static size_t fused_smem(const nsdf_model* m) {
 }
 
 static size_t coop_smem(const nsdf_model* m) {
-    return m->blob_bytes + (COOP_THREADS / 32) * 2 * COOP_R * WARP_ACT_STRIDE * sizeof(float);
+    const size_t need = m->blob_bytes + (COOP_THREADS / 32) * 2 * COOP_R * WARP_ACT_STRIDE * sizeof(float);
+    return need > COOP_MIN_SMEM ? need : COOP_MIN_SMEM;   // more than half an SM: one CTA per SM
+}
+
+// The cooperative tracer's warps wait on one another (queues, termination counters): every CTA of the grid must be resident.
+// cudaLaunchCooperativeKernel guarantees that or fails; the grid never exceeds one CTA per SM.
+static cudaError_t launch_coop(const RenderParams& rp, unsigned int grid, size_t smem, cudaStream_t stream) {
+    void* args[] = {const_cast<RenderParams*>(&rp)};
+    return cudaLaunchCooperativeKernel((const void*)trace_coop_kernel, dim3(grid), dim3(COOP_THREADS), args, smem, stream);
 }
 
 // express queue of the cooperative tracer: pushes stop at half of it; the other half is room for every warp's last push
-constexpr size_t XQUEUE_ENTRIES = 1u << 17;
+constexpr size_t XQUEUE_ENTRIES = 1u << 17;        // per view of a call
 
-static int ensure_scratch(nsdf_model* m, size_t queue_entries) {
+static int ensure_scratch(nsdf_model* m, size_t queue_entries, size_t xqueue_entries) {
     cudaError_t e;
     if (!m->d_counters) {
         e = cudaMalloc(&m->d_counters, 8 * sizeof(unsigned int));
         if (e != cudaSuccess) return (int)e;
-        e = cudaMalloc(&m->d_xqueue, XQUEUE_ENTRIES * sizeof(StragglerEntry));
+    }
+    if (xqueue_entries > m->xqueue_capacity) {
+        if (m->d_xqueue) cudaFree(m->d_xqueue);
+        m->d_xqueue = nullptr;
+        m->xqueue_capacity = 0;
+        e = cudaMalloc(&m->d_xqueue, xqueue_entries * sizeof(StragglerEntry));
         if (e != cudaSuccess) return (int)e;
-        e = cudaMemset(m->d_xqueue, 0, XQUEUE_ENTRIES * sizeof(StragglerEntry));
+        e = cudaMemset(m->d_xqueue, 0, xqueue_entries * sizeof(StragglerEntry));
         if (e != cudaSuccess) return (int)e;
+        m->xqueue_capacity = xqueue_entries;
     }
     if (queue_entries > m->queue_capacity) {
         if (m->d_queue) cudaFree(m->d_queue);
@@ -66,6 +81,13 @@ void render_release(nsdf_model* m) {
     if (m->d_queue) cudaFree(m->d_queue);
     if (m->d_xqueue) cudaFree(m->d_xqueue);
     m->d_xqueue = nullptr;
+    m->xqueue_capacity = 0;
+    if (m->d_views) cudaFree(m->d_views);
+    m->d_views = nullptr;
+    m->views_capacity = 0;
+    if (m->d_frame_stage) cudaFree(m->d_frame_stage);
+    m->d_frame_stage = nullptr;
+    m->frame_stage_jobs = 0;
     if (m->d_stats_scratch) cudaFree(m->d_stats_scratch);
     if (m->d_tile_scratch) cudaFree(m->d_tile_scratch);
     m->d_tile_scratch = nullptr;
@@ -94,11 +116,11 @@ int scene_program_pack(const nsdf_scene_op* program, int n_ops, SceneProgram* ou
 }
 
 __global__ void __launch_bounds__(256) scene_eval_kernel(const __grid_constant__ SceneProgram prog, const float* __restrict__ xyz,
-                                                         const float* __restrict__ nsdf, int frame, int refmath,
+                                                         const float* __restrict__ nsdf, double zoff, int refmath,
                                                          float* __restrict__ out, int64_t n) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    out[i] = scene_program_eval(prog, f3{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}, nsdf[i], frame, refmath != 0);
+    out[i] = scene_program_eval(prog, f3{xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]}, nsdf[i], zoff, refmath != 0);
 }
 
 int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,
@@ -107,15 +129,18 @@ int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xy
     const int rc = scene_program_pack(program, n_ops, &prog);
     if (rc) return rc;
     if (n <= 0) return NSDF_OK;
-    scene_eval_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, stream>>>(prog, d_xyz, d_nsdf, frame,
+    scene_eval_kernel<<<(unsigned int)((n + 255) / 256), 256, 0, stream>>>(prog, d_xyz, d_nsdf, many_sphere_zoff(frame),
                                                                            math == NSDF_MATH_REFERENCE ? 1 : 0, d_out, n);
     return (int)cudaGetLastError();
 }
 
-int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream) {
     if (!m->fused || (m->in[0] != 3 && m->in[0] != 4)) return NSDF_EUNSUPPORTED;
+    if (n_views < 1 || n_views > 128) return NSDF_EINVAL;
+    if (n_views > 1 && (long long)W * H > (1LL << 24)) return NSDF_EINVAL;   // RaySlot::pix carries the view in its top byte
+    const nsdf_camera* cam = cams;
     // 4-input (x, y, z, t) nets: fp32 tracers only; t = the frame number (createBatch, volumeRender_kernel.cu:532-545)
     if (m->in[0] == 4 && (opts->flags & NSDF_RENDER_TC_FARFIELD)) return NSDF_EUNSUPPORTED;
     if (opts->tile_world < 1 || opts->tile_rank < 0 || opts->tile_rank >= opts->tile_world) return NSDF_EINVAL;
@@ -126,6 +151,10 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     std::memcpy(rp.cam.inv_view, cam->inv_view, sizeof(rp.cam.inv_view));
     std::memcpy(rp.cam.normal, cam->normal, sizeof(rp.cam.normal));
     rp.cam.frame = cam->frame;
+    rp.cam.zoff = many_sphere_zoff(cam->frame);
+    rp.n_views = n_views;
+    rp.views = nullptr;
+    rp.view_pixels = (unsigned int)((long long)W * H);
     rp.blob = m->d_blob;
     rp.n_sq = m->n_sq;
     rp.blob_bytes = m->blob_bytes;
@@ -150,8 +179,11 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.tile_world = opts->tile_world;
     const int my_tiles = (rp.n_tiles - opts->tile_rank + opts->tile_world - 1) / opts->tile_world;
     if (my_tiles <= 0) return NSDF_OK;
-    if ((long long)my_tiles * TILE_PIXELS >= (1LL << 32)) return NSDF_EINVAL;
-    rp.total_idx = (unsigned int)my_tiles * TILE_PIXELS;
+    const long long n_jobs_ll = (long long)my_tiles * n_views;       // job = (view, tile of this call)
+    if (n_jobs_ll * TILE_PIXELS >= (1LL << 32)) return NSDF_EINVAL;
+    const int n_jobs = (int)n_jobs_ll;
+    rp.my_tiles = my_tiles;
+    rp.total_idx = (unsigned int)n_jobs * TILE_PIXELS;
     rp.max_steps = opts->max_steps;
     rp.isolate_steps = env_int("NSDF_COOP_ISOLATE", 0);
     rp.marathon_steps = env_int("NSDF_COOP_MARATHON", 0);
@@ -163,6 +195,12 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     rp.express_lanes = 0u;
     rp.express_from_bulk = 0;
     rp.express_warps = env_int("NSDF_COOP_EXPRESS_WARPS", 4);
+    rp.express_rays = env_int("NSDF_COOP_EXPRESS_RAYS", 1);   // measured: several rays per lane slow the longest chains more than the extra lanes help
+    if (rp.express_rays < 1) rp.express_rays = 1;
+    if (rp.express_rays > 8) rp.express_rays = 8;
+    rp.express_solo_steps = env_int("NSDF_COOP_EXPRESS_SOLO", 768);
+    rp.tail_lanes = env_int("NSDF_COOP_TAIL_LANES", 0);   // measured neutral at 1080p and harmful for small frames: off
+    rp.tail_push_max = env_int("NSDF_COOP_TAIL_PUSH", 2);
     rp.express_steps_old = env_int("NSDF_COOP_EXPRESS_OLD", 192);      // older rays ask for a lane every 2nd step instead of every 16th:
     rp.express_check_old = env_int("NSDF_COOP_EXPRESS_OLD_MASK", 1);   // the lottery for a free lane favours them (median 11.9 -> 11.3 ms)
     rp.consumer_warps = env_int("NSDF_COOP_CONSUMER_WARPS", 0);
@@ -204,8 +242,49 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
             if (qcap > cap_max) qcap = cap_max;
         }
     }
-    int rc = ensure_scratch(m, qcap);
+    int rc = ensure_scratch(m, qcap, XQUEUE_ENTRIES * (size_t)n_views);
     if (rc) return rc;
+    const unsigned int xq_soft_cap = (unsigned int)(XQUEUE_ENTRIES * (size_t)n_views / 2);
+    if (n_views > 1) {
+        // batched views: only the cooperative single-launch schedule enumerates (view, tile) jobs
+        if (simple || farfield || !coop || hybrid) return NSDF_EUNSUPPORTED;
+        if ((size_t)n_views > m->views_capacity) {
+            if (m->d_views) cudaFree(m->d_views);
+            m->d_views = nullptr;
+            m->views_capacity = 0;
+            if (cudaMalloc(&m->d_views, (size_t)n_views * sizeof(Camera)) != cudaSuccess) return NSDF_ENOMEM;
+            m->views_capacity = (size_t)n_views;
+        }
+        std::vector<Camera> hv((size_t)n_views);
+        for (int v = 0; v < n_views; ++v) {
+            std::memcpy(hv[v].inv_view, cams[v].inv_view, sizeof(hv[v].inv_view));
+            std::memcpy(hv[v].normal, cams[v].normal, sizeof(hv[v].normal));
+            hv[v].frame = cams[v].frame;
+            hv[v].zoff = many_sphere_zoff(cams[v].frame);
+        }
+        cudaError_t ev = cudaMemcpyAsync(m->d_views, hv.data(), hv.size() * sizeof(Camera), cudaMemcpyHostToDevice, stream);
+        if (ev != cudaSuccess) return (int)ev;
+        ev = cudaStreamSynchronize(stream);   // hv is a local: the copy must have left it (a few KB, once per batch)
+        if (ev != cudaSuccess) return (int)ev;
+        rp.views = reinterpret_cast<const Camera*>(m->d_views);
+    }
+    // staged frame stores (render_kernels.cuh emit_pixel / flush_tile): for tile-partitioned calls, whose d_out is a peer
+    // GPU's memory in the multi-GPU gather, or on request
+    rp.stage = nullptr;
+    rp.tile_done = nullptr;
+    if (coop && !hybrid && !farfield && (opts->tile_world > 1 || (opts->flags & NSDF_RENDER_STAGED_STORES))) {
+        if ((size_t)n_jobs > m->frame_stage_jobs) {
+            if (m->d_frame_stage) cudaFree(m->d_frame_stage);
+            m->d_frame_stage = nullptr;
+            m->frame_stage_jobs = 0;
+            if (cudaMalloc(&m->d_frame_stage, (size_t)n_jobs * (TILE_PIXELS + 1) * sizeof(uint32_t)) != cudaSuccess) return NSDF_ENOMEM;
+            m->frame_stage_jobs = (size_t)n_jobs;
+        }
+        rp.stage = reinterpret_cast<uint32_t*>(m->d_frame_stage);
+        rp.tile_done = reinterpret_cast<unsigned int*>(m->d_frame_stage) + m->frame_stage_jobs * TILE_PIXELS;
+        cudaError_t es = cudaMemsetAsync(rp.tile_done, 0, (size_t)n_jobs * sizeof(unsigned int), stream);
+        if (es != cudaSuccess) return (int)es;
+    }
     rp.pixel_counter = m->d_counters;
     rp.queue = straggler ? reinterpret_cast<StragglerEntry*>(m->d_queue) : nullptr;
     rp.queue_capacity = straggler ? (unsigned int)qcap : 0u;
@@ -231,7 +310,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         if (e != cudaSuccess) return (int)e;
         e = cudaFuncSetAttribute(trace_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
         if (e != cudaSuccess) return (int)e;
-        e = cudaFuncSetAttribute(trace_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        e = cudaFuncSetAttribute(trace_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_done = true;
     }
@@ -242,19 +321,19 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
     // pixels (1080p: 18.5 -> 15.2 ms); neutral-to-negative for small frames (probe cost), for the two-pass schedule (its
     // second pass only starts after the bulk) and for the mixed-precision mode (already at one ray's chain).
     const int probe_steps = env_int("NSDF_TILE_PRIORITY_STEPS", 32);
-    const bool priority_default = coop && my_tiles >= env_int("NSDF_TILE_PRIORITY_MIN_TILES", 128);
+    const bool priority_default = coop && n_jobs >= env_int("NSDF_TILE_PRIORITY_MIN_TILES", 128);
     if (probe_steps > 0 && !simple && !only_latency && (priority_default || env_int("NSDF_TILE_PRIORITY_FORCE", 0))) {
-        if ((size_t)my_tiles > m->tile_scratch_capacity) {
+        if ((size_t)n_jobs > m->tile_scratch_capacity) {
             if (m->d_tile_scratch) cudaFree(m->d_tile_scratch);
             m->d_tile_scratch = nullptr;
             m->tile_scratch_capacity = 0;
-            e = cudaMalloc(&m->d_tile_scratch, 2 * (size_t)my_tiles * sizeof(int));
+            e = cudaMalloc(&m->d_tile_scratch, 2 * (size_t)n_jobs * sizeof(int));
             if (e != cudaSuccess) return (int)e;
-            m->tile_scratch_capacity = (size_t)my_tiles;
+            m->tile_scratch_capacity = (size_t)n_jobs;
         }
         int* d_score = m->d_tile_scratch;
         int* d_order = m->d_tile_scratch + m->tile_scratch_capacity;
-        e = cudaMemsetAsync(d_score, 0, (size_t)my_tiles * sizeof(int), stream);
+        e = cudaMemsetAsync(d_score, 0, (size_t)n_jobs * sizeof(int), stream);
         if (e != cudaSuccess) return (int)e;
         NSDF_PER_DEVICE_FLAG(probe_attr);
         if (!probe_attr) {
@@ -262,9 +341,9 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
             if (e != cudaSuccess) return (int)e;
             probe_attr = true;
         }
-        const unsigned int probes = (unsigned int)my_tiles * PROBES_PER_TILE;
-        tile_probe_kernel<<<(probes + 127u) / 128u, 128, m->blob_bytes, stream>>>(rp, my_tiles, probe_steps, d_score);
-        tile_sort_kernel<<<1, 256, 0, stream>>>(d_score, my_tiles, rp.tile_rank, rp.tile_world, d_order);
+        const unsigned int probes = (unsigned int)n_jobs * PROBES_PER_TILE;
+        tile_probe_kernel<<<(probes + 127u) / 128u, 128, m->blob_bytes, stream>>>(rp, n_jobs, probe_steps, d_score);
+        tile_sort_kernel<<<1, 256, 0, stream>>>(d_score, n_jobs, d_order);
         e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         rp.tile_order = d_order;
@@ -327,11 +406,10 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         rp2.express_from_bulk = 1;
         if (rp2.express_period > 0 && rp2.express_steps > 0) {
             rp2.xqueue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);
-            rp2.xqueue_soft_cap = (unsigned int)(XQUEUE_ENTRIES / 2);
-            rp2.express_lanes = ((unsigned int)sms / rp2.express_period) * (unsigned int)occ * (unsigned int)rp.express_warps;
+            rp2.xqueue_soft_cap = xq_soft_cap;
+            rp2.express_lanes = ((unsigned int)(sms * occ) / rp2.express_period) * (unsigned int)(rp.express_warps * rp.express_rays);
         }
-        trace_coop_kernel<<<sms * occ, COOP_THREADS, coop_smem(m), stream>>>(rp2);
-        return (int)cudaGetLastError();
+        return (int)launch_coop(rp2, (unsigned int)(sms * occ), coop_smem(m), stream);
     }
 
     if (coop) {
@@ -361,8 +439,8 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
         rp.express_from_bulk = env_int("NSDF_COOP_EXPRESS_FROM_BULK", 1);
         if (coop_queue && rp.express_period > 0 && rp.express_steps > 0) {
             rp.xqueue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);
-            rp.xqueue_soft_cap = (unsigned int)(XQUEUE_ENTRIES / 2);
-            rp.express_lanes = ((unsigned int)sms / rp.express_period) * (unsigned int)occ * (unsigned int)rp.express_warps;
+            rp.xqueue_soft_cap = xq_soft_cap;
+            rp.express_lanes = (cap / rp.express_period) * (unsigned int)(rp.express_warps * rp.express_rays);
         }
         if (hybrid && coop_queue) {
             rp.hybrid = env_int("NSDF_COOP_HYBRID", 8);   // a dry producer warp with <= this many rays hands them all over
@@ -372,8 +450,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
             const unsigned int quiet_sms = rp.consumer_period ? (unsigned int)sms / rp.consumer_period : 0u;
             rp.queue_room = opts->evict_steps > 0 ? 0u : (unsigned int)env_int("NSDF_COOP_ROOM", (int)(quiet_sms * 2u * per_cta));
         }
-        trace_coop_kernel<<<want < cap ? want : cap, COOP_THREADS, coop_smem(m), stream>>>(rp);
-        return (int)cudaGetLastError();
+        return (int)launch_coop(rp, want < cap ? want : cap, coop_smem(m), stream);
     }
 
     if (!two_kernel) {
@@ -425,7 +502,8 @@ int render_launch(nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matca
             rp2.total_idx = 0;
             rp2.consumer_period = 0;
             rp2.queue_static = 1;
-            trace_coop_kernel<<<sms * occ, COOP_THREADS, coop_smem(m), stream>>>(rp2);
+            e = launch_coop(rp2, (unsigned int)(sms * occ), coop_smem(m), stream);
+            if (e != cudaSuccess) return (int)e;
         } else {
             trace_latency_kernel<LAT_R><<<sms, LAT_THREADS, latency_smem(m), stream>>>(rp);
         }

@@ -38,7 +38,13 @@ struct StragglerEntry {            // 48 bytes, 16-byte aligned
 };
 
 struct RenderParams {
-    Camera cam;
+    Camera cam;                    // the view of a single-view call (n_views == 1); batched calls read views[]
+    int n_views;                   // views rendered by this launch (nsdf_render_views): their tails overlap each other's bulk
+    const Camera* views;           // device array [n_views] (global memory), null when n_views == 1
+    unsigned int view_pixels;      // W * H: view v's frame starts at out + v * view_pixels
+    int my_tiles;                  // tiles of ONE view this call renders; job g = view * my_tiles + tile slot
+    uint32_t* stage;               // staged frame stores (tile-partitioned calls): [job][64 x 64] finished pixels, flushed to `out`
+    unsigned int* tile_done;       //   as 16-byte row segments by the warp that completes a tile ([job] pixel counters); null = direct
     const float* blob;
     int n_sq;
     uint32_t blob_bytes;
@@ -49,8 +55,8 @@ struct RenderParams {
     int W, H;
     int tiles_x, n_tiles;
     int tile_rank, tile_world;
-    const int* tile_order;         // [j] = tile traced j-th by this call (tile_priority.cuh), or null: rank + j*world
-    unsigned int total_idx;        // pixel indices this call enumerates (my tiles * 4096)
+    const int* tile_order;         // [j] = job traced j-th by this call (tile_priority.cuh), or null: job j
+    unsigned int total_idx;        // pixel indices this call enumerates (jobs * 4096)
     int max_steps, evict_steps;
     int evict_steps_hi;            // fused kernel: unconditional hand-over (evict_steps applies while the backlog is short)
     unsigned int queue_room;       // fused kernel: backlog (tail - head) below which evict_steps applies
@@ -72,6 +78,10 @@ struct RenderParams {
     unsigned int express_period;   //   the warps 0..3 of every CTA on SMs with smid % express_period == express_period - 1 are express
     unsigned int express_lanes;    //   lanes: they hold ONE ray each, so that it marches at the 1-ray latency on a quiet scheduler
     int express_warps;             //   express lanes per CTA of an express SM (warps 0..express_warps-1)
+    int tail_lanes;                //   once the pixels are gone, warps 0..tail_lanes-1 of every CTA are lanes for the express queue (0 = off)
+    int tail_push_max;             //   and a warp outside them that is down to this many marching rays hands them over
+    int express_rays;              //   rays an express lane marches together (1..8)
+    int express_solo_steps;        //   a lane holding a ray with this many steps takes no further rays (0 = never alone by rule)
     int express_steps_old, express_check_old;   //   rays past express_steps_old steps ask for a lane whenever steps & express_check_old == 0
     int express_from_bulk;         //   producing warps hand rays over to free express lanes too (else only the consumers do)
     int timeline;                  // development: record the timeline of long rays (trace_coop.cuh g_timeline)
@@ -89,16 +99,19 @@ struct RenderParams {
 };
 
 // sceneSDF (volumeRender_kernel.cu:217-230) of this call: one of the two compiled scenes, or the op list
-// scene_pre_eval is the part that depends on the point alone: a marching warp takes it while the network is still evaluating.
-__device__ __forceinline__ float scene_pre_eval(const RenderParams& rp, f3 p) {
-    return scene_pre(rp.scene, p, rp.cam.frame);
+// The camera of view v: kernel parameters for a single-view call, a (cached) global array for a batch.
+__device__ __forceinline__ const Camera& view_cam(const RenderParams& rp, int view) {
+    return rp.n_views > 1 ? rp.views[view] : rp.cam;
 }
-__device__ __forceinline__ float scene_eval(const RenderParams& rp, f3 p, float nsdf, float pre) {
-    if (rp.scene == NSDF_SCENE_PROGRAM) return scene_program_eval(rp.prog, p, nsdf, rp.cam.frame, rp.refmath != 0);
-    return scene_sdf(rp.scene, p, nsdf, rp.cam.frame, rp.refmath != 0, pre);
-}
-__device__ __forceinline__ float scene_eval(const RenderParams& rp, f3 p, float nsdf) {
-    return scene_eval(rp, p, nsdf, scene_pre_eval(rp, p));
+// RaySlot::pix packs the view into the top byte: (view << 24) | (y * W + x); batched calls require W * H <= 2^24, views <= 128.
+__device__ __forceinline__ int slot_view(int packed) { return (int)((unsigned int)packed >> 24); }
+__device__ __forceinline__ int slot_pixel(int packed) { return packed & 0x00ffffff; }
+
+// rem: the ray's clearance state (device_math.cuh, many_sphere_union); pass a local -1 where no state is carried.
+__device__ __forceinline__ float scene_eval(const RenderParams& rp, int view, f3 p, float nsdf, float& rem) {
+    const double zoff = view_cam(rp, view).zoff;
+    if (rp.scene == NSDF_SCENE_PROGRAM) return scene_program_eval(rp.prog, p, nsdf, zoff, rp.refmath != 0);
+    return scene_sdf(rp.scene, p, nsdf, zoff, rp.refmath != 0, rem);
 }
 
 struct RaySlot {
@@ -108,18 +121,80 @@ struct RaySlot {
     f3 p, d;
     float tfar;
     float s0, s1, s2;
+    float rem;    // clearance to the scene's analytic parts at p (many_sphere_union), < 0 = unknown
 };
 
 struct LocalStats { unsigned int queries, hits, rays, evicted, unfinished, pixels; };
 
-__device__ __forceinline__ bool decode_pixel(const RenderParams& rp, unsigned int idx, int& x, int& y) {
+__device__ __forceinline__ bool decode_pixel(const RenderParams& rp, unsigned int idx, int& x, int& y, int& view) {
     const unsigned int j = idx / TILE_PIXELS, within = idx % TILE_PIXELS;
-    const int t = rp.tile_order ? __ldg(rp.tile_order + j) : rp.tile_rank + (int)j * rp.tile_world;
+    const int g = rp.tile_order ? __ldg(rp.tile_order + j) : (int)j;
+    view = g / rp.my_tiles;
+    const int t = rp.tile_rank + (g - view * rp.my_tiles) * rp.tile_world;
     const int tx = t % rp.tiles_x, ty = t / rp.tiles_x;
     const unsigned int sb = within >> 5, l = within & 31u;        // 8x4-pixel sub-blocks: one warp's first fill
     x = tx * TILE + (int)(sb & 7u) * 8 + (int)(l & 7u);
     y = ty * TILE + (int)(sb >> 3) * 4 + (int)(l >> 3);
     return x < rp.W && y < rp.H;
+}
+
+// ---- frame stores ---------------------------------------------------------------------------------------------------
+// Direct: one 4-byte store per finished pixel (the frame stays in L2 until the launch ends; ncu: DRAM write traffic below the
+// frame size).  Staged (rp.stage != null; tile-partitioned calls, whose `out` is a peer GPU's memory reached over NVLink): the
+// pixel goes to this GPU's staging tile and counts the tile down; the warp whose pixel completes the tile copies its 64 rows
+// to `out` as coalesced 16-byte stores (256 B per row), so that the frame gather is a few thousand 256-byte row writes
+// instead of millions of 4-byte ones, still inside the tracing kernel.
+// emit_pixel returns the job whose tile this pixel completed (the caller's WARP must then call flush_tile), or -1.
+__device__ __forceinline__ int emit_pixel(const RenderParams& rp, int packed, uint32_t color) {
+    const int view = slot_view(packed), pix = slot_pixel(packed);
+    if (!rp.stage) {
+        rp.out[(size_t)view * rp.view_pixels + pix] = color;
+        return -1;
+    }
+    const int x = pix % rp.W, y = pix / rp.W;
+    const int tx = x / TILE, ty = y / TILE;
+    const int t = ty * rp.tiles_x + tx;
+    const int g = view * rp.my_tiles + (t - rp.tile_rank) / rp.tile_world;
+    rp.stage[(size_t)g * TILE_PIXELS + (y - ty * TILE) * TILE + (x - tx * TILE)] = color;
+    __threadfence();
+    const int tw = min(TILE, rp.W - tx * TILE), th = min(TILE, rp.H - ty * TILE);
+    const unsigned int old = atomicAdd(rp.tile_done + g, 1u);
+    return (old + 1u == (unsigned int)(tw * th)) ? g : -1;
+}
+// All 32 lanes: copy the finished staging tile of job g to the frame.
+__device__ __forceinline__ void flush_tile(const RenderParams& rp, int g, int lane) {
+    __threadfence();
+    const int view = g / rp.my_tiles;
+    const int t = rp.tile_rank + (g - view * rp.my_tiles) * rp.tile_world;
+    const int x0 = (t % rp.tiles_x) * TILE, y0 = (t / rp.tiles_x) * TILE;
+    const int tw = min(TILE, rp.W - x0), th = min(TILE, rp.H - y0);
+    const uint32_t* src = rp.stage + (size_t)g * TILE_PIXELS;
+    uint32_t* dst = rp.out + (size_t)view * rp.view_pixels + (size_t)y0 * rp.W + x0;
+    if ((rp.W & 3) == 0 && (tw & 3) == 0 && (((size_t)rp.out) & 15) == 0) {
+        const int qpr = tw >> 2;                       // 16-byte segments per row
+        for (int i = lane; i < th * 16; i += 32) {
+            const int row = i >> 4, q = i & 15;
+            if (q < qpr) {
+                const uint4 v = __ldcg(reinterpret_cast<const uint4*>(src + row * TILE) + q);
+                reinterpret_cast<uint4*>(dst + (size_t)row * rp.W)[q] = v;
+            }
+        }
+    } else {
+        for (int i = lane; i < th * TILE; i += 32) {
+            const int row = i >> 6, c = i & 63;
+            if (c < tw) dst[(size_t)row * rp.W + c] = __ldcg(src + row * TILE + c);
+        }
+    }
+}
+// Warp-level epilogue of a step: flush every tile one of the lanes completed (flush_g = emit_pixel's result, -1 = none).
+__device__ __forceinline__ void flush_completed(const RenderParams& rp, int flush_g, int lane) {
+    if (!rp.stage) return;
+    unsigned int fm = __ballot_sync(0xffffffffu, flush_g >= 0);
+    while (fm) {
+        const int src = __ffs(fm) - 1;
+        flush_tile(rp, __shfl_sync(0xffffffffu, flush_g, src), lane);
+        fm &= fm - 1u;
+    }
 }
 
 // Point the network is asked about (createBatch, volumeRender_kernel.cu:526-545).
@@ -131,13 +206,18 @@ __device__ __forceinline__ f3 slot_query_point(const RaySlot& s) {
 }
 
 // singleMarch (volumeRender_kernel.cu:416-477) for one slot whose request returned `nsdf`.
-__device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const RenderParams& rp, LocalStats& st) {
+// flush_g receives the job whose staged tile this update completed (emit_pixel), else it is left alone.
+__device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const RenderParams& rp, LocalStats& st, int& flush_g) {
     ++st.queries;
+    const int view = slot_view(s.pix);
+    // q == s.p while marching; a tetrahedron vertex is 1.74e-5 away from it
+    float rem = s.mode > 0 ? s.rem - 2.0e-5f : s.rem;
 #ifdef NSDF_DEBUG_TSCALE   // development: every ray crawls and runs to max_steps (per-step latency probe)
-    const float sv = s.mode > 0 ? scene_eval(rp, q, nsdf) : scene_eval(rp, q, nsdf) * NSDF_DEBUG_TSCALE + 2e-6f;
+    const float sv = s.mode > 0 ? scene_eval(rp, view, q, nsdf, rem) : scene_eval(rp, view, q, nsdf, rem) * NSDF_DEBUG_TSCALE + 2e-6f;
 #else
-    const float sv = scene_eval(rp, q, nsdf);   // q == s.p while marching
+    const float sv = scene_eval(rp, view, q, nsdf, rem);
 #endif
+    if (s.mode <= 0) s.rem = rem;
     if (s.mode > 0) {
         if (s.mode == 1) s.s0 = sv;
         else if (s.mode == 2) s.s1 = sv;
@@ -145,8 +225,10 @@ __device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const 
         if (s.mode < 4) { ++s.mode; return; }
         const float sarr[4] = {s.s0, s.s1, s.s2, sv};
         const f3 n = tet_normal(sarr, rp.refmath != 0);
-        rp.out[s.pix] = (rp.color_type == NSDF_COLOR_FACING) ? facing_color(n, s.d, rp.refmath != 0)
-                                                             : matcap_color(rp.cam, n, rp.matcap, rp.mw, rp.mh, rp.refmath != 0);
+        const uint32_t color = (rp.color_type == NSDF_COLOR_FACING)
+                                   ? facing_color(n, s.d, rp.refmath != 0)
+                                   : matcap_color(view_cam(rp, view), n, rp.matcap, rp.mw, rp.mh, rp.refmath != 0);
+        flush_g = emit_pixel(rp, s.pix, color);
         ++st.hits;
         s.mode = -1;
         return;
@@ -155,31 +237,37 @@ __device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const 
     s.tfar = s.tfar - t;
     ++s.steps;
     if (s.tfar <= 0.0f) {             // left the march budget: background (:463-467)
-        rp.out[s.pix] = 0u;
+        flush_g = emit_pixel(rp, s.pix, 0u);
         s.mode = -1;
         return;
     }
     s.p = f3{fmaf(s.d.x, t, s.p.x), fmaf(s.d.y, t, s.p.y), fmaf(s.d.z, t, s.p.z)};
+    s.rem = s.rem - clearance_step(t);
     if (t < NSDF_MARCHING_EPSILON) s.mode = 1;
     if (s.steps >= rp.max_steps) {    // loop bound of render_kernel (:652): never shaded, stays 0
-        rp.out[s.pix] = 0u;
+        flush_g = emit_pixel(rp, s.pix, 0u);
         ++st.unfinished;
         s.mode = -1;
     }
 }
 
+__device__ __forceinline__ void slot_update(RaySlot& s, float nsdf, f3 q, const RenderParams& rp, LocalStats& st) {
+    int unused = -1;
+    slot_update(s, nsdf, q, rp, st, unused);   // direct stores only (the host never stages for the kernels that call this form)
+}
+
 // Starts the ray of enumeration index idx in slot s (initMarcher).  Returns with s.mode == -1 when
 // the pixel is outside the frame or misses the bounding sphere.
-__device__ __forceinline__ void slot_start(RaySlot& s, unsigned int idx, const RenderParams& rp, LocalStats& st) {
-    int x, y;
+__device__ __forceinline__ void slot_start(RaySlot& s, unsigned int idx, const RenderParams& rp, LocalStats& st, int& flush_g) {
+    int x, y, view;
     s.mode = -1;
-    if (!decode_pixel(rp, idx, x, y)) return;
+    if (!decode_pixel(rp, idx, x, y, view)) return;
     ++st.pixels;
-    const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H, rp.refmath != 0);
-    const int pix = y * rp.W + x;
-    if (!r.hit || rp.max_steps <= 0) { rp.out[pix] = 0u; return; }
+    const RayInit r = init_ray(view_cam(rp, view), x, y, rp.W, rp.H, rp.refmath != 0);
+    const int pix = (y * rp.W + x) | (view << 24);
+    if (!r.hit || rp.max_steps <= 0) { flush_g = emit_pixel(rp, pix, 0u); return; }
     ++st.rays;
-    s.pix = pix; s.steps = 0; s.mode = 0; s.p = r.p; s.d = r.d; s.tfar = r.tfar;
+    s.pix = pix; s.steps = 0; s.mode = 0; s.p = r.p; s.d = r.d; s.tfar = r.tfar; s.rem = -1.0f;
 }
 
 __device__ __forceinline__ void flush_stats(const LocalStats& st, nsdf_render_stats* g) {
@@ -204,6 +292,11 @@ __device__ __forceinline__ unsigned int lanemask_lt() {
     unsigned int m;
     asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
     return m;
+}
+
+__device__ __forceinline__ void slot_start(RaySlot& s, unsigned int idx, const RenderParams& rp, LocalStats& st) {
+    int unused = -1;
+    slot_start(s, idx, rp, st, unused);
 }
 
 // Warp-aggregated append of marching rays to the straggler queue.
@@ -330,7 +423,7 @@ __global__ void __launch_bounds__(512, 1) trace_latency_kernel(const __grid_cons
                         const float4 e0 = src[0], e1 = src[1], e2 = src[2];
                         slot.pix = __float_as_int(e0.x); slot.steps = __float_as_int(e0.y);
                         slot.p = f3{e0.z, e0.w, e1.x}; slot.d = f3{e1.y, e1.z, e1.w};
-                        slot.tfar = e2.x; slot.mode = 0;
+                        slot.tfar = e2.x; slot.mode = 0; slot.rem = -1.0f;
                     }
                 }
                 if (base + cnt >= n_queue) exhausted = true;

@@ -83,12 +83,11 @@ __device__ __forceinline__ float sdf_cylinder(f3 p, f3 c) {
 }
 
 // manySphere(p, nSDF, doUnion) (:176-196); the union form is many_sphere_union of device_math.cuh, bit for bit.
-__device__ __forceinline__ float many_sphere(f3 p, float nsdf, int frame, bool do_union, bool ref) {
-    if (do_union) return many_sphere_union(p, nsdf, frame, ref, many_sphere_dmin(p, frame));
+__device__ __forceinline__ float many_sphere(f3 p, float nsdf, double zoff, bool do_union, bool ref) {
+    if (do_union) { float rem = -1.0f; return many_sphere_union(p, nsdf, zoff, ref, rem); }
     float s = nsdf;
     float cx = p.x;
     float cy = (float)__dsub_rn((double)p.y, 0.6);
-    const double zoff = __dadd_rn(-0.7, __ddiv_rn(__dmul_rn((double)(frame * 2), 0.7), 360.0));
     const float cz = (float)__dadd_rn((double)p.z, zoff);
     const float zz = cz * cz;
 #pragma unroll 1
@@ -127,7 +126,7 @@ __device__ __forceinline__ float many_cylinder_cut(f3 p, float nsdf, bool ref) {
     return s;
 }
 
-__device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p, float nsdf, int frame, bool ref) {
+__device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p, float nsdf, double zoff, bool ref) {
     float s = 0.0f;
     const int n = prog.n_ops < SCENE_MAX_OPS ? prog.n_ops : SCENE_MAX_OPS;
 #pragma unroll 1
@@ -147,7 +146,7 @@ __device__ __noinline__ float scene_program_eval(const SceneProgram& prog, f3 p,
                 }
                 case MOD_ROUND: s = s - a[0]; break;
                 case MOD_ONION: s = fabsf(s) - a[0]; break;
-                case MOD_MANY_SPHERE: s = many_sphere(p, s, frame, a[0] != 0.0f, ref); break;
+                case MOD_MANY_SPHERE: s = many_sphere(p, s, zoff, a[0] != 0.0f, ref); break;
                 case MOD_MANY_CYLINDER_CUT: s = many_cylinder_cut(p, s, ref); break;
                 default: break;
             }

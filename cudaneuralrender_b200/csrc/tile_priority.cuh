@@ -27,7 +27,7 @@ constexpr int PROBE_STRIDE = 8;                                   // pixels betw
 constexpr int PROBES_PER_TILE = (TILE / PROBE_STRIDE) * (TILE / PROBE_STRIDE);   // 64
 constexpr int PROBE_MAX_SCORE = PROBES_PER_TILE;
 
-__global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__ RenderParams rp, int n_my_tiles, int probe_steps,
+__global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__ RenderParams rp, int n_jobs, int probe_steps,
                                                           int* __restrict__ tile_score) {
     extern __shared__ __align__(16) float s_w[];
     __shared__ uint64_t s_bar;
@@ -36,14 +36,15 @@ __global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__
     const int j = g / PROBES_PER_TILE, s = g % PROBES_PER_TILE;   // tile slot of this call, probe inside the tile
     bool marching = false;
     f3 p = {0.f, 0.f, 0.f}, d = {0.f, 0.f, 0.f};
-    float tfar = 0.f;
-    if (j < n_my_tiles) {
-        const int t = rp.tile_rank + j * rp.tile_world;
+    float tfar = 0.f, rem = -1.0f;
+    const int view = j < n_jobs ? j / rp.my_tiles : 0;
+    if (j < n_jobs) {
+        const int t = rp.tile_rank + (j - view * rp.my_tiles) * rp.tile_world;
         const int tx = t % rp.tiles_x, ty = t / rp.tiles_x;
         const int x = tx * TILE + (s % (TILE / PROBE_STRIDE)) * PROBE_STRIDE + PROBE_STRIDE / 2 - 1;
         const int y = ty * TILE + (s / (TILE / PROBE_STRIDE)) * PROBE_STRIDE + PROBE_STRIDE / 2 - 1;
         if (x < rp.W && y < rp.H) {
-            const RayInit r = init_ray(rp.cam, x, y, rp.W, rp.H, rp.refmath != 0);
+            const RayInit r = init_ray(view_cam(rp, view), x, y, rp.W, rp.H, rp.refmath != 0);
             if (r.hit) { marching = true; p = r.p; d = r.d; tfar = r.tfar; }
         }
     }
@@ -52,8 +53,9 @@ __global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__
         float x[1][3] = {{p.x, p.y, p.z}}, y[1];
         mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
         if (marching) {
-            const float t = scene_eval(rp, p, y[0]);
+            const float t = scene_eval(rp, view, p, y[0], rem);
             tfar = tfar - t;
+            rem = rem - clearance_step(t);
             if (tfar <= 0.0f || t < NSDF_MARCHING_EPSILON) marching = false;
             else p = f3{fmaf(d.x, t, p.x), fmaf(d.y, t, p.y), fmaf(d.z, t, p.z)};
         }
@@ -61,9 +63,9 @@ __global__ void __launch_bounds__(128) tile_probe_kernel(const __grid_constant__
     if (marching) atomicAdd(tile_score + j, 1);
 }
 
-// tile_order[rank among my tiles by descending score] = global tile id.  One block of 256 threads.
-__global__ void __launch_bounds__(256) tile_sort_kernel(const int* __restrict__ tile_score, int n_my_tiles, int tile_rank,
-                                                         int tile_world, int* __restrict__ tile_order) {
+// tile_order[rank among this call's jobs by descending score] = job (view * my_tiles + tile slot).  One block of 256 threads.
+__global__ void __launch_bounds__(256) tile_sort_kernel(const int* __restrict__ tile_score, int n_my_tiles,
+                                                         int* __restrict__ tile_order) {
     __shared__ int s_count[PROBE_MAX_SCORE + 1], s_start[PROBE_MAX_SCORE + 1];
     for (int i = threadIdx.x; i <= PROBE_MAX_SCORE; i += blockDim.x) s_count[i] = 0;
     __syncthreads();
@@ -82,7 +84,7 @@ __global__ void __launch_bounds__(256) tile_sort_kernel(const int* __restrict__ 
         int sc = tile_score[j];
         sc = sc < 0 ? 0 : (sc > PROBE_MAX_SCORE ? PROBE_MAX_SCORE : sc);
         const int pos = atomicAdd(&s_start[sc], 1);
-        tile_order[pos] = tile_rank + j * tile_world;
+        tile_order[pos] = j;
     }
 }
 

@@ -14,8 +14,8 @@
 // per step on a full SM); with fewer it drops to the lane = neuron evaluators for 8/4/2/1 rays, and a
 // warp left with one ray runs lone_ray_march (1.15 us per step when its SM is otherwise quiet).
 //
-// Serial tail: "express lanes".  Every express_period-th SM takes no pixels; warps 0..3 of its CTAs hold
-// ONE ray each, popped from the express queue.  Any other warp hands a ray that has marched
+// Serial tail: "express lanes".  Every express_period-th CTA (= SM: one CTA per SM, cooperative launch) takes no pixels; its
+// warps 0..3 hold ONE ray each, popped from the express queue.  Any other warp hands a ray that has marched
 // express_steps steps to that queue when a lane is free (three L2 counters), and keeps it otherwise.
 // The older scheme (quiet SMs consuming a main queue fed at evict_steps_hi steps) is still here for
 // callers that set evict_steps, for the hybrid schedule and for the second pass of the mixed-precision
@@ -48,8 +48,11 @@ __device__ __forceinline__ void timeline_event(int pix, int steps, int kind) {
     }
 }
 
-constexpr int COOP_THREADS = 256;
+constexpr int COOP_THREADS = 512;   // ONE CTA per SM (the launch pads its shared memory past half an SM): 16 warps, 4 per scheduler
 constexpr int COOP_R = 16;  // ray slots per warp (lanes 0..COOP_R-1 own them)
+// Shared memory a CTA asks for at least, so that two can never share an SM: roles are per CTA (= per SM), and an express
+// CTA's lone rays must have their schedulers to themselves.
+constexpr size_t COOP_MIN_SMEM = 116 * 1024;
 
 // Evaluates the K lowest-ranked active rays of the warp.  src[j] = lane of the j-th active ray.
 template <int K>
@@ -83,34 +86,39 @@ __device__ __forceinline__ void lone_ray_march(RaySlot& slot, int owner, const f
     d.z = __shfl_sync(0xffffffffu, slot.d.z, owner);
     float tfar = __shfl_sync(0xffffffffu, slot.tfar, owner);
     int steps = __shfl_sync(0xffffffffu, slot.steps, owner);
+    float rem = __shfl_sync(0xffffffffu, slot.rem, owner);
+    const int view = slot_view(__shfl_sync(0xffffffffu, slot.pix, owner));
     int mode = 0;
     bool background = false, unfinished = false;
     unsigned int q = 0;
 #pragma unroll 1
     for (int it = 0; it < max_iter; ++it) {
+        const float x[1][3] = {{p.x, p.y, p.z}};
         float y[1];
-        const float pre = scene_pre_eval(rp, p);   // point-only part of sceneSDF: off the dependent chain
-        y[0] = mlp32_eval_lone(s_w, n_sq, abuf, p.x, p.y, p.z, lane, rp.t4, rp.n_in == 4);
+        mlp32_eval_warp<1>(s_w, n_sq, abuf, x, y, lane, rp.t4, rp.n_in == 4);
         ++q;
 #ifdef NSDF_DEBUG_TSCALE
-        const float t = scene_eval(rp, p, y[0], pre) * NSDF_DEBUG_TSCALE + 2e-6f;
+        const float t = scene_eval(rp, view, p, y[0], rem) * NSDF_DEBUG_TSCALE + 2e-6f;
 #else
-        const float t = scene_eval(rp, p, y[0], pre);
+        const float t = scene_eval(rp, view, p, y[0], rem);
 #endif
         tfar = tfar - t;
         ++steps;
         if (tfar <= 0.0f) { background = true; mode = -1; break; }
         p = f3{fmaf(d.x, t, p.x), fmaf(d.y, t, p.y), fmaf(d.z, t, p.z)};
+        rem = rem - clearance_step(t);
         if (t < NSDF_MARCHING_EPSILON) mode = 1;
         if (steps >= rp.max_steps) { unfinished = true; mode = -1; break; }
         if (mode != 0) break;
     }
+    int flush_g = -1;
     if (lane == owner) {
-        slot.p = p; slot.tfar = tfar; slot.steps = steps; slot.mode = mode;
+        slot.p = p; slot.tfar = tfar; slot.steps = steps; slot.mode = mode; slot.rem = rem;
         st.queries += q;
-        if (background || unfinished) rp.out[slot.pix] = 0u;
+        if (background || unfinished) flush_g = emit_pixel(rp, slot.pix, 0u);
         if (unfinished) ++st.unfinished;
     }
+    flush_completed(rp, flush_g, lane);
 }
 
 __device__ __forceinline__ unsigned int sm_id() {
@@ -124,7 +132,7 @@ __device__ __forceinline__ unsigned int sm_id() {
 // rp.consumer_period-th SM, which take no pixels of their own -- a lone long ray there is not slowed
 // by busy neighbours.  Warps that run out of pixels join the consumers.  Termination: every warp has
 // stopped producing (pixel_counter[3] == all warps) and the queue is empty.
-__global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __grid_constant__ RenderParams rp) {
+__global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __grid_constant__ RenderParams rp) {
     extern __shared__ __align__(16) float s_w[];
     __shared__ uint64_t s_bar;
     stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
@@ -151,11 +159,15 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
     // a warp that marches one or two long rays is latency-bound and takes few issue slots from the 16-ray warps beside it)
     // express SMs (trace timeline: a lone ray steps in 1.14 us on an SM where nothing else runs, in 3.5 us beside the crowded
     // warps of a quiet SM, in 5.5 us beside 16-ray warps): warps 0..3 of their CTAs hold ONE ray each, taken from the express queue
-    const bool express_sm = use_queue && rp.xqueue && rp.express_period && (sm_id() % rp.express_period) == rp.express_period - 1;
+    // Roles go by CTA: the launch is cooperative with one CTA per SM, so CTA b has SM-wide resources to itself whichever SM it got.
+    // An express CTA's lanes are its warps 0..express_warps-1: with 4 of them each sits alone on its scheduler (measured,
+    // profiles/r02_lone_bench.txt: 1836 clocks per dependent evaluation with one lone warp per scheduler, 3097 with two).
+    const bool express_sm = use_queue && rp.xqueue && rp.express_period && (blockIdx.x % rp.express_period) == rp.express_period - 1;
     const bool express_lane = express_sm && warp < rp.express_warps;
-    bool producing = !(use_queue && (express_sm || (rp.consumer_period && (sm_id() % rp.consumer_period) == rp.consumer_period - 1) ||
+    bool producing = !(use_queue && (express_sm || (rp.consumer_period && (blockIdx.x % rp.consumer_period) == rp.consumer_period - 1) ||
                                      warp >= COOP_THREADS / 32 - rp.consumer_warps));
-    bool bulk_over = false, xbusy = false;   // warp-uniform
+    bool bulk_over = false;   // warp-uniform
+    int xcount = 0;           // express rays this lane holds (counted in pc[6]), warp-uniform
     unsigned int* const pc = rp.pixel_counter;
     const int pop_max = rp.pop_max > 0 && rp.pop_max < COOP_R ? rp.pop_max : COOP_R;
     bool exhausted = !producing;
@@ -211,7 +223,10 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
         // ---- refill idle ray slots (ballot compaction over the slot lanes); not while a long ray is on board
         const bool hold = rp.isolate_steps > 0 &&
                           __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.isolate_steps) != 0u;
+        int flush_g = -1;    // staged stores: job whose tile this lane completed in this iteration
         while (!exhausted && !hold) {
+            flush_completed(rp, flush_g, lane);
+            flush_g = -1;
             const bool need = lane < COOP_R && slot.mode < 0;
             const unsigned int m = __ballot_sync(0xffffffffu, need);
             if (!m) break;
@@ -224,14 +239,14 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
                 const unsigned int idx = base + __popc(m & lanemask_lt());
                 if (idx < n_src) {
                     if (!from_queue) {
-                        slot_start(slot, idx, rp, st);
+                        slot_start(slot, idx, rp, st, flush_g);
                     } else {   // a ray the far-field pass handed over: continue it from its current point
                         const float4* src = reinterpret_cast<const float4*>(rp.queue + idx);
                         const float4 e0 = __ldcg(src), e1 = __ldcg(src + 1);
                         const float tf = __ldcg(reinterpret_cast<const float*>(src + 2));
                         slot.pix = __float_as_int(e0.x); slot.steps = __float_as_int(e0.y);
                         slot.p = f3{e0.z, e0.w, e1.x}; slot.d = f3{e1.y, e1.z, e1.w};
-                        slot.tfar = tf; slot.mode = 0;
+                        slot.tfar = tf; slot.mode = 0; slot.rem = -1.0f;
                     }
                 }
             }
@@ -240,6 +255,8 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
                 if (rp.timeline && lane == 0) atomicMax(&g_timeline[1], global_ns());
             }
         }
+        flush_completed(rp, flush_g, lane);
+        flush_g = -1;
         unsigned int act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
         if (rp.xqueue && rp.express_steps > 0 && (!producing || rp.express_from_bulk) && !express_sm && !bulk_over) {
             // rays that have come this far move to an express lane, if one is free
@@ -266,6 +283,24 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
                 }
             }
         }
+        // ---- tail hand-over: when the pixels are gone, a frame's last milliseconds are a few hundred long rays scattered over all
+        // warps, 16 lone warps per SM stepping at a third of the speed four would (lone_bench: 6081 vs 1836 clocks per step).
+        // A warp that is not a lane (warp >= tail_lanes) and is down to tail_push_max marching rays hands them to the express
+        // queue; the lanes of all CTAs take them one at a time.
+        if (rp.xqueue && rp.tail_lanes > 0 && exhausted && !express_lane && warp >= rp.tail_lanes && act &&
+            __popc(act) <= rp.tail_push_max) {
+            const bool go = lane < COOP_R && slot.mode == 0;
+            const unsigned int gm = __ballot_sync(0xffffffffu, go);
+            if (gm) {
+                unsigned int ok = 0;
+                if (lane == 0) ok = (ld_volatile_u32(pc + 4) + 32u <= rp.xqueue_soft_cap) ? 1u : 0u;
+                if (__shfl_sync(0xffffffffu, ok, 0)) {
+                    if (rp.timeline && go) timeline_event(slot.pix, slot.steps, 104);
+                    queue_push(slot, go, rp.xqueue, pc + 4, rp, st);
+                    act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
+                }
+            }
+        }
         if (use_queue && exhausted) {
             if (producing && !act) {          // out of pixels and rays: from now on a consumer
                 producing = false;
@@ -279,26 +314,37 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             if (!producing && !marathon && (!act || --poll <= 0)) {
                 poll = 8;
                 if (express_sm) {
-                    if (xbusy && !act) {                       // the express ray of this lane is done
-                        if (lane == 0) atomicSub(pc + 6, 1u);
-                        xbusy = false;
+                    // an express lane marches up to express_rays rays together (lone_bench: 1836 clocks per step for one ray, 2594
+                    // for two, 3204 for four: four rays in a lane advance 2.3 x as many steps per second as one), but takes no
+                    // company once one of its rays has passed express_solo_steps: the frame's longest chains run alone
+                    const int now = __popc(act);
+                    if (xcount > now) {                        // express rays of this lane that have finished
+                        if (lane == 0) atomicSub(pc + 6, (unsigned int)(xcount - now));
+                        xcount = now;
                     }
-                    if (express_lane && !act) {
-                        const bool popped = queue_pop(slot, lane == 0, rp.xqueue, pc + 4, pc + 5, rp);
+                    const bool solo = rp.express_solo_steps > 0 &&
+                        __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_solo_steps) != 0u;
+                    if (express_lane && now < rp.express_rays && !solo) {
+                        const bool popped = queue_pop(slot, lane < rp.express_rays && slot.mode < 0, rp.xqueue, pc + 4, pc + 5, rp);
                         if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 103);
-                        if (__ballot_sync(0xffffffffu, popped)) {
-                            xbusy = true;
-                            if (lane == 0) atomicAdd(pc + 6, 1u);
+                        const int got = __popc(__ballot_sync(0xffffffffu, popped));
+                        if (got) {
+                            xcount += got;
+                            if (lane == 0) atomicAdd(pc + 6, (unsigned int)got);
                         }
                     }
                     // once every warp is out of pixels an express SM consumes like any other
-                    if (bulk_over && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
+                    if (bulk_over && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0)) {
                         fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
+                        if (!express_lane && warp < rp.tail_lanes && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
+                            queue_pop(slot, lane == 0, rp.xqueue, pc + 4, pc + 5, rp);
+                    }
                 } else {
                     const bool popped = fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
                     if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 101);
-                    // leftovers of the express queue once its lanes may have gone
-                    if (rp.xqueue && bulk_over && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
+                    // tail of the frame: once every warp is out of pixels, warps 0..tail_lanes-1 of EVERY CTA are lanes for the
+                    // express queue (one lone ray each: up to four per SM step at full speed, lone_bench), fed by tail_handover below
+                    if (rp.xqueue && bulk_over && warp < rp.tail_lanes && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
                         queue_pop(slot, lane == 0, rp.xqueue, pc + 4, pc + 5, rp);
                 }
                 act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
@@ -360,7 +406,8 @@ __global__ void __launch_bounds__(COOP_THREADS, 2) trace_coop_kernel(const __gri
             else if (na == 2) mine = coop_eval<2>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
             else mine = coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
         }
-        if (active) slot_update(slot, mine, q, rp, st);
+        if (active) slot_update(slot, mine, q, rp, st, flush_g);
+        flush_completed(rp, flush_g, lane);
         if (rp.timeline && active && slot.mode == 0 && slot.steps >= 256 && (slot.steps & 255) == 0) timeline_event(slot.pix, slot.steps, na);
         // ---- long rays leave for the quiet SMs
         if (use_queue && producing)

@@ -98,7 +98,7 @@ __device__ __forceinline__ bool queue_pop(RaySlot& s, bool want, const Straggler
         const float tf = __ldcg(reinterpret_cast<const float*>(src + 2));
         s.pix = __float_as_int(e0.x); s.steps = __float_as_int(e0.y);
         s.p = f3{e0.z, e0.w, e1.x}; s.d = f3{e1.y, e1.z, e1.w};
-        s.tfar = tf; s.mode = 0;
+        s.tfar = tf; s.mode = 0; s.rem = -1.0f;
     }
     return mine;
 }

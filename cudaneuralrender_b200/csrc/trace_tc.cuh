@@ -133,7 +133,8 @@ trace_tc_kernel(const __grid_constant__ RenderParams rp, const TraceTcParams tp)
         bool hand_over = false;
         if (active) {
             ++st.queries;
-            const float t = scene_eval(rp, slot.p, nsdf);
+            float rem_unused = -1.0f;
+            const float t = scene_eval(rp, 0, slot.p, nsdf, rem_unused);
             if (t >= tp.thr) {
                 const float ts = t - tp.margin;
                 slot.tfar = slot.tfar - ts;

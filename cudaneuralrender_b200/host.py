@@ -455,6 +455,30 @@ def render_kernel(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNe
                "nsdf_render")
 
 
+def view_cameras(views, frames=None):
+    """[(rx_deg, ry_deg) ...] (+ optional frame numbers) -> (Camera * n) array: updateViewMatrices (src/main.cpp:207-222) per view,
+    default viewTranslation (0, 0, -2)."""
+    n = len(views)
+    arr = (Camera * n)()
+    for i, (rx, ry) in enumerate(views):
+        capi.lib().nsdf_camera_from_view(float(rx), float(ry), 0.0, 0.0, -2.0, int(frames[i]) if frames is not None else 0,
+                                         C.byref(arr[i]))
+    return arr
+
+
+def render_views(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNetwork, cams, matcap: Optional[Image] = None,
+                 stats: Optional[torch.Tensor] = None, tile_rank: int = 0, tile_world: int = 1):
+    """nsdf_render_views: len(cams) frames in ONE persistent launch (the `--spin` loop of src/main.cpp:470-478 as a batch);
+    view v lands in d_output[v*W*H : (v+1)*W*H].  cams: (Camera * n) from view_cameras()."""
+    opts = _opts(tile_rank, tile_world)
+    mat_ptr, mw, mh = None, 0, 0
+    if matcap is not None and matcap.deviceData is not None:
+        mat_ptr, mw, mh = matcap.deviceData.data_ptr(), matcap.shape.x, matcap.shape.y
+    capi.check(capi.lib().nsdf_render_views(nn.handle(), cams, len(cams), mat_ptr, mw, mh, C.byref(opts), d_output.data_ptr(),
+                                            imageW, imageH, stats.data_ptr() if stats is not None else None, _stream_ptr()),
+               "nsdf_render_views")
+
+
 def render_host(nn: NeuralNetwork, imageW: int, imageH: int, matcap: Optional[np.ndarray] = None):
     """Host-buffer call (nsdf_render_host): uploads the matcap, renders, returns (uint32[H,W], stats dict)."""
     opts = _opts()

@@ -217,6 +217,9 @@ typedef struct nsdf_render_opts {
 #define NSDF_RENDER_TC_FARFIELD 128u    /* mixed precision: march on the tensor cores while t >= threshold (fp16x3 rung,
                                            |error| <= 1e-4), hand every ray that gets close to the surface to the fp32 path
                                            (accept test, normals, shading unchanged).  Not bit-identical to the default. */
+#define NSDF_RENDER_STAGED_STORES 1024u /* finished pixels go to a staging tile and every completed 64x64 tile is copied to d_out as 16-byte
+                                           row segments by the warp that completes it; always on for tile-partitioned calls
+                                           (tile_world > 1, where d_out is usually a peer GPU's memory), optional otherwise          */
 #define NSDF_RENDER_PHASE_LATENCY 8u    /* launch only the latency kernel on the queue a PHASE_THROUGHPUT call
                                            of the same model handle left behind (per-kernel timing)            */
 
@@ -250,10 +253,20 @@ void nsdf_camera_from_view(float rx_deg, float ry_deg, float tx, float ty, float
 int nsdf_render(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
                 const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                 void* stream);
+/* n_views frames in ONE persistent launch (the multi-view loop of src/main.cpp:470-478, `--spin`): view v is rendered with
+ * cams[v] (HOST array) into d_out + v * W * H.  The (view, tile) jobs of all views share the launch, so the serial tail of one
+ * view (a handful of rays with thousands of dependent steps) hides behind the bulk of the others instead of idling the GPU
+ * once per frame.  1 <= n_views <= 128, W * H <= 2^24 for n_views > 1; frames are bit-identical to n_views calls of
+ * nsdf_render.  Only the default schedule (opts->flags without the A/B bits). */
+int nsdf_render_views(const nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
+                      const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream);
 /* Host-buffer variant: uploads the matcap, renders, copies the frame back; synchronous.
  * h_stats may be NULL. */
 int nsdf_render_host(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* h_matcap, int mw, int mh,
                      const nsdf_render_opts* opts, uint32_t* h_out, int W, int H, nsdf_render_stats* h_stats);
+/* Host-buffer variant of nsdf_render_views: h_out receives n_views * W * H texels. */
+int nsdf_render_views_host(const nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* h_matcap, int mw, int mh,
+                           const nsdf_render_opts* opts, uint32_t* h_out, int W, int H, nsdf_render_stats* h_stats);
 
 /* ---- multi-GPU frame gather over NVLink (one process per GPU) --------------------------------
  * The presenting rank exports its frame buffer; the other ranks open it and pass the mapped

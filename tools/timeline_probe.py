@@ -7,13 +7,17 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from cudaneuralrender_b200 import host, _capi as capi
 model, W, H = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
+scene, ry = host.SCENE_TANH, 0.0
 for kv in sys.argv[4:]:
-    k, v = kv.split("="); os.environ[k] = v
+    k, v = kv.split("=")
+    if k == "SCENE": scene = int(v)          # 0 tanh, 1 manySphere (the reference's HEAD)
+    elif k == "RY": ry = float(v)
+    else: os.environ[k] = v
 nn = host.NeuralNetwork(); assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"))
 matcap = host.Image(); assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", "blue.png"))
 host.copyStaticSettings(host.COLOR_MATCAP, 3)
-host.updateViewMatrices((0.0, 0.0, 0.0), (0.0, 0.0, -2.0), 0)
-host.setSceneOptions(host.SCENE_TANH, 6000, 0, 0)
+host.updateViewMatrices((0.0, ry, 0.0), (0.0, 0.0, -2.0), 0)
+host.setSceneOptions(scene, 6000, 0, 0, host.MATH_REFERENCE)
 frame = torch.zeros(W * H, dtype=torch.int32, device="cuda")
 for _ in range(3): host.render_kernel(frame, W, H, nn, matcap)
 torch.cuda.synchronize()
@@ -50,6 +54,6 @@ for pix in longest:
     prev = None
     for t, _, steps, kind in rows:
         rate = "" if prev is None or steps == prev[1] else f"  {(t - prev[0]) / (steps - prev[1]):.0f} ns/step"
-        if kind in (100, 101, 102, 103) or steps % 1024 < 64 or steps < 1100:
-            print(f"   t {(t - t0) / 1e6:7.3f} ms  steps {steps:5d}  { {100: 'pushed', 101: 'popped', 102: 'pushed to express', 103: 'popped by express lane'}.get(int(kind), 'rays in warp ' + str(kind)) }{rate}")
+        if kind in (100, 101, 102, 103, 104) or steps % 1024 < 64 or steps < 1100:
+            print(f"   t {(t - t0) / 1e6:7.3f} ms  steps {steps:5d}  { {100: 'pushed', 101: 'popped', 102: 'pushed to express', 103: 'popped by express lane', 104: 'handed over (tail)'}.get(int(kind), 'rays in warp ' + str(kind)) }{rate}")
         prev = (t, steps)
