@@ -93,6 +93,10 @@ PROTOTYPES = {
                                     C.POINTER(RenderStats)]),
     "nsdf_render_host": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i,
                               C.POINTER(RenderStats)]),
+    "nsdf_multi_create": (_i, [_vp, _ip, _i, C.POINTER(_vp)]),
+    "nsdf_multi_destroy": (None, [_vp]),
+    "nsdf_multi_device_count": (_i, [_vp]),
+    "nsdf_multi_render": (_i, [_vp, C.POINTER(Camera), _i, _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, C.POINTER(RenderStats)]),
     "nsdf_ipc_export": (_i, [_vp, C.c_char_p]),
     "nsdf_ipc_open": (_i, [C.c_char_p, C.POINTER(_vp)]),
     "nsdf_ipc_close": (_i, [_vp]),

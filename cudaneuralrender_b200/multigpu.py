@@ -169,3 +169,48 @@ def render_frame_tiled(nn, matcap, W: int, H: int, frame: PeerFrame, stats=None)
 
     host.render_kernel(None, W, H, nn, matcap, stats=stats, tile_rank=frame.rank, tile_world=frame.world,
                        d_output_ptr=frame.ptr)
+
+
+# ---- one process, several GPUs (nsdf_multi_*) ---------------------------------------------------------------------------
+class MultiRenderer:
+    """nsdf_multi: the network cloned onto `devices`; devices[0] presents.  render() partitions ONE view by 64x64 tiles (every
+    device's tracer stores its tiles into the presenting device's frame over NVLink) and SEVERAL views by view (v -> device
+    v % n, gathered with peer copies).  No torch.distributed: a single host thread drives all devices."""
+
+    def __init__(self, nn, devices: Sequence[int]):
+        import ctypes as C
+
+        from . import _capi as capi
+
+        self._capi, self._C = capi, C
+        self.devices = list(devices)
+        self._h = C.c_void_p(None)
+        arr = (C.c_int * len(self.devices))(*self.devices)
+        capi.check(capi.lib().nsdf_multi_create(nn.handle(), arr, len(self.devices), C.byref(self._h)), "nsdf_multi_create")
+
+    def render(self, d_output, W: int, H: int, cams, matcap: Optional[np.ndarray] = None, opts=None):
+        """d_output: int32/uint32 tensor of len(cams) * W * H texels on devices[0].  cams: (Camera * n), host.view_cameras().
+        matcap: uint32[mh, mw] HOST array or None.  Returns the stats dict (totals over the devices).  Synchronous."""
+        from . import host
+
+        capi, C = self._capi, self._C
+        o = opts if opts is not None else host._opts()
+        st = capi.RenderStats()
+        mp, mw, mh = None, 0, 0
+        if matcap is not None:
+            matcap = np.ascontiguousarray(matcap, dtype=np.uint32)
+            mp, mh, mw = matcap.ctypes.data, matcap.shape[0], matcap.shape[1]
+        capi.check(capi.lib().nsdf_multi_render(self._h, cams, len(cams), mp, mw, mh, C.byref(o), d_output.data_ptr(), W, H,
+                                                C.byref(st)), "nsdf_multi_render")
+        return {k: int(getattr(st, k)) for k, _ in capi.RenderStats._fields_}
+
+    def close(self):
+        if self._h:
+            self._capi.lib().nsdf_multi_destroy(self._h)
+            self._h = self._C.c_void_p(None)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

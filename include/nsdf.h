@@ -14,6 +14,11 @@
  *   - `stream` is a cudaStream_t passed as void* (NULL = default stream).  Calls that take a
  *     stream are asynchronous with respect to the host unless stated otherwise.
  *   - A model handle belongs to the device that was current when it was created.
+ *   - ONE render at a time per model handle: the tracer's queues, counters and staging buffers are scratch of the handle
+ *     (the reference keeps file-scope globals, src/volumeRender_kernel.cu:578-585).  Use one handle per stream / thread;
+ *     nsdf_multi_* holds one per device.  The tracer is launched cooperatively (cudaLaunchCooperativeKernel, one CTA per SM):
+ *     its warps wait on one another, so the launch either gets the whole grid resident or fails with a CUDA error -- it
+ *     never spins on CTAs that cannot run.
  * ===================================================================================== */
 #ifndef NSDF_H_
 #define NSDF_H_
@@ -275,6 +280,23 @@ int nsdf_render_views_host(const nsdf_model* m, const nsdf_camera* cams, int n_v
 int nsdf_ipc_export(void* d_ptr, unsigned char handle_out[NSDF_IPC_HANDLE_BYTES]);
 int nsdf_ipc_open(const unsigned char handle[NSDF_IPC_HANDLE_BYTES], void** d_ptr_out);
 int nsdf_ipc_close(void* d_ptr);
+
+/* ---- one process, several GPUs ------------------------------------------------------------------------------
+ * The reference drives one device from one host thread.  nsdf_multi clones a network onto the listed devices
+ * (devices[0] presents: d_out of nsdf_multi_render lives there; every other device needs peer access to it, else
+ * NSDF_EUNSUPPORTED).
+ *   n_views == 1 : the frame is partitioned by 64x64 tiles, tile t -> device t % n; each device's tracer stores its finished
+ *                  tiles straight into d_out over NVLink (256-byte row segments from inside the kernel).
+ *   n_views  > 1 : view v -> device v % n (the `--spin` loop of src/main.cpp:470-478 spread over the devices); each device
+ *                  renders its views in one persistent launch and copies them to d_out + v * W * H on the presenting device.
+ * h_matcap is a HOST array (uploaded to every device); opts->tile_rank / tile_world must be 0 / 1.  Synchronous.  Frames are
+ * bit-identical to nsdf_render on one device.  h_stats (may be NULL) receives the totals over all devices. */
+typedef struct nsdf_multi nsdf_multi;
+int nsdf_multi_create(const nsdf_model* m, const int* devices, int n_devices, nsdf_multi** out);
+void nsdf_multi_destroy(nsdf_multi* mm);
+int nsdf_multi_device_count(const nsdf_multi* mm);
+int nsdf_multi_render(nsdf_multi* mm, const nsdf_camera* cams, int n_views, const uint32_t* h_matcap, int mw, int mh,
+                      const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* h_stats);
 
 /* ---- image I/O used by the drop-in executables (src/neuralUtils/image.cu:36-110,
  * src/common/helper_image.h:252-329) ------------------------------------------------------------ */

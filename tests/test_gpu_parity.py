@@ -636,6 +636,49 @@ def test_full_size_4k_band_against_oracle(env):
     assert int((ref["image"][1024:1088] != 0).sum()) > 1000
 
 
+def test_batched_views_and_staged_stores(env):
+    """nsdf_render_views (n views in ONE persistent launch) == n calls of nsdf_render, bytewise and in the query count, in both
+    scenes; the staged 16-byte tile stores (NSDF_RENDER_STAGED_STORES, always on for tile partitions) == the direct stores, for a
+    frame whose width is not a multiple of 4 as well; per-view frame numbers animate the manySphere scene per view."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "plane_1")
+    W, H = 200, 136
+    views = [(0.0, 0.0), (10.0, 45.0), (-20.0, 200.0), (0.0, 300.0), (5.0, 123.0)]
+    frames_no = [0, 3, 40, 0, 7]
+    host.copyStaticSettings(host.COLOR_FACING, 3)
+    for scene in (host.SCENE_TANH, host.SCENE_MANYSPHERE):
+        host.setSceneOptions(scene, 6000)
+        ref = torch.zeros(len(views) * W * H, dtype=torch.int32, device="cuda")
+        st1 = torch.zeros(6, dtype=torch.int64, device="cuda")
+        for v, (rx, ry) in enumerate(views):
+            host.updateViewMatrices((rx, ry, 0.0), (0.0, 0.0, -2.0), frames_no[v])
+            host.render_kernel(ref[v * W * H:(v + 1) * W * H], W, H, nn, stats=st1)
+        out = torch.full_like(ref, 0x55)
+        st2 = torch.zeros(6, dtype=torch.int64, device="cuda")
+        host.render_views(out, W, H, nn, host.view_cameras(views, frames_no), stats=st2)
+        assert torch.equal(out, ref), scene
+        assert torch.equal(st1, st2)
+        # views of a batch, tile-partitioned three ways (staged stores)
+        out3 = torch.full_like(ref, 0x55)
+        for r in range(3):
+            host.render_views(out3, W, H, nn, host.view_cameras(views, frames_no), tile_rank=r, tile_world=3)
+        assert torch.equal(out3, ref), scene
+        # one view against the oracle
+        iv, nm = oracle.view_matrices(10.0, 45.0)
+        o = oracle.render(om, iv, nm, W, H, scene=oracle.SCENE_TANH if scene == host.SCENE_TANH else oracle.SCENE_MANYSPHERE, frame=3)
+        assert np.array_equal(out[W * H:2 * W * H].cpu().numpy().view(np.uint32).reshape(H, W), o["image"])
+    for (W2, H2) in ((200, 136), (203, 77), (64, 64)):
+        host.setSceneOptions(host.SCENE_MANYSPHERE, 6000)
+        host.updateViewMatrices((0.0, 30.0, 0.0), (0.0, 0.0, -2.0), 0)
+        a = torch.zeros(W2 * H2, dtype=torch.int32, device="cuda")
+        host.render_kernel(a, W2, H2, nn)
+        host.setSceneOptions(host.SCENE_MANYSPHERE, 6000, host.capi.RENDER_STAGED_STORES)
+        b = torch.full_like(a, 0x55)
+        host.render_kernel(b, W2, H2, nn)
+        assert torch.equal(a, b), (W2, H2)
+    host.setSceneOptions()
+
+
 def test_error_behaviour(env):
     torch, host = env["torch"], env["host"]
     from cudaneuralrender_b200 import _capi

@@ -49,6 +49,51 @@ def test_peer_frame_world1_and_emulated_ranks(gpu):
     f.close()
 
 
+def test_multi_renderer_one_device(gpu):
+    """nsdf_multi_* with a single device: same frames as nsdf_render / nsdf_render_views (runs on the 1-GPU box)."""
+    from cudaneuralrender_b200 import multigpu
+    from oracle import oracle
+    host, nn, mc = _setup()
+    host.setSceneOptions(host.SCENE_MANYSPHERE, 6000, 0, 0, host.MATH_REFERENCE)
+    W, H = 200, 136
+    views = [(0.0, 30.0), (10.0, 200.0), (0.0, 0.0)]
+    ref = torch.zeros(len(views) * W * H, dtype=torch.int32, device="cuda")
+    host.render_views(ref, W, H, nn, host.view_cameras(views), mc)
+    mr = multigpu.MultiRenderer(nn, [0])
+    matcap_np = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    out = torch.full_like(ref, 0x55)
+    st = mr.render(out, W, H, host.view_cameras(views), matcap_np)
+    assert torch.equal(out, ref) and st["pixels"] == len(views) * W * H
+    one = torch.full((W * H,), 0x55, dtype=torch.int32, device="cuda")
+    mr.render(one, W, H, host.view_cameras(views[:1]), matcap_np)
+    assert torch.equal(one, ref[:W * H])
+    mr.close()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_multi_renderer_over_all_gpus(gpu):
+    """One process, all GPUs of the box: a frame partitioned by tiles (peer stores over NVLink from inside the tracer) and a
+    turntable partitioned by views are bytewise equal to the single-GPU frames."""
+    from cudaneuralrender_b200 import multigpu
+    from oracle import oracle
+    host, nn, mc = _setup()
+    host.setSceneOptions(host.SCENE_MANYSPHERE, 6000, 0, 0, host.MATH_REFERENCE)
+    matcap_np = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    n = torch.cuda.device_count()
+    mr = multigpu.MultiRenderer(nn, list(range(n)))
+    for (W, H) in ((1000, 520), (203, 77)):
+        views = [(0.0, 5.625 * k) for k in range(2 * n + 1)]
+        ref = torch.zeros(len(views) * W * H, dtype=torch.int32, device="cuda")
+        host.render_views(ref, W, H, nn, host.view_cameras(views), mc)
+        out = torch.full_like(ref, 0x55)
+        st = mr.render(out, W, H, host.view_cameras(views), matcap_np)
+        assert torch.equal(out, ref) and st["pixels"] == len(views) * W * H, (W, H)
+        one = torch.full((W * H,), 0x55, dtype=torch.int32, device="cuda")
+        st = mr.render(one, W, H, host.view_cameras(views[:1]), matcap_np)
+        assert torch.equal(one, ref[:W * H]) and st["pixels"] == W * H, (W, H)
+    mr.close()
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_tiles_over_two_gpus_match_single(gpu):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
@@ -57,5 +102,6 @@ def test_tiles_over_two_gpus_match_single(gpu):
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert out.returncode == 0, out.stderr[-2000:]
     line = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][-1])
-    assert line["n_gpus"] == 2 and line["tiles_equal_single_gpu"] is True
-    assert line["tile_balance_queries"] > 0.9
+    leg = line["frame4k_tiles"]
+    assert line["n_gpus"] == 2 and leg["tiles_equal_single_gpu"] is True
+    assert leg["tile_balance_queries"] > 0.9
