@@ -6,13 +6,75 @@
 // viewRotation.y = i and frameNumber = i (doABarrelRoll :470-478).  Output: <prefix><basename>.png with the
 // reference's 180-degree turn (Image::savePNG), and the same frame as PPM with --ppm.
 // Extra flags: --ppm, --scene manysphere|tanh|round|displace|sphere|cylindercut|spherecut (scene programs; default manysphere = HEAD), --math reference|deterministic, --max-steps N, --precision N (NSDF_PREC_*), --views N
-// (turntable of N views instead of 360), --gpu K (device ordinal), --stats.
+// (turntable of N views instead of 360), --gpu K (device ordinal), --gpus N (one process drives N devices: a single frame is
+// partitioned by 64x64 tiles, a turntable by views; nsdf_multi_*), --batch B (views per persistent launch and device,
+// default 16), --stats.
+// A turntable is rendered in batches (nsdf_render_views: the serial tail of one view hides behind the bulk of the others)
+// while host threads encode and write the previous batch's PNG files, so the GPU never waits for the encoder.
+#include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <condition_variable>
 #include <cstring>
+#include <deque>
 #include <iostream>
+#include <memory>
+#include <mutex>
 #include <string>
+#include <thread>
+#include <vector>
 #include "volumeRender.hh"
+
+namespace {
+// Frames handed to host threads: Image::savePNG (src/neuralUtils/image.cu:67-110) + the optional PPM, off the render loop.
+class FrameWriter {
+public:
+    explicit FrameWriter(int n_threads) {
+        for (int i = 0; i < n_threads; ++i) workers_.emplace_back([this] { run(); });
+    }
+    ~FrameWriter() { finish(); }
+    void push(std::string name, std::shared_ptr<Image> img, bool ppm) {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            q_.push_back(Job{std::move(name), std::move(img), ppm});
+        }
+        cv_.notify_one();
+    }
+    bool finish() {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            if (done_) return ok_;
+            done_ = true;
+        }
+        cv_.notify_all();
+        for (auto& t : workers_) t.join();
+        return ok_;
+    }
+
+private:
+    struct Job { std::string name; std::shared_ptr<Image> img; bool ppm; };
+    void run() {
+        for (;;) {
+            Job j;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [this] { return done_ || !q_.empty(); });
+                if (q_.empty()) return;
+                j = std::move(q_.front());
+                q_.pop_front();
+            }
+            bool ok = j.img->savePNG(j.name + ".png");
+            if (ok && j.ppm) ok = j.img->savePPM(j.name + ".ppm");
+            if (!ok) { std::lock_guard<std::mutex> lk(m_); ok_ = false; }
+        }
+    }
+    std::mutex m_;
+    std::condition_variable cv_;
+    std::deque<Job> q_;
+    std::vector<std::thread> workers_;
+    bool done_ = false, ok_ = true;
+};
+}  // namespace
 
 static char* getCmdOption(char** begin, char** end, const std::string& option) {
     for (char** it = begin; it != end; ++it)
@@ -36,7 +98,7 @@ static void usage() {
                  "\t--spin 360 frames (or --views N) rotating about y\n"
                  "\t--animation 4-input (xyzt) networks\n"
                  "\t--ppm also write <name>.ppm   --scene manysphere|tanh|round|displace|sphere|cylindercut|spherecut   --math reference|deterministic   --max-steps N   --precision N\n"
-                 "\t--gpu K   --stats   -h (--help)\n";
+                 "\t--gpu K   --gpus N (tiles of one frame / views of a turntable over N devices)   --batch B   --stats   -h (--help)\n";
 }
 static int countDigit(int n) {
     int c = 0;
@@ -109,45 +171,89 @@ int main(int argc, char** argv) {
     setMathMode(mathMode);
     if (progOps) setSceneProgram(prog, progOps);
 
-    uint* d_output = nullptr;
-    nsdfCheck(nsdf_dev_malloc(reinterpret_cast<void**>(&d_output), (size_t)width * height * sizeof(uint)));
-    Image out(width, height, true);
-    out.allocateMemory();
-    const dim3 blockSize(8, 8), gridSize((width + 7) / 8, (height + 7) / 8);
-    const std::string base = path.substr(path.find_last_of("/\\") + 1);
-
+    const int gpus = getCmdOption(argv, end, "--gpus") ? atoi(getCmdOption(argv, end, "--gpus")) : 1;
+    int batch = getCmdOption(argv, end, "--batch") ? atoi(getCmdOption(argv, end, "--batch")) : 16;
+    if (batch < 1) batch = 1;
+    if ((long long)width * height > (1LL << 24)) batch = 1;     // nsdf_render_views: batches need W * H <= 2^24
+    if (gpus < 1 || gpus > nsdf_device_count()) { std::cerr << "--gpus: " << nsdf_device_count() << " device(s) present\n"; return 1; }
     const int frames = doSpin ? views : 1;
-    for (int i = 0; i < frames; ++i) {
-        const float yaw = doSpin ? ry + 360.0f * i / views : ry;
-        nsdfCheck(nsdf_dev_memset(d_output, 0, (size_t)width * height * sizeof(uint)));
-        updateViewMatrices(rx, yaw, 0.0f, 0.0f, zoom, doSpin ? i : 0);
+    const int per_round = doSpin ? std::min(frames, batch * gpus) : 1;      // frames rendered per call
+    if (per_round > 128 * gpus) { std::cerr << "--batch: at most 128 views per device and launch\n"; return 1; }
+
+    nsdf_model* model = nn.handle();
+    if (!model) { std::cerr << "the network has no dense layers\n"; return 1; }
+    nsdf_multi* multi = nullptr;
+    if (gpus > 1) {
+        std::vector<int> devs;
+        int first = 0;
+        if (getCmdOption(argv, end, "--gpu")) first = atoi(getCmdOption(argv, end, "--gpu"));
+        for (int i = 0; i < gpus; ++i) devs.push_back((first + i) % nsdf_device_count());
+        nsdfCheck(nsdf_multi_create(model, devs.data(), gpus, &multi));
+    }
+    uint* d_output = nullptr;
+    const size_t frame_px = (size_t)width * height;
+    nsdfCheck(nsdf_dev_malloc(reinterpret_cast<void**>(&d_output), frame_px * per_round * sizeof(uint)));
+    nsdf_render_stats* d_stats = nullptr;
+    nsdfCheck(nsdf_dev_malloc(reinterpret_cast<void**>(&d_stats), sizeof(nsdf_render_stats)));
+    const dim3 blockSize(8, 8);
+    const std::string base = path.substr(path.find_last_of("/\\") + 1);
+    nsdf_render_opts opts;
+    getRenderOptions(&opts);
+    const bool useMatcap = colorType == NSDF_COLOR_MATCAP;
+    unsigned hw = std::thread::hardware_concurrency();
+    FrameWriter writer((int)std::max(1u, std::min(8u, hw ? hw : 1u)));
+
+    for (int i0 = 0; i0 < frames; i0 += per_round) {
+        const int n = std::min(per_round, frames - i0);
+        std::vector<nsdf_camera> cams((size_t)n);
+        for (int k = 0; k < n; ++k) {
+            const int i = i0 + k;
+            const float yaw = doSpin ? ry + 360.0f * i / views : ry;     // doABarrelRoll: viewRotation.y = i, frameNumber = i
+            nsdf_camera_from_view(rx, yaw, 0.0f, 0.0f, zoom, doSpin ? i : 0, &cams[(size_t)k]);
+        }
+        nsdfCheck(nsdf_dev_memset(d_output, 0, frame_px * n * sizeof(uint)));     // generateSingleImage: cudaMemset (main.cpp:407-408)
+        nsdf_render_stats st;
+        std::memset(&st, 0, sizeof(st));
         nsdfCheck(nsdf_device_synchronize());
         const auto t0 = std::chrono::steady_clock::now();
-        render_kernel(gridSize, blockSize, d_output, (uint)width, (uint)height, (uint)numInputs, nn, matcap);
-        nsdfCheck(nsdf_device_synchronize());
-        const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-        if (i == 0)
-            std::printf("volumeRender, Throughput = %.4f MTexels/s, Time = %.5f s, Size = %u Texels, NumDevsUsed = %u, Workgroup = %u\n",
-                        (1.0e-6 * width * height) / dt, dt, (unsigned)(width * height), 1u, blockSize.x * blockSize.y);
-        if (cmdOptionExists(argv, end, "--stats")) {
-            nsdf_render_stats st;
-            getLastRenderStats(&st);
-            std::printf("frame %d: %.3f ms, %llu MLP queries (%.2f Gq/s), %llu hit pixels, %llu rays, %llu unfinished\n", i, dt * 1e3,
-                        st.queries, st.queries / dt * 1e-9, st.hit_pixels, st.rays, st.unfinished);
-        }
-        nsdfCheck(nsdf_memcpy_d2h(out.hostData.get(), d_output, (size_t)width * height * sizeof(uint)));
-        std::string name;
-        if (doSpin) {
-            if (countDigit(i) < 2) name = "00";
-            else if (countDigit(i) == 2) name = "0";
-            name += std::to_string(i);
+        if (multi) {
+            nsdfCheck(nsdf_multi_render(multi, cams.data(), n, useMatcap ? matcap.hostData.get() : nullptr, (int)matcap.shape.x,
+                                        (int)matcap.shape.y, &opts, d_output, width, height, &st));
         } else {
-            name = base;
+            nsdfCheck(nsdf_dev_memset(d_stats, 0, sizeof(nsdf_render_stats)));
+            nsdfCheck(nsdf_render_views(model, cams.data(), n, useMatcap ? matcap.deviceData.get() : nullptr, (int)matcap.shape.x,
+                                        (int)matcap.shape.y, &opts, d_output, width, height, d_stats, nullptr));
+            nsdfCheck(nsdf_device_synchronize());
+            nsdfCheck(nsdf_memcpy_d2h(&st, d_stats, sizeof(st)));
         }
-        std::cout << "saving frame: " << prefix + name + ".png" << std::endl;
-        if (!out.savePNG(prefix + name + ".png")) return 1;
-        if (ppm && !out.savePPM(prefix + name + ".ppm")) return 1;
+        const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (i0 == 0)
+            std::printf("volumeRender, Throughput = %.4f MTexels/s, Time = %.5f s, Size = %u Texels, NumDevsUsed = %u, Workgroup = %u\n",
+                        (1.0e-6 * width * height * n) / dt, dt / n, (unsigned)(width * height), (unsigned)gpus, blockSize.x * blockSize.y);
+        if (cmdOptionExists(argv, end, "--stats"))
+            std::printf("frame %d%s: %.3f ms%s, %llu MLP queries (%.2f Gq/s), %llu hit pixels, %llu rays, %llu unfinished\n", i0,
+                        n > 1 ? (".." + std::to_string(i0 + n - 1)).c_str() : "", dt * 1e3 / n, n > 1 ? " per frame" : "", st.queries,
+                        st.queries / dt * 1e-9, st.hit_pixels, st.rays, st.unfinished);
+        for (int k = 0; k < n; ++k) {
+            const int i = i0 + k;
+            auto out = std::make_shared<Image>(width, height, true);
+            out->allocateMemory();
+            nsdfCheck(nsdf_memcpy_d2h(out->hostData.get(), d_output + (size_t)k * frame_px, frame_px * sizeof(uint)));
+            std::string name;
+            if (doSpin) {
+                if (countDigit(i) < 2) name = "00";
+                else if (countDigit(i) == 2) name = "0";
+                name += std::to_string(i);
+            } else {
+                name = base;
+            }
+            std::cout << "saving frame: " << prefix + name + ".png" << std::endl;
+            writer.push(prefix + name, out, ppm);      // encoded and written by a host thread while the next batch renders
+        }
     }
+    const bool wrote = writer.finish();
+    if (multi) nsdf_multi_destroy(multi);
+    nsdf_dev_free(d_stats);
     nsdf_dev_free(d_output);
-    return 0;
+    return wrote ? 0 : 1;
 }

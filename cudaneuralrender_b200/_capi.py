@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libnsdf.so")
+# NSDF_LIB=dev selects the development build (make -C csrc dev: A/B schedules, knobs from the environment) for tools/ sweeps
+LIB_PATH = os.path.join(_HERE, "libnsdf_dev.so" if os.environ.get("NSDF_LIB") == "dev" else "libnsdf.so")
 
 NSDF_OK = 0
 ACT_RELU, ACT_TANH_LINEAR = 0, 1
@@ -26,10 +27,17 @@ class SceneOp(C.Structure):
     _fields_ = [("prim", C.c_int), ("combine", C.c_int), ("a", C.c_float * 8)]
 
 
+class Tuning(C.Structure):
+    """nsdf_tuning (include/nsdf.h)."""
+    _fields_ = [(n, C.c_int) for n in ("express_period", "express_steps", "express_warps", "express_old_steps", "express_old_mask",
+                                       "express_from_bulk", "express_rays", "express_solo_steps", "tile_priority_steps",
+                                       "tile_priority_min_jobs", "tail_lanes", "tail_push_max")]
+
+
 class RenderOpts(C.Structure):
     _fields_ = [("color_type", C.c_int), ("scene", C.c_int), ("max_steps", C.c_int), ("tile_rank", C.c_int),
                 ("tile_world", C.c_int), ("evict_steps", C.c_int), ("flags", C.c_int), ("program", C.POINTER(SceneOp)),
-                ("n_ops", C.c_int), ("math", C.c_int)]
+                ("n_ops", C.c_int), ("math", C.c_int), ("tuning", C.POINTER(Tuning))]
 
 
 SCENE_TANH, SCENE_MANYSPHERE, SCENE_PROGRAM = 0, 1, 2
@@ -75,6 +83,7 @@ PROTOTYPES = {
     "nsdf_model_load_h5": (_i, [C.c_char_p, C.POINTER(_vp)]),
     "nsdf_h5_read_keras": (_i, [C.c_char_p, _ip, _ip, _i, _fp, _sz, C.POINTER(_sz)]),
     "nsdf_h5_write_keras": (_i, [C.c_char_p, _fp, _ip, _i]),
+    "nsdf_h5_write_keras_ex": (_i, [C.c_char_p, _fp, _ip, _i, _i]),
     "nsdf_model_destroy": (None, [_vp]),
     "nsdf_model_num_layers": (_i, [_vp]),
     "nsdf_model_dims": (_i, [_vp, _ip]),
@@ -85,6 +94,8 @@ PROTOTYPES = {
     "nsdf_mlp_forward_lattice": (_i, [_vp, _vp, _i, _f, _f, _i64, _i64, _i, _vp]),
     "nsdf_dense_layer_forward": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i64, _i, _vp]),
     "nsdf_render_opts_default": (None, [C.POINTER(RenderOpts)]),
+    "nsdf_tuning_default": (None, [C.POINTER(Tuning)]),
+    "nsdf_build_has_dev_schedules": (_i, []),
     "nsdf_scene_eval": (_i, [C.POINTER(SceneOp), _i, _vp, _vp, _i, _i, _vp, _i64, _vp]),
     "nsdf_camera_from_view": (None, [_f, _f, _f, _f, _f, _i, C.POINTER(Camera)]),
     "nsdf_render": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
@@ -103,6 +114,7 @@ PROTOTYPES = {
     "nsdf_png_load": (_i, [C.c_char_p, _vp, _sz, _ip, _ip]),
     "nsdf_png_save": (_i, [C.c_char_p, _vp, _i, _i, _i]),
     "nsdf_ppm_save": (_i, [C.c_char_p, _vp, _i, _i]),
+    "nsdf_zlib_inflate": (_i, [_vp, _sz, _vp, _sz, C.POINTER(_sz)]),
 }
 
 _lib = None

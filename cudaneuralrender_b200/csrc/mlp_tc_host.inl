@@ -2,10 +2,14 @@
 namespace nsdf {
 namespace {
 
+#ifdef NSDF_DEV_SCHEDULES
 int env_int(const char* name, int dflt) {
     const char* s = getenv(name);
     return (s && *s) ? atoi(s) : dflt;
 }
+#else
+constexpr int env_int(const char*, int dflt) { return dflt; }   // product build: no environment reads, measured defaults
+#endif
 
 // 16-bit encodings (round to nearest even) and their values
 uint16_t enc16(float v, int mode) {
@@ -272,6 +276,7 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
             default: return NSDF_EINVAL;
         }
     }
+#ifdef NSDF_DEV_SCHEDULES      // the v3 schedule measured slower than v2 in every configuration: development builds only
     if (kernel == 3) {
         const int cfg = env_int("NSDF_TC3_CFG", 0);
         switch (precision) {
@@ -281,6 +286,7 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
             default: return NSDF_EINVAL;
         }
     }
+#endif
     const int halves = env_int("NSDF_TC_EPI_HALVES", 1);
     switch (precision) {
         case NSDF_PREC_TC_FP16:

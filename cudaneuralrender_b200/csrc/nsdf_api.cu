@@ -278,7 +278,12 @@ int nsdf_h5_read_keras(const char* path, int* n_layers_out, int* dims_out, int d
 }
 
 int nsdf_h5_write_keras(const char* path, const float* params, const int* dims, int n_layers) {
+    return nsdf_h5_write_keras_ex(path, params, dims, n_layers, NSDF_H5_CONTIGUOUS);
+}
+
+int nsdf_h5_write_keras_ex(const char* path, const float* params, const int* dims, int n_layers, int storage) {
     if (!path || !params || !dims || n_layers <= 0 || n_layers > 256) return NSDF_EINVAL;
+    if (storage < NSDF_H5_CONTIGUOUS || storage > NSDF_H5_CHUNKED_DEFLATE) return NSDF_EINVAL;
     std::vector<nsdf::h5::KerasLayer> layers((size_t)n_layers);
     const float* p = params;
     for (int l = 0; l < n_layers; ++l) {
@@ -295,7 +300,7 @@ int nsdf_h5_write_keras(const char* path, const float* params, const int* dims, 
         p += od;
     }
     try {
-        nsdf::h5::write_keras_weights(path, layers);
+        nsdf::h5::write_keras_weights(path, layers, storage);
     } catch (const std::exception& e) {
         std::fprintf(stderr, "nsdf: writing %s: %s\n", path, e.what());
         return NSDF_EIO;
@@ -401,6 +406,23 @@ void nsdf_render_opts_default(nsdf_render_opts* o) {
     o->program = nullptr;
     o->n_ops = 0;
     o->math = NSDF_MATH_REFERENCE;
+    o->tuning = nullptr;
+}
+
+void nsdf_tuning_default(nsdf_tuning* t) {
+    if (!t) return;
+    t->express_period = -1;
+    t->express_steps = 160;
+    t->express_warps = 4;
+    t->express_old_steps = 192;
+    t->express_old_mask = 1;
+    t->express_from_bulk = 1;
+    t->express_rays = 1;
+    t->express_solo_steps = 768;
+    t->tile_priority_steps = 32;
+    t->tile_priority_min_jobs = 128;
+    t->tail_lanes = 0;
+    t->tail_push_max = 2;
 }
 
 int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,

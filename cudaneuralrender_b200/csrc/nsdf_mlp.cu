@@ -8,6 +8,7 @@
 
 namespace nsdf {
 
+#ifdef NSDF_DEV_SCHEDULES   // development rungs (make dev); the product runs mlp_fp32_thread_s_kernel and mlp_fp32_warp_kernel<4>
 // Thread-per-point fused MLP.  Persistent: chunks of blockDim*P points are strided over the grid.
 template <int P>
 __global__ void __launch_bounds__(256, (P >= 2) ? 1 : 2)
@@ -36,6 +37,7 @@ mlp_fp32_thread_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int 
         }
     }
 }
+#endif  // NSDF_DEV_SCHEDULES
 
 // Thread-per-4-points fused MLP (mlp32_eval_thread4s): accumulators in registers, activations in a thread-private
 // shared-memory column behind the weights.  One CTA per SM.
@@ -97,6 +99,7 @@ mlp_fp32_warp_kernel(const float* __restrict__ blob, uint32_t blob_bytes, int n_
     }
 }
 
+#ifdef NSDF_DEV_SCHEDULES   // development rungs: the tracer's tile evaluators on dense batches, constant-memory weights, the warp pipeline
 // The 16-point register-tiled form of the same evaluator (mlp32_eval_warp16): what the tracer's warps run while
 // more than 8 of their 16 ray slots are busy.
 __global__ void __launch_bounds__(256, 2)
@@ -333,6 +336,8 @@ mlp_fp32_pipe_kernel(const float* __restrict__ blob, const float* __restrict__ x
     }
 }
 
+#endif  // NSDF_DEV_SCHEDULES
+
 // Generic dense layer (any M, K; N = 1 per batch): replaces denseLayerForward /
 // batchedDenseLayerForward (src/layers/denseLayer.cu:86-176) with the same arithmetic.
 __global__ void __launch_bounds__(256)
@@ -353,6 +358,39 @@ dense_layer_kernel(const float* __restrict__ W, const float* __restrict__ A, flo
     }
 }
 
+#ifndef NSDF_DEV_SCHEDULES
+// Product dispatch: the thread-per-4-points evaluator (3.44 Gq/s on the 256^3 sweep, 68 % of the FFMA pipe) and, for
+// NSDF_PREC_FP32_WARP, the lane = neuron evaluator the tracer's thinning warps run.  No environment reads.
+int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res,
+                 float lo, float hi, int64_t first, cudaStream_t stream) {
+    if (n == 0) return NSDF_OK;
+    LatticeParams lp{lattice ? 1 : 0, res, lo, hi, (long long)first};
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    if (precision == NSDF_PREC_FP32_WARP) {
+        constexpr int R = 4, threads = 512;
+        const size_t smem = m->blob_bytes + (threads / 32) * 2 * R * WARP_ACT_STRIDE * sizeof(float);
+        cudaError_t e = cudaFuncSetAttribute(mlp_fp32_warp_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        const long long want = (n + (long long)(threads / 32) * R - 1) / ((long long)(threads / 32) * R);
+        const int grid = (int)(want < (long long)sms ? want : (long long)sms);
+        mlp_fp32_warp_kernel<R><<<grid, threads, smem, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+        return (int)cudaGetLastError();
+    }
+    // 384 threads x 512 B of activations + the weights must fit the 227 KB a CTA may own (deep nets: 256 threads)
+    const bool wide = m->blob_bytes + 384u * 512u <= 227u * 1024u;
+    const int th = wide ? 384 : 256;
+    const size_t smem4 = m->blob_bytes + (size_t)th * 32 * 4 * sizeof(float);
+    cudaError_t e = wide ? cudaFuncSetAttribute(mlp_fp32_thread_s_kernel<4, 384, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4)
+                         : cudaFuncSetAttribute(mlp_fp32_thread_s_kernel<4, 256, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem4);
+    if (e != cudaSuccess) return (int)e;
+    const long long chunk = (long long)th * 4;
+    const long long want = (n + chunk - 1) / chunk;
+    const int grid = (int)(want < (long long)sms ? want : (long long)sms);
+    if (wide) mlp_fp32_thread_s_kernel<4, 384, 1><<<grid, 384, smem4, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+    else mlp_fp32_thread_s_kernel<4, 256, 1><<<grid, 256, smem4, stream>>>(m->d_blob, m->blob_bytes, m->n_sq, d_x, d_y, n, lp);
+    return (int)cudaGetLastError();
+}
+#else  // development build: every rung, selected through the environment
 static int env_int(const char* name, int dflt) {
     const char* s = getenv(name);
     return (s && *s) ? atoi(s) : dflt;
@@ -489,6 +527,8 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
     }
     return (int)cudaGetLastError();
 }
+
+#endif  // NSDF_DEV_SCHEDULES
 
 int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const float* d_b, int M, int K,
                        int64_t num_batches, int activation, cudaStream_t stream) {

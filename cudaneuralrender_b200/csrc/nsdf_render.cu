@@ -11,16 +11,24 @@
 #include "render_kernels.cuh"
 #include "trace_coop.cuh"
 #include "trace_fused.cuh"
+#ifdef NSDF_DEV_SCHEDULES
 #include "trace_tc.cuh"
+#endif
 #include "tile_priority.cuh"
 
 namespace nsdf {
 
+#ifdef NSDF_DEV_SCHEDULES
+// Development build (make dev -> libnsdf_dev.so): every knob of the tracer can be overridden through the environment, read per
+// call, and the superseded A/B schedules are compiled in.  The product build reads NO environment variable: its knobs are
+// nsdf_render_opts.tuning (include/nsdf.h nsdf_tuning).
 static int env_int(const char* name, int dflt) {
     const char* s = getenv(name);
     return (s && *s) ? atoi(s) : dflt;
 }
+#endif
 
+#ifdef NSDF_DEV_SCHEDULES
 constexpr int LAT_R = 4;            // ray slots per warp in the latency kernel
 constexpr int LAT_THREADS = 512;
 
@@ -31,6 +39,8 @@ static size_t latency_smem(const nsdf_model* m) {
 static size_t fused_smem(const nsdf_model* m) {
     return m->blob_bytes + (FUSED_THREADS / 32) * 2 * FUSED_R * WARP_ACT_STRIDE * sizeof(float);
 }
+
+#endif  // NSDF_DEV_SCHEDULES
 
 static size_t coop_smem(const nsdf_model* m) {
     const size_t need = m->blob_bytes + (COOP_THREADS / 32) * 2 * COOP_R * WARP_ACT_STRIDE * sizeof(float);
@@ -134,6 +144,8 @@ int scene_eval_launch(const nsdf_scene_op* program, int n_ops, const float* d_xy
     return (int)cudaGetLastError();
 }
 
+#ifdef NSDF_DEV_SCHEDULES
+// The development build's launcher: all schedules, all knobs from the environment (defaults = the product's).
 int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream) {
@@ -512,8 +524,211 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
     return (int)e;
 }
 
+#else  // ---- product build --------------------------------------------------------------------------------------------------
+
+static void resolve_tuning(const nsdf_render_opts* opts, unsigned int total_idx, nsdf_tuning* T) {
+    nsdf_tuning_default(T);
+    if (opts->tuning) *T = *opts->tuning;
+    if (T->express_period < 0) T->express_period = total_idx >= 3000000u ? 24 : 12;   // large calls are bound by the bulk
+    if (T->express_rays < 1) T->express_rays = 1;
+    if (T->express_rays > 8) T->express_rays = 8;
+    if (T->express_warps < 1) T->express_warps = 1;
+    if (T->express_warps > COOP_THREADS / 32) T->express_warps = COOP_THREADS / 32;
+}
+
+// The product launcher: one schedule (the cooperative persistent tracer, trace_coop.cuh) plus the one-thread-per-pixel
+// debug kernel; knobs from nsdf_render_opts.tuning, no environment reads.
+int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
+                  const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                  cudaStream_t stream) {
+    if (!m->fused || (m->in[0] != 3 && m->in[0] != 4)) return NSDF_EUNSUPPORTED;
+    if (n_views < 1 || n_views > 128) return NSDF_EINVAL;
+    if (n_views > 1 && (long long)W * H > (1LL << 24)) return NSDF_EINVAL;   // RaySlot::pix carries the view in its top byte
+    // the A/B schedules, the mixed-precision far field and the caller-set hand-over threshold exist in development builds only
+    const unsigned int product_flags = NSDF_RENDER_SIMPLE | NSDF_RENDER_NO_QUIET_SMS | NSDF_RENDER_STAGED_STORES;
+    if (((unsigned int)opts->flags & ~product_flags) != 0u || opts->evict_steps != 0) return NSDF_EUNSUPPORTED;
+    if (opts->tile_world < 1 || opts->tile_rank < 0 || opts->tile_rank >= opts->tile_world) return NSDF_EINVAL;
+    if (opts->color_type == NSDF_COLOR_MATCAP && (!d_matcap || mw <= 0 || mh <= 0)) return NSDF_EINVAL;
+    if (opts->math != NSDF_MATH_REFERENCE && opts->math != NSDF_MATH_DETERMINISTIC) return NSDF_EINVAL;
+    const bool simple = (opts->flags & NSDF_RENDER_SIMPLE) != 0;
+    if (simple && n_views > 1) return NSDF_EUNSUPPORTED;
+
+    RenderParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    std::memcpy(rp.cam.inv_view, cams->inv_view, sizeof(rp.cam.inv_view));
+    std::memcpy(rp.cam.normal, cams->normal, sizeof(rp.cam.normal));
+    rp.cam.frame = cams->frame;
+    rp.cam.zoff = many_sphere_zoff(cams->frame);
+    rp.n_views = n_views;
+    rp.view_pixels = (unsigned int)((long long)W * H);
+    rp.blob = m->d_blob;
+    rp.n_sq = m->n_sq;
+    rp.blob_bytes = m->blob_bytes;
+    rp.matcap = d_matcap;
+    rp.mw = mw;
+    rp.mh = mh;
+    rp.color_type = opts->color_type;
+    rp.scene = opts->scene;
+    if (opts->scene == NSDF_SCENE_PROGRAM) {
+        const int rc_prog = scene_program_pack(opts->program, opts->n_ops, &rp.prog);
+        if (rc_prog) return rc_prog;
+    } else if (opts->scene != NSDF_SCENE_TANH && opts->scene != NSDF_SCENE_MANYSPHERE) {
+        return NSDF_EINVAL;
+    }
+    rp.out = d_out;
+    rp.W = W;
+    rp.H = H;
+    rp.tiles_x = (W + TILE - 1) / TILE;
+    rp.n_tiles = rp.tiles_x * ((H + TILE - 1) / TILE);
+    rp.tile_rank = opts->tile_rank;
+    rp.tile_world = opts->tile_world;
+    const int my_tiles = (rp.n_tiles - opts->tile_rank + opts->tile_world - 1) / opts->tile_world;
+    if (my_tiles <= 0) return NSDF_OK;
+    const long long n_jobs_ll = (long long)my_tiles * n_views;       // job = (view, tile of this call)
+    if (n_jobs_ll * TILE_PIXELS >= (1LL << 32)) return NSDF_EINVAL;
+    const int n_jobs = (int)n_jobs_ll;
+    rp.my_tiles = my_tiles;
+    rp.total_idx = (unsigned int)n_jobs * TILE_PIXELS;
+    rp.max_steps = opts->max_steps;
+    rp.n_in = m->in[0];
+    rp.t4 = (float)cams->frame;
+    rp.refmath = opts->math == NSDF_MATH_REFERENCE ? 1 : 0;
+    rp.stats = d_stats;
+    rp.evict_steps = 1 << 30;
+    rp.evict_steps_hi = 1 << 30;
+    nsdf_tuning T;
+    resolve_tuning(opts, rp.total_idx, &T);
+
+    int rc = ensure_scratch(m, 0, XQUEUE_ENTRIES * (size_t)n_views);
+    if (rc) return rc;
+    cudaError_t e = cudaSuccess;
+    if (n_views > 1) {
+        if ((size_t)n_views > m->views_capacity) {
+            if (m->d_views) cudaFree(m->d_views);
+            m->d_views = nullptr;
+            m->views_capacity = 0;
+            if (cudaMalloc(&m->d_views, (size_t)n_views * sizeof(Camera)) != cudaSuccess) return NSDF_ENOMEM;
+            m->views_capacity = (size_t)n_views;
+        }
+        std::vector<Camera> hv((size_t)n_views);
+        for (int v = 0; v < n_views; ++v) {
+            std::memcpy(hv[v].inv_view, cams[v].inv_view, sizeof(hv[v].inv_view));
+            std::memcpy(hv[v].normal, cams[v].normal, sizeof(hv[v].normal));
+            hv[v].frame = cams[v].frame;
+            hv[v].zoff = many_sphere_zoff(cams[v].frame);
+        }
+        e = cudaMemcpyAsync(m->d_views, hv.data(), hv.size() * sizeof(Camera), cudaMemcpyHostToDevice, stream);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaStreamSynchronize(stream);   // hv is a local: the copy must have left it (a few KB, once per batch)
+        if (e != cudaSuccess) return (int)e;
+        rp.views = reinterpret_cast<const Camera*>(m->d_views);
+    }
+    // staged frame stores (render_kernels.cuh emit_pixel / flush_tile): for tile-partitioned calls, whose d_out is a peer
+    // GPU's memory in the multi-GPU gather, or on request
+    if (!simple && (opts->tile_world > 1 || (opts->flags & NSDF_RENDER_STAGED_STORES))) {
+        if ((size_t)n_jobs > m->frame_stage_jobs) {
+            if (m->d_frame_stage) cudaFree(m->d_frame_stage);
+            m->d_frame_stage = nullptr;
+            m->frame_stage_jobs = 0;
+            if (cudaMalloc(&m->d_frame_stage, (size_t)n_jobs * (TILE_PIXELS + 1) * sizeof(uint32_t)) != cudaSuccess) return NSDF_ENOMEM;
+            m->frame_stage_jobs = (size_t)n_jobs;
+        }
+        rp.stage = reinterpret_cast<uint32_t*>(m->d_frame_stage);
+        rp.tile_done = reinterpret_cast<unsigned int*>(m->d_frame_stage) + m->frame_stage_jobs * TILE_PIXELS;
+        e = cudaMemsetAsync(rp.tile_done, 0, (size_t)n_jobs * sizeof(unsigned int), stream);
+        if (e != cudaSuccess) return (int)e;
+    }
+    rp.pixel_counter = m->d_counters;
+    e = cudaMemsetAsync(m->d_counters, 0, 8 * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return (int)e;
+
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    NSDF_PER_DEVICE_FLAG(attr_done);
+    if (!attr_done) {
+        e = cudaFuncSetAttribute(trace_simple_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(trace_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(tile_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+    if (simple) {
+        const unsigned int blocks = (rp.total_idx + 127u) / 128u;
+        trace_simple_kernel<<<blocks, 128, m->blob_bytes, stream>>>(rp);
+        return (int)cudaGetLastError();
+    }
+
+    // ---- tile priority: probe every 8th pixel for a few steps and trace the jobs (view, tile) with grazing rays first, so that
+    // the call's longest dependent chains start at t = 0 and hide behind the bulk (tile_priority.cuh).  Order-free: same bytes.
+    if (T.tile_priority_steps > 0 && n_jobs >= T.tile_priority_min_jobs) {
+        if ((size_t)n_jobs > m->tile_scratch_capacity) {
+            if (m->d_tile_scratch) cudaFree(m->d_tile_scratch);
+            m->d_tile_scratch = nullptr;
+            m->tile_scratch_capacity = 0;
+            e = cudaMalloc(&m->d_tile_scratch, 2 * (size_t)n_jobs * sizeof(int));
+            if (e != cudaSuccess) return (int)e;
+            m->tile_scratch_capacity = (size_t)n_jobs;
+        }
+        int* d_score = m->d_tile_scratch;
+        int* d_order = m->d_tile_scratch + m->tile_scratch_capacity;
+        e = cudaMemsetAsync(d_score, 0, (size_t)n_jobs * sizeof(int), stream);
+        if (e != cudaSuccess) return (int)e;
+        const unsigned int probes = (unsigned int)n_jobs * PROBES_PER_TILE;
+        tile_probe_kernel<<<(probes + 127u) / 128u, 128, m->blob_bytes, stream>>>(rp, n_jobs, T.tile_priority_steps, d_score);
+        tile_sort_kernel<<<1, 256, 0, stream>>>(d_score, n_jobs, d_order);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return (int)e;
+        rp.tile_order = d_order;
+    }
+
+    // ---- one persistent, cooperative launch: one CTA per SM (trace_coop.cuh)
+    int occ = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
+    if (e != cudaSuccess) return (int)e;
+    if (occ < 1) return NSDF_EUNSUPPORTED;
+    const unsigned int per_cta = (COOP_THREADS / 32) * COOP_R;
+    const unsigned int cap = (unsigned int)(sms * occ);
+    const unsigned int want = (rp.total_idx + per_cta - 1) / per_cta;
+    m->frame_seq = m->frame_seq + 1u ? m->frame_seq + 1u : 1u;
+    rp.frame_seq = m->frame_seq;
+    // Serial tail: every express_period-th CTA (= SM) is an express SM whose lanes hold ONE ray each; any warp
+    // hands a ray that has marched express_steps steps to a free lane.  Only for grids that cover the machine (a smaller grid
+    // could consist of express CTAs alone).
+    const bool full_grid = want >= cap;
+    const bool express = full_grid && !(opts->flags & NSDF_RENDER_NO_QUIET_SMS) && T.express_period > 0 && T.express_steps > 0;
+    if (express) {
+        rp.queue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);   // non-null: enables the consumer machinery (nothing is pushed to it)
+        rp.queue_capacity = 0u;
+        rp.xqueue = reinterpret_cast<StragglerEntry*>(m->d_xqueue);
+        rp.xqueue_soft_cap = (unsigned int)(XQUEUE_ENTRIES * (size_t)n_views / 2);
+        rp.express_period = (unsigned int)T.express_period;
+        rp.express_steps = T.express_steps;
+        rp.express_warps = T.express_warps;
+        rp.express_rays = T.express_rays;
+        rp.express_solo_steps = T.express_solo_steps;
+        rp.express_steps_old = T.express_old_steps;
+        rp.express_check_old = T.express_old_mask;
+        rp.express_from_bulk = T.express_from_bulk;
+        rp.express_lanes = (cap / rp.express_period) * (unsigned int)(rp.express_warps * rp.express_rays);
+        rp.tail_lanes = T.tail_lanes;
+        rp.tail_push_max = T.tail_push_max;
+    }
+    return (int)launch_coop(rp, want < cap ? want : cap, coop_smem(m), stream);
+}
+#endif  // NSDF_DEV_SCHEDULES
+
 }  // namespace nsdf
 
+extern "C" int nsdf_build_has_dev_schedules(void) {
+#ifdef NSDF_DEV_SCHEDULES
+    return 1;
+#else
+    return 0;
+#endif
+}
+
+#ifdef NSDF_DEV_SCHEDULES
 // Development hook (not part of include/nsdf.h): copies the tracer's timeline log to the host and clears it.
 extern "C" int nsdf_dev_timeline_read(unsigned long long* out, int n_words) {
     const size_t total = sizeof(unsigned long long) * (4 + 4 * nsdf::TIMELINE_EVENTS);
@@ -527,3 +742,4 @@ extern "C" int nsdf_dev_timeline_read(unsigned long long* out, int n_words) {
     }
     return (int)e;
 }
+#endif  // NSDF_DEV_SCHEDULES

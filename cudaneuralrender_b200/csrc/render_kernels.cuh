@@ -322,6 +322,7 @@ __device__ __forceinline__ void evict_slot(RaySlot& s, bool do_evict, const Rend
     }
 }
 
+#ifdef NSDF_DEV_SCHEDULES   // superseded A/B schedules: development builds only (make dev)
 // ---------------------------------------------------------------------------------------------
 template <int P>
 __global__ void __launch_bounds__(256, (P >= 2) ? 1 : 2) trace_throughput_kernel(const __grid_constant__ RenderParams rp) {
@@ -448,6 +449,8 @@ __global__ void __launch_bounds__(512, 1) trace_latency_kernel(const __grid_cons
     }
     flush_stats(st, rp.stats);
 }
+
+#endif  // NSDF_DEV_SCHEDULES
 
 // ---------------------------------------------------------------------------------------------
 // Debug / A-B kernel: one thread per enumeration index, no refill, no eviction.

@@ -33,6 +33,11 @@ namespace nsdf {
 
 // Development timeline (NSDF_COOP_TIMELINE=1): [0] kernel start, [1] last warp out of pixels, [2] kernel end (globaltimer ns),
 // [3] number of events, then events {time, pix, steps, kind}: kind 100 = pushed, 101 = popped, else rays in the warp.
+#ifdef NSDF_DEV_SCHEDULES
+#define NSDF_TIMELINE(rp) ((rp).timeline)
+#else
+#define NSDF_TIMELINE(rp) false      // product build: the timeline hooks and the A/B schedules are compiled out
+#endif
 constexpr int TIMELINE_EVENTS = 32768;
 __device__ unsigned long long g_timeline[4 + 4 * TIMELINE_EVENTS];
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -49,7 +54,12 @@ __device__ __forceinline__ void timeline_event(int pix, int steps, int kind) {
 }
 
 constexpr int COOP_THREADS = 512;   // ONE CTA per SM (the launch pads its shared memory past half an SM): 16 warps, 4 per scheduler
-constexpr int COOP_R = 16;  // ray slots per warp (lanes 0..COOP_R-1 own them)
+#ifndef NSDF_COOP_R
+#define NSDF_COOP_R 16
+#endif
+constexpr int COOP_R = NSDF_COOP_R;  // ray slots per warp (lanes 0..COOP_R-1 own them).  32 (every lane owns a ray, 8 x 4 register tile) was measured
+                                     // SLOWER in the tracer: 1080p 19.2 -> 24.0 ms, batched turntable 10.9 -> 11.5 ms per frame (step latency doubles)
+static_assert(COOP_R == 16 || COOP_R == 32, "COOP_R");
 // Shared memory a CTA asks for at least, so that two can never share an SM: roles are per CTA (= per SM), and an express
 // CTA's lone rays must have their schedulers to themselves.
 constexpr size_t COOP_MIN_SMEM = 116 * 1024;
@@ -138,7 +148,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
     stage_weights(s_w, rp.blob, rp.blob_bytes, &s_bar);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (rp.timeline && blockIdx.x == 0 && threadIdx.x == 0) g_timeline[0] = global_ns();
+    if (NSDF_TIMELINE(rp) && blockIdx.x == 0 && threadIdx.x == 0) g_timeline[0] = global_ns();
     float* abuf = s_w + (rp.blob_bytes >> 2) + warp * (2 * COOP_R * WARP_ACT_STRIDE);
     const unsigned int total_warps = gridDim.x * (COOP_THREADS / 32);
     const bool from_queue = rp.queue_static != 0;
@@ -175,6 +185,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
     int poll = 0;
     unsigned int idle = 0;
 
+#ifdef NSDF_DEV_SCHEDULES
     // ---- hybrid schedule: the bulk of the frame on the ray-per-lane evaluator, long rays to the quiet SMs
     if (rp.hybrid && use_queue && producing) {
         RaySlot ps;
@@ -218,6 +229,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
         exhausted = true;
         if (lane == 0) { __threadfence(); atomicAdd(rp.pixel_counter + 3, 1u); }
     }
+#endif
 
     for (;;) {
         // ---- refill idle ray slots (ballot compaction over the slot lanes); not while a long ray is on board
@@ -252,7 +264,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
             }
             if (base + cnt >= n_src) {
                 exhausted = true;
-                if (rp.timeline && lane == 0) atomicMax(&g_timeline[1], global_ns());
+                if (NSDF_TIMELINE(rp) && lane == 0) atomicMax(&g_timeline[1], global_ns());
             }
         }
         flush_completed(rp, flush_g, lane);
@@ -276,7 +288,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
                 ok = __shfl_sync(0xffffffffu, ok, 0);
                 bulk_over = __shfl_sync(0xffffffffu, over, 0) != 0u;
                 if (ok) {
-                    if (rp.timeline && go) timeline_event(slot.pix, slot.steps, 102);
+                    if (NSDF_TIMELINE(rp) && go) timeline_event(slot.pix, slot.steps, 102);
                     queue_push(slot, go, rp.xqueue, pc + 4, rp, st);
                     if (!exhausted) continue;      // a producing warp refills the slots it has just emptied
                     act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
@@ -295,7 +307,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
                 unsigned int ok = 0;
                 if (lane == 0) ok = (ld_volatile_u32(pc + 4) + 32u <= rp.xqueue_soft_cap) ? 1u : 0u;
                 if (__shfl_sync(0xffffffffu, ok, 0)) {
-                    if (rp.timeline && go) timeline_event(slot.pix, slot.steps, 104);
+                    if (NSDF_TIMELINE(rp) && go) timeline_event(slot.pix, slot.steps, 104);
                     queue_push(slot, go, rp.xqueue, pc + 4, rp, st);
                     act = __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0);
                 }
@@ -326,7 +338,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
                         __ballot_sync(0xffffffffu, lane < COOP_R && slot.mode == 0 && slot.steps >= rp.express_solo_steps) != 0u;
                     if (express_lane && now < rp.express_rays && !solo) {
                         const bool popped = queue_pop(slot, lane < rp.express_rays && slot.mode < 0, rp.xqueue, pc + 4, pc + 5, rp);
-                        if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 103);
+                        if (NSDF_TIMELINE(rp) && popped) timeline_event(slot.pix, slot.steps, 103);
                         const int got = __popc(__ballot_sync(0xffffffffu, popped));
                         if (got) {
                             xcount += got;
@@ -341,7 +353,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
                     }
                 } else {
                     const bool popped = fused_pop(slot, lane < pop_max && slot.mode < 0, rp);
-                    if (rp.timeline && popped) timeline_event(slot.pix, slot.steps, 101);
+                    if (NSDF_TIMELINE(rp) && popped) timeline_event(slot.pix, slot.steps, 101);
                     // tail of the frame: once every warp is out of pixels, warps 0..tail_lanes-1 of EVERY CTA are lanes for the
                     // express queue (one lone ray each: up to four per SM step at full speed, lone_bench), fed by tail_handover below
                     if (rp.xqueue && bulk_over && warp < rp.tail_lanes && !__ballot_sync(0xffffffffu, lane < COOP_R && slot.mode >= 0))
@@ -376,7 +388,7 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
                 // chunks end on multiples of 64 steps (the queues and the express hand-over are looked at in between)
                 const int chunk = 64 - (__shfl_sync(0xffffffffu, slot.steps, owner) & 63);
                 lone_ray_march(slot, owner, s_w, rp.n_sq, abuf, rp, st, lane, use_queue ? chunk : (1 << 30));
-                if (rp.timeline && lane == owner && (slot.steps & 255) < 64 && slot.steps >= 256) timeline_event(slot.pix, slot.steps, 1);
+                if (NSDF_TIMELINE(rp) && lane == owner && (slot.steps & 255) < 64 && slot.steps >= 256) timeline_event(slot.pix, slot.steps, 1);
                 continue;
             }
         }
@@ -385,6 +397,19 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
         const int rank = __popc(act & lanemask_lt());
         const f3 q = active ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
         float mine;
+#if NSDF_COOP_R == 32
+        if (na > 16) {
+            // 17..32 busy slots: the 8-neuron x 4-ray register tile over 32 points (mlp32_eval_tile<4>): 1.5 B of shared memory
+            // per FFMA instead of 2 (dense 3.19 against 2.84 Gq/s), and every lane owns a ray, so the scene function and the
+            // ray update run at full lane efficiency
+            float4* xin = reinterpret_cast<float4*>(abuf + 32 * WARP_ACT_STRIDE);
+            if (active) xin[rank] = make_float4(q.x, q.y, q.z, 0.0f);
+            else xin[na + __popc(~act & lanemask_lt())] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // idle lanes zero the unused ranks
+            float y[1];
+            mlp32_eval_tile<4>(s_w, rp.n_sq, abuf, lane, y, rp.t4, rp.n_in == 4);
+            mine = __shfl_sync(0xffffffffu, y[0], rank);
+        } else
+#endif
         if (na > 8) {
             // 9..16 busy slots: the register-tiled 16-point evaluator.  Owners write their query point at their rank,
             // unused ranks are zeroed (their results are computed and dropped).
@@ -408,16 +433,16 @@ __global__ void __launch_bounds__(COOP_THREADS, 1) trace_coop_kernel(const __gri
         }
         if (active) slot_update(slot, mine, q, rp, st, flush_g);
         flush_completed(rp, flush_g, lane);
-        if (rp.timeline && active && slot.mode == 0 && slot.steps >= 256 && (slot.steps & 255) == 0) timeline_event(slot.pix, slot.steps, na);
+        if (NSDF_TIMELINE(rp) && active && slot.mode == 0 && slot.steps >= 256 && (slot.steps & 255) == 0) timeline_event(slot.pix, slot.steps, na);
         // ---- long rays leave for the quiet SMs
         if (use_queue && producing)
         {
             const bool leave = lane < COOP_R && slot.mode == 0 && slot.steps >= rp.evict_steps_hi;
-            if (rp.timeline && leave) timeline_event(slot.pix, slot.steps, 100);
+            if (NSDF_TIMELINE(rp) && leave) timeline_event(slot.pix, slot.steps, 100);
             fused_push(slot, leave, rp, st);
         }
     }
-    if (rp.timeline && lane == 0) atomicMax(&g_timeline[2], global_ns());
+    if (NSDF_TIMELINE(rp) && lane == 0) atomicMax(&g_timeline[2], global_ns());
     flush_stats(st, rp.stats);
 }
 

@@ -106,6 +106,7 @@ __device__ __forceinline__ bool fused_pop(RaySlot& s, bool want, const RenderPar
     return queue_pop(s, want, rp.queue, rp.pixel_counter + 1, rp.pixel_counter + 2, rp);
 }
 
+#ifdef NSDF_DEV_SCHEDULES   // the producer/consumer A/B schedule; the queue helpers above serve the default tracer
 __global__ void __launch_bounds__(FUSED_THREADS, 2) trace_fused_kernel(const __grid_constant__ RenderParams rp) {
     extern __shared__ __align__(16) float s_w[];
     __shared__ uint64_t s_bar;
@@ -226,5 +227,7 @@ __global__ void __launch_bounds__(FUSED_THREADS, 2) trace_fused_kernel(const __g
     }
     flush_stats(st, rp.stats);
 }
+
+#endif  // NSDF_DEV_SCHEDULES
 
 }  // namespace nsdf

@@ -338,8 +338,9 @@ def read_keras_h5(path: str):
     return out
 
 
-def write_keras_h5(path: str, layers) -> None:
-    """layers: [(kernel[in][out], bias[out])] -> Keras save_weights-style file (groups dense, dense_1, ...; nsdf_h5_write_keras)."""
+def write_keras_h5(path: str, layers, storage: int = 0) -> None:
+    """layers: [(kernel[in][out], bias[out])] -> Keras save_weights-style file (groups dense, dense_1, ...; nsdf_h5_write_keras).
+    storage: 0 contiguous datasets, 1 chunked, 2 chunked + shuffle + deflate filters (NSDF_H5_*)."""
     dims, chunks = [], []
     for k, (kernel, bias) in enumerate(layers):
         kernel = np.asarray(kernel, dtype=np.float32); bias = np.asarray(bias, dtype=np.float32).ravel()
@@ -350,8 +351,8 @@ def write_keras_h5(path: str, layers) -> None:
         dims.append(kernel.shape[1])
         chunks += [np.ascontiguousarray(kernel.T).ravel(), bias]
     params = np.concatenate(chunks).astype(np.float32)
-    capi.check(capi.lib().nsdf_h5_write_keras(path.encode(), params.ctypes.data_as(C.POINTER(C.c_float)),
-                                              (C.c_int * len(dims))(*dims), len(layers)), "nsdf_h5_write_keras")
+    capi.check(capi.lib().nsdf_h5_write_keras_ex(path.encode(), params.ctypes.data_as(C.POINTER(C.c_float)),
+                                                 (C.c_int * len(dims))(*dims), len(layers), int(storage)), "nsdf_h5_write_keras")
 
 
 # ---- renderer: the three extern "C" entry points of src/volumeRender_kernel.cu ------------------
@@ -369,6 +370,7 @@ class _RenderState:
         self.flags = 0
         self.evict_steps = 0
         self.math = MATH_REFERENCE
+        self.tuning = None      # capi.Tuning or None (library defaults)
 
 
 _state = _RenderState()
@@ -426,7 +428,28 @@ def _opts(tile_rank: int = 0, tile_world: int = 1) -> RenderOpts:
         o.program = C.cast(_state.program, C.POINTER(capi.SceneOp))
         o.n_ops = len(_state.program)
     o.math = _state.math
+    if _state.tuning is not None:
+        o.tuning = C.pointer(_state.tuning)
     return o
+
+
+def setTuning(**knobs):
+    """nsdf_tuning for the following renders: setTuning() restores the library defaults, setTuning(express_steps=96, ...)
+    changes the named knobs of the defaults."""
+    if not knobs:
+        _state.tuning = None
+        return
+    t = capi.Tuning()
+    capi.lib().nsdf_tuning_default(C.byref(t))
+    for k, v in knobs.items():
+        if not hasattr(t, k):
+            raise KeyError(k)
+        setattr(t, k, int(v))
+    _state.tuning = t
+
+
+def dev_schedules_available() -> bool:
+    return bool(capi.lib().nsdf_build_has_dev_schedules())
 
 
 def scene_eval(ops, xyz: torch.Tensor, nsdf: torch.Tensor, frame: int = 0, math: int = MATH_DETERMINISTIC) -> torch.Tensor:

@@ -77,6 +77,11 @@ extern "C" void setSceneProgram(const nsdf_scene_op* ops, int nOps) {
     g.opts.n_ops = nOps;
 }
 
+extern "C" void getRenderOptions(nsdf_render_opts* out) {
+    ensure_init();
+    *out = g.opts;
+}
+
 extern "C" void getLastRenderStats(nsdf_render_stats* out) {
     ensure_init();
     *out = g.last;

@@ -150,6 +150,13 @@ int nsdf_h5_read_keras(const char* path, int* n_layers_out, int* dims_out, int d
  * exactly the groups present, so stacks of more than ten layers load in network order (the reference's name sort,
  * src/neuralNetwork.cpp:88-91, puts dense_10 before dense_2).  No device needed.  SURVEY 8 f1. */
 int nsdf_h5_write_keras(const char* path, const float* params, const int* dims, int n_layers);
+/* Same with a storage layout for the datasets.  The reader (nsdf_model_load_h5, nsdf_h5_read_keras, the HighFive shim) takes
+ * whatever libhdf5 would hand the reference for float32/float64 data: contiguous, compact, and chunked datasets with the
+ * shuffle, deflate (gzip) and fletcher32 filters (what h5py writes with compression="gzip"). */
+#define NSDF_H5_CONTIGUOUS 0
+#define NSDF_H5_CHUNKED 1
+#define NSDF_H5_CHUNKED_DEFLATE 2 /* chunked + shuffle + deflate filter pipeline; the streams are stored (uncompressed) blocks */
+int nsdf_h5_write_keras_ex(const char* path, const float* params, const int* dims, int n_layers, int storage);
 void nsdf_model_destroy(nsdf_model* m);
 int nsdf_model_num_layers(const nsdf_model* m);
 /* dims_out receives n_layers+1 ints. */
@@ -192,6 +199,29 @@ typedef struct nsdf_camera {
     int frame;          /* c_frameNumber                                                           */
 } nsdf_camera;
 
+/* Knobs of the persistent tracer (csrc/trace_coop.cuh); nsdf_tuning_default fills the measured best for 1080p..4K frames on a
+ * B200.  The product library reads no environment variable: this struct is the only way in.  The serial tail of a frame is a
+ * handful of rays that need thousands of DEPENDENT network evaluations: "express" SMs take no pixels and hold
+ * one such ray per lane (warp), stepping it at ~1.3 us instead of the ~14 us a ray pays inside a full 16-ray warp.            */
+typedef struct nsdf_tuning {
+    int express_period;      /* every express_period-th SM is an express SM; 0 = none; -1 = 12 (24 for calls >= 3 M pixels)   */
+    int express_steps;       /* a ray that has marched this many steps moves to a free express lane (160)                      */
+    int express_warps;       /* lanes per express SM (4: one per scheduler steps fastest)                                       */
+    int express_old_steps;   /* rays older than this (192) ask for a lane whenever steps & express_old_mask == 0 ...            */
+    int express_old_mask;    /* ... (1: every 2nd step) instead of every 16th, so that a freed lane goes to the older ray      */
+    int express_from_bulk;   /* 1: warps that still take pixels hand rays over too                                             */
+    int express_rays;        /* rays a lane marches together (1; more measured slower for the longest chains)                  */
+    int express_solo_steps;  /* with express_rays > 1: a lane holding a ray this old takes no company (768)                    */
+    int tile_priority_steps; /* probe every 8th pixel for this many steps and trace jobs with grazing rays first (32; 0 = off) */
+    int tile_priority_min_jobs; /* ... for calls of at least this many (view, tile) jobs (128)                                 */
+    int tail_lanes;          /* once the pixels are gone, warps 0..tail_lanes-1 of every SM are lanes too (0 = off)             */
+    int tail_push_max;       /* ... fed by warps that are down to this many marching rays (2)                                   */
+} nsdf_tuning;
+void nsdf_tuning_default(nsdf_tuning* t);
+/* 1 if this library was built with -DNSDF_DEV_SCHEDULES (libnsdf_dev.so: superseded A/B schedules, mixed-precision far field,
+ * knobs from the environment); the product build returns 0 and answers NSDF_EUNSUPPORTED to their flags. */
+int nsdf_build_has_dev_schedules(void);
+
 typedef struct nsdf_render_opts {
     int color_type;   /* NSDF_COLOR_*                                                      */
     int scene;        /* NSDF_SCENE_*                                                      */
@@ -203,6 +233,7 @@ typedef struct nsdf_render_opts {
     const nsdf_scene_op* program; /* HOST array, read during the call; used when scene == NSDF_SCENE_PROGRAM */
     int n_ops;        /* 1..NSDF_SCENE_MAX_OPS                                             */
     int math;         /* NSDF_MATH_*                                                       */
+    const nsdf_tuning* tuning; /* NULL = nsdf_tuning_default                                       */
 } nsdf_render_opts;
 
 #define NSDF_RENDER_SIMPLE 1u      /* one-thread-per-pixel kernel without refill (debug / A-B testing) */
@@ -305,6 +336,8 @@ int nsdf_multi_render(nsdf_multi* mm, const nsdf_camera* cams, int n_views, cons
 int nsdf_png_load(const char* path, uint32_t* texels, size_t capacity, int* w, int* h);
 /* Image::savePNG: flip != 0 reverses the texel stream (the reference's default 180-degree turn). */
 int nsdf_png_save(const char* path, const uint32_t* texels, int w, int h, int flip);
+/* The zlib / DEFLATE decoder the PNG reader and the HDF5 reader (deflate-filtered chunks) share (include/nsdf_inflate.hpp). */
+int nsdf_zlib_inflate(const unsigned char* in, size_t n, unsigned char* out, size_t capacity, size_t* n_out);
 /* sdkSavePPM4ub / __savePPM: "P6\n<W>\n<H>\n255\n" + RGB. */
 int nsdf_ppm_save(const char* path, const uint32_t* texels, int w, int h);
 

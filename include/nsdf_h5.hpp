@@ -31,6 +31,8 @@
 #include <string>
 #include <vector>
 
+#include "nsdf_inflate.hpp"
+
 namespace nsdf {
 namespace h5 {
 
@@ -236,11 +238,102 @@ private:
         node.string_attrs[name] = std::move(v);
     }
 
+    // Raw-data chunk B-tree (version 1, node type 1): collects (chunk offsets in elements, file address, stored size, filter mask)
+    struct Chunk { std::vector<uint64_t> off; uint64_t addr; uint32_t size; uint32_t mask; };
+    void walk_chunk_btree(uint64_t addr, unsigned nd, std::vector<Chunk>& out, int depth) const {
+        if (depth > 16) throw FormatError("chunk B-tree too deep");
+        need(addr, 8 + 2 * so_);
+        if (!sig(addr, "TREE") || rd(addr + 4, 1) != 1) throw FormatError("bad chunk B-tree node");
+        const unsigned level = (unsigned)rd(addr + 5, 1), used = (unsigned)rd(addr + 6, 2);
+        const uint64_t key = 8 + 8ull * nd;                 // chunk size (4), filter mask (4), nd offsets of 8 bytes
+        uint64_t pos = addr + 8 + 2 * so_;
+        for (unsigned i = 0; i < used; ++i) {
+            need(pos, key + so_);
+            const uint64_t child = rd(pos + key, so_) + base_;
+            if (level > 0) {
+                walk_chunk_btree(child, nd, out, depth + 1);
+            } else {
+                Chunk c;
+                c.size = (uint32_t)rd(pos, 4);
+                c.mask = (uint32_t)rd(pos + 4, 4);
+                for (unsigned k = 0; k < nd; ++k) c.off.push_back(rd(pos + 8 + 8ull * k, 8));
+                c.addr = child;
+                out.push_back(std::move(c));
+            }
+            pos += key + so_;
+        }
+    }
+    void read_chunked(Node& d, uint64_t n, unsigned elem, uint64_t btree, const std::vector<uint64_t>& cdims,
+                      const std::vector<unsigned>& filters) const {
+        const size_t rank = d.dims.size();
+        if (cdims.size() != rank + 1 || cdims[rank] != elem) throw FormatError("dataset '" + d.name + "': bad chunk dimensions");
+        uint64_t chunk_elems = 1;
+        for (size_t k = 0; k < rank; ++k) {
+            if (cdims[k] == 0 || chunk_elems > (1ull << 28) / cdims[k]) throw FormatError("dataset '" + d.name + "': chunk too large");
+            chunk_elems *= cdims[k];
+        }
+        for (unsigned f : filters)
+            if (f != 1 && f != 2 && f != 3) throw FormatError("dataset '" + d.name + "': unsupported filter " + std::to_string(f));
+        d.data.assign((size_t)n, 0.0f);           // unallocated chunks read as the fill value 0
+        if (btree == ~(uint64_t)0 + base_ || n == 0) return;
+        std::vector<Chunk> chunks;
+        walk_chunk_btree(btree, (unsigned)rank + 1, chunks, 0);
+        std::vector<uint8_t> raw;
+        for (const Chunk& c : chunks) {
+            need(c.addr, c.size);
+            raw.assign(buf_.begin() + (size_t)c.addr, buf_.begin() + (size_t)(c.addr + c.size));
+            for (size_t fi = filters.size(); fi-- > 0;) {          // undo the pipeline back to front
+                if (c.mask & (1u << fi)) continue;                 // this filter was skipped for this chunk
+                if (filters[fi] == 1) {
+                    raw = zl::zlib_inflate(raw.data(), raw.size(), (size_t)chunk_elems * elem);
+                } else if (filters[fi] == 2) {                     // shuffle: byte b of element e was stored at b * count + e
+                    const size_t cnt = raw.size() / elem;
+                    std::vector<uint8_t> un(raw.size());
+                    for (size_t e = 0; e < cnt; ++e)
+                        for (unsigned b = 0; b < elem; ++b) un[e * elem + b] = raw[(size_t)b * cnt + e];
+                    for (size_t t = cnt * elem; t < raw.size(); ++t) un[t] = raw[t];
+                    raw.swap(un);
+                } else if (filters[fi] == 3) {                     // fletcher32: four checksum bytes behind the data
+                    if (raw.size() < 4) throw FormatError("dataset '" + d.name + "': short fletcher32 chunk");
+                    raw.resize(raw.size() - 4);
+                }
+            }
+            if (raw.size() < chunk_elems * elem) throw FormatError("dataset '" + d.name + "': short chunk");
+            // scatter the chunk into the row-major dataset, clipping at the extent
+            std::vector<uint64_t> idx(rank, 0);
+            for (uint64_t e = 0; e < chunk_elems; ++e) {
+                bool inside = true;
+                uint64_t lin = 0;
+                for (size_t k = 0; k < rank; ++k) {
+                    const uint64_t g = c.off[k] + idx[k];
+                    if (g >= d.dims[k]) { inside = false; break; }
+                    lin = lin * d.dims[k] + g;
+                }
+                if (inside) {
+                    if (elem == 4) {
+                        std::memcpy(&d.data[(size_t)lin], raw.data() + e * 4, 4);
+                    } else {
+                        double v;
+                        std::memcpy(&v, raw.data() + e * 8, 8);
+                        d.data[(size_t)lin] = (float)v;
+                    }
+                }
+                for (size_t k = rank; k-- > 0;) {
+                    if (++idx[k] < cdims[k]) break;
+                    idx[k] = 0;
+                }
+            }
+        }
+    }
+
     void read_dataset(Node& d, const std::vector<Msg>& msgs) const {
         bool have_dims = false, have_layout = false;
         unsigned elem = 0;   // 4 = float32, 8 = float64
         uint64_t data_off = 0, data_size = 0;
-        bool compact = false;
+        bool compact = false, chunked = false;
+        uint64_t chunk_btree = 0;
+        std::vector<uint64_t> chunk_dims;        // rank + 1 entries, the last one is the element size
+        std::vector<unsigned> filters;           // filter ids in pipeline order (1 = deflate, 2 = shuffle, 3 = fletcher32)
         for (const Msg& m : msgs) {
             if (m.type == 0x0001) {
                 const unsigned ver = (unsigned)rd(m.body, 1), rank = (unsigned)rd(m.body + 1, 1);
@@ -275,10 +368,32 @@ private:
                     data_size = rd(m.body + 2, 2);
                     data_off = m.body + 4;
                     compact = true;
+                } else if (lclass == 2) {
+                    // chunked storage (what h5py writes for compressed or resizable datasets): rank + 1 chunk dimensions
+                    // (the last one is the element size) and a version-1 B-tree of raw chunks
+                    const unsigned cr = (unsigned)rd(m.body + 2, 1);
+                    chunk_btree = rd(m.body + 3, so_) + base_;
+                    for (unsigned i = 0; i < cr; ++i) chunk_dims.push_back(rd(m.body + 3 + so_ + 4u * i, 4));
+                    chunked = true;
                 } else {
-                    throw FormatError("chunked dataset '" + d.name + "' is not supported");
+                    throw FormatError("dataset '" + d.name + "': unknown storage layout class");
                 }
                 have_layout = true;
+            } else if (m.type == 0x000B) {
+                // filter pipeline, version 1 or 2
+                const unsigned ver = (unsigned)rd(m.body, 1), nf = (unsigned)rd(m.body + 1, 1);
+                uint64_t p = m.body + (ver == 1 ? 8 : 2);
+                for (unsigned i = 0; i < nf; ++i) {
+                    const unsigned id = (unsigned)rd(p, 2);
+                    unsigned name_len = 0;
+                    if (ver == 1 || id >= 256) { name_len = (unsigned)rd(p + 2, 2); p += 2; }
+                    const unsigned ncv = (unsigned)rd(p + 4, 2);
+                    p += 6;
+                    if (ver == 1) name_len = (name_len + 7u) & ~7u;
+                    p += name_len + 4u * ncv;
+                    if (ver == 1 && (ncv & 1u)) p += 4;
+                    filters.push_back(id);
+                }
             }
         }
         if (!have_dims || !have_layout) throw FormatError("dataset '" + d.name + "' lacks dataspace or layout");
@@ -287,6 +402,10 @@ private:
         for (size_t v : d.dims) {
             if (v != 0 && n > (uint64_t)buf_.size() / v) throw FormatError("dataset '" + d.name + "' larger than file");
             n *= v;
+        }
+        if (chunked) {
+            read_chunked(d, n, elem, chunk_btree, chunk_dims, filters);
+            return;
         }
         if (data_size < n * elem) throw FormatError("dataset '" + d.name + "': storage smaller than extent");
         need(data_off, n * elem);
@@ -369,9 +488,13 @@ class Writer {
 public:
     // kernel: [in][out] row-major (Keras); bias: [out].  Layers are written in the given order; the group of
     // layer i is names[i] (e.g. dense, dense_1, ...).
-    static std::vector<uint8_t> keras_weights(const std::vector<KerasLayer>& layers) {
+    // storage: 0 = contiguous (what Keras / h5py write for these small datasets, and what the shipped files hold),
+    //          1 = chunked, 2 = chunked + shuffle + deflate (zlib streams of stored blocks: the layout h5py produces
+    //          with compression="gzip", shuffle=True, without a compressor of our own)
+    static std::vector<uint8_t> keras_weights(const std::vector<KerasLayer>& layers, int storage = 0) {
         if (layers.empty()) throw FormatError("no layers to write");
         Writer w;
+        w.storage_ = storage;
         w.buf_.assign(96, 0);
         std::vector<std::pair<std::string, Child>> top;
         std::vector<std::string> layer_names;
@@ -407,8 +530,8 @@ public:
         return std::move(w.buf_);
     }
 
-    static void keras_weights(const std::string& path, const std::vector<KerasLayer>& layers) {
-        const std::vector<uint8_t> bytes = keras_weights(layers);
+    static void keras_weights(const std::string& path, const std::vector<KerasLayer>& layers, int storage = 0) {
+        const std::vector<uint8_t> bytes = keras_weights(layers, storage);
         FILE* f = std::fopen(path.c_str(), "wb");
         if (!f) throw FormatError("unable to create file '" + path + "'");
         const size_t put = std::fwrite(bytes.data(), 1, bytes.size(), f);
@@ -421,6 +544,7 @@ private:
     struct Child { uint64_t header = 0, btree = 0, heap = 0; bool is_group = false; };
     typedef std::vector<uint8_t> Bytes;   // one header message: type(2) size(2) flags(1) reserved(3) body (multiple of 8)
     std::vector<uint8_t> buf_;
+    int storage_ = 0;
 
     uint64_t alloc(size_t n) {
         const uint64_t off = (buf_.size() + 7u) & ~(uint64_t)7u;
@@ -464,7 +588,100 @@ private:
         for (const Bytes& m : msgs) { std::memcpy(buf_.data() + p, m.data(), m.size()); p += m.size(); }
         return at;
     }
+    static uint32_t adler32(const uint8_t* p, size_t n) {
+        uint32_t a = 1, b = 0;
+        for (size_t i = 0; i < n; ++i) { a = (a + p[i]) % 65521u; b = (b + a) % 65521u; }
+        return (b << 16) | a;
+    }
+    // zlib stream made of stored blocks
+    static Bytes zlib_stored(const Bytes& in) {
+        Bytes out = {0x78, 0x01};
+        size_t pos = 0;
+        do {
+            const size_t len = std::min<size_t>(65535, in.size() - pos);
+            const bool last = pos + len == in.size();
+            out.push_back(last ? 1 : 0);
+            out.push_back((uint8_t)(len & 255)); out.push_back((uint8_t)(len >> 8));
+            out.push_back((uint8_t)(~len & 255)); out.push_back((uint8_t)((~len >> 8) & 255));
+            out.insert(out.end(), in.begin() + (long)pos, in.begin() + (long)(pos + len));
+            pos += len;
+        } while (pos < in.size());
+        const uint32_t ad = adler32(in.data(), in.size());
+        for (int s = 24; s >= 0; s -= 8) out.push_back((uint8_t)(ad >> s));
+        return out;
+    }
+    // chunked dataset: chunks of at most 8 rows (rank 2) / 16 elements (rank 1), one leaf node of a version-1 chunk B-tree
+    Child dataset_chunked(const std::vector<size_t>& dims, const std::vector<float>& data) {
+        const size_t rank = dims.size();
+        std::vector<size_t> cd(rank);
+        if (rank == 1) cd[0] = std::min<size_t>(dims[0], 16);
+        else { cd[0] = std::min<size_t>(dims[0], 8); for (size_t k = 1; k < rank; ++k) cd[k] = dims[k]; }
+        size_t chunk_elems = 1;
+        for (size_t v : cd) chunk_elems *= v;
+        const size_t n_chunks = (dims[0] + cd[0] - 1) / cd[0];
+        if (n_chunks > 2 * 32) throw FormatError("too many chunks for a one-node chunk B-tree");
+        const bool filtered = storage_ == 2;
+        struct Stored { uint64_t addr; uint32_t size; size_t row0; };
+        std::vector<Stored> stored;
+        size_t inner = 1;
+        for (size_t k = 1; k < rank; ++k) inner *= dims[k];
+        for (size_t c = 0; c < n_chunks; ++c) {
+            Bytes raw(chunk_elems * 4, 0);
+            const size_t row0 = c * cd[0], rows = std::min(cd[0], dims[0] - row0);
+            std::memcpy(raw.data(), data.data() + row0 * inner, rows * inner * 4);
+            if (filtered) {
+                Bytes sh(raw.size());
+                const size_t cnt = raw.size() / 4;
+                for (size_t e = 0; e < cnt; ++e)
+                    for (unsigned b = 0; b < 4; ++b) sh[(size_t)b * cnt + e] = raw[e * 4 + b];
+                raw = zlib_stored(sh);
+            }
+            const uint64_t at = alloc(raw.size());
+            std::memcpy(buf_.data() + at, raw.data(), raw.size());
+            stored.push_back({at, (uint32_t)raw.size(), row0});
+        }
+        // B-tree node: "TREE", type 1, level 0, entries, siblings undefined, then key/child pairs and the final key
+        const size_t key = 8 + 8 * (rank + 1);
+        const uint64_t node = alloc(24 + (2 * 32 + 1) * key + 2 * 32 * 8);
+        std::memcpy(buf_.data() + node, "TREE", 4);
+        put(node + 4, 1, 1); put(node + 5, 0, 1); put(node + 6, stored.size(), 2);
+        put(node + 8, UNDEF, 8); put(node + 16, UNDEF, 8);
+        uint64_t p = node + 24;
+        for (const Stored& st : stored) {
+            put(p, st.size, 4); put(p + 4, 0, 4);
+            put(p + 8, st.row0, 8);
+            for (size_t k = 1; k <= rank; ++k) put(p + 8 + 8 * k, 0, 8);
+            put(p + key, st.addr, 8);
+            p += key + 8;
+        }
+        put(p, 0, 4); put(p + 4, 0, 4); put(p + 8, n_chunks * cd[0], 8);    // final key: one past the last chunk
+        for (size_t k = 1; k <= rank; ++k) put(p + 8 + 8 * k, 0, 8);
+        Bytes space, type, fill, layout, pipeline;
+        app(space, 1, 1); app(space, dims.size(), 1); app(space, 1, 1); app(space, 0, 5);
+        for (size_t d : dims) app(space, d, 8);
+        for (size_t d : dims) app(space, d, 8);
+        app(type, 0x11, 1); app(type, 0x20, 1); app(type, 0x1f, 1); app(type, 0, 1); app(type, 4, 4);
+        app(type, 0, 2); app(type, 32, 2); app(type, 23, 1); app(type, 8, 1); app(type, 0, 1); app(type, 23, 1); app(type, 127, 4);
+        app(fill, 2, 1); app(fill, 2, 1); app(fill, 2, 1); app(fill, 1, 1); app(fill, 0, 4);
+        app(layout, 3, 1); app(layout, 2, 1); app(layout, rank + 1, 1); app(layout, node, 8);
+        for (size_t v : cd) app(layout, v, 4);
+        app(layout, 4, 4);
+        std::vector<Bytes> msgs = {message(0x0001, 0, space), message(0x0003, 1, type), message(0x0005, 1, fill)};
+        if (filtered) {   // filter pipeline v1: shuffle (id 2, one client value: element size), deflate (id 1, one: level)
+            app(pipeline, 1, 1); app(pipeline, 2, 1); app(pipeline, 0, 6);
+            for (int f = 0; f < 2; ++f) {
+                app(pipeline, f == 0 ? 2 : 1, 2); app(pipeline, 0, 2); app(pipeline, 1, 2); app(pipeline, 1, 2);
+                app(pipeline, f == 0 ? 4 : 1, 4); app(pipeline, 0, 4);      // one client value + padding
+            }
+            msgs.push_back(message(0x000B, 0, pipeline));
+        }
+        msgs.push_back(message(0x0008, 0, layout));
+        Child c;
+        c.header = object_header(msgs);
+        return c;
+    }
     Child dataset(const std::vector<size_t>& dims, const std::vector<float>& data) {
+        if (storage_ != 0 && !data.empty()) return dataset_chunked(dims, data);
         const uint64_t raw = alloc(data.size() * 4);
         if (!data.empty()) std::memcpy(buf_.data() + raw, data.data(), data.size() * 4);
         Bytes space, type, fill, layout;
@@ -537,8 +754,8 @@ private:
     }
 };
 
-inline void write_keras_weights(const std::string& path, const std::vector<KerasLayer>& layers) {
-    Writer::keras_weights(path, layers);
+inline void write_keras_weights(const std::string& path, const std::vector<KerasLayer>& layers, int storage = 0) {
+    Writer::keras_weights(path, layers, storage);
 }
 
 }  // namespace h5

@@ -37,5 +37,7 @@ extern "C" void setRenderOptions(int scene, int maxSteps, int flags);
 extern "C" void setMathMode(int math);
 // sceneSDF (volumeRender_kernel.cu:217-230) as data: the op list is copied; selects NSDF_SCENE_PROGRAM (include/nsdf.h)
 extern "C" void setSceneProgram(const nsdf_scene_op* ops, int nOps);
+// the options render_kernel would use now (for callers of nsdf_render_views / nsdf_multi_render)
+extern "C" void getRenderOptions(nsdf_render_opts* out);
 extern "C" void getLastRenderStats(nsdf_render_stats* out);
 extern "C" void updateViewMatrices(float rxDeg, float ryDeg, float tx, float ty, float tz, int frameNumber);

@@ -79,3 +79,26 @@ def test_renderer_app_scene_program(gpu, tmp_path):
     assert np.array_equal(png, rgba[::-1, ::-1, :])
     bad = subprocess.run(cmd[:-4] + ["--scene", "nonsense"], capture_output=True, text=True)
     assert bad.returncode != 0
+
+
+def test_renderer_app_turntable_batches(gpu, tmp_path):
+    """--views N --batch B: the turntable of src/main.cpp:470-478 rendered in batches of B views per persistent launch
+    (nsdf_render_views), PNG files written by host threads; every frame equals the oracle's frame of that view."""
+    from PIL import Image
+    from oracle import oracle
+    W, H, N = 96, 64, 5
+    prefix = str(tmp_path) + "/"
+    cmd = [os.path.join(ROOT, "apps", "neuralSDFRenderer"), "-i", model_path("car_1"), "-o", prefix, "-W", str(W), "-H", str(H),
+           "--views", str(N), "--batch", "2", "--scene", "manysphere", "--math", "deterministic", "--stats",
+           "-M", os.path.join(MATCAPS, "blue.png")]
+    out = subprocess.run(cmd, capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert out.stdout.count("saving frame:") == N
+    om = oracle.Model.from_h5(model_path("car_1"))
+    mc = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    for i in range(N):
+        iv, nm = oracle.view_matrices(0.0, 360.0 * i / N)
+        ref = oracle.render(om, iv, nm, W, H, matcap=mc, scene=oracle.SCENE_MANYSPHERE, frame=i)["image"].reshape(H, W)
+        rgba = np.stack([ref & 255, (ref >> 8) & 255, (ref >> 16) & 255, (ref >> 24) & 255], -1).astype(np.uint8)
+        png = np.asarray(Image.open(prefix + "%03d.png" % i).convert("RGBA"))
+        assert np.array_equal(png, rgba[::-1, ::-1, :]), i

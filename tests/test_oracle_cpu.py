@@ -384,3 +384,38 @@ def test_oracle_workload_characterisation(built):
     r = oracle.render(m, iv, nm, 512, 512)
     assert abs(int(r["hit"].sum()) - 37897) <= 40
     assert abs(r["queries"] - 3126923) / 3126923 < 2e-3
+
+
+def test_h5_chunked_and_filtered_datasets(built, tmp_path):
+    """the reference reads whatever libhdf5 reads (src/neuralNetwork.cpp:85-151).  Chunked datasets (version-1
+    chunk B-tree), with and without the shuffle + deflate filter pipeline, load through the product reader bit for bit; a
+    deflate stream with dynamic Huffman blocks (zlib's own compressor) decodes through the same inflate the matcap PNGs use."""
+    import zlib
+    from cudaneuralrender_b200 import host
+    layers = host.read_keras_h5(model_path("plane_3"))
+    rng = np.random.default_rng(5)
+    layers.insert(3, (rng.standard_normal((32, 32)).astype(np.float32), rng.standard_normal(32).astype(np.float32)))  # 10 layers
+    for storage in (1, 2):
+        out = str(tmp_path / f"chunked{storage}.h5")
+        host.write_keras_h5(out, layers, storage)
+        raw = open(out, "rb").read()
+        assert b"TREE\x01\x00" in raw                     # a raw-data chunk B-tree node is in the file
+        back = host.read_keras_h5(out)
+        assert len(back) == len(layers)
+        for (k0, b0), (k1, b1) in zip(layers, back):
+            assert k0.shape == k1.shape and np.array_equal(k0.view(np.uint32), k1.view(np.uint32))
+            assert np.array_equal(b0.view(np.uint32), b1.view(np.uint32))
+    # the decoder behind the deflate filter (include/nsdf_inflate.hpp, shared with the PNG reader) on streams made by zlib's own
+    # compressor: stored, fixed-Huffman and dynamic-Huffman blocks, shuffled float data like an h5py gzip chunk
+    import ctypes as C
+    from cudaneuralrender_b200 import _capi as capi
+    k = layers[2][0]
+    shuffled = np.ascontiguousarray(k.view(np.uint8).reshape(-1, 4).T).tobytes()
+    for payload in (shuffled, open(model_path("plane_3"), "rb").read(), b"", b"a" * 70000, bytes(rng.integers(0, 256, 5000, dtype=np.uint8))):
+        for level in (0, 1, 6, 9):
+            z = zlib.compress(payload, level)
+            out = (C.c_ubyte * max(1, len(payload)))()
+            n_out = C.c_size_t(0)
+            rc = capi.lib().nsdf_zlib_inflate(z, len(z), out, len(payload), C.byref(n_out))
+            assert rc == 0 and n_out.value == len(payload) and bytes(out[:len(payload)]) == payload, (len(payload), level)
+    assert capi.lib().nsdf_zlib_inflate(b"\x78\x9c\xff\xff", 4, out, 1, C.byref(n_out)) != 0     # garbage is an error, not a crash

@@ -1,8 +1,12 @@
 #!/usr/bin/env python
-"""Development sweep: device time of a few frames under lists of tracer knobs (environment variables read per call by the
-development build of libnsdf.so).  usage: sweep.py [reps=N] [cases=a,b,..] 'K1=v1 K2=v2' 'K1=v3' ...   ('' = defaults)
+"""Development sweep: device time of a few frames under lists of tracer knobs.  lower-case names are nsdf_tuning fields (any
+build); NSDF_* names are environment variables, read per call by the DEVELOPMENT build only (lib=dev as first argument, after
+`make -C cudaneuralrender_b200/csrc dev`).  usage: sweep.py [lib=dev] [reps=N] [cases=a,b,..] 'k1=v1 k2=v2' 'k1=v3' ...
 cases: tanh0 (plane_1 1080p tanh view 0), head0, head8 (ry=45), head24 (ry=135), car512 (car_1 512^2 HEAD), k4 (3a3d 4K HEAD)"""
 import os, sys
+if "lib=dev" in sys.argv[1:]:
+    os.environ["NSDF_LIB"] = "dev"
+    sys.argv.remove("lib=dev")
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -27,8 +31,12 @@ ref = {}
 for cfg in configs:
     for k in list(os.environ):
         if k.startswith("NSDF_") and k not in base_env: del os.environ[k]
+    tuning = {}
     for kv in cfg.split():
-        k, v = kv.split("="); os.environ[k] = v
+        k, v = kv.split("=")
+        if k.islower(): tuning[k] = int(v)
+        else: os.environ[k] = v
+    host.setTuning(**tuning)
     row = []
     for c in cases:
         model, W, H, scene, ry = CASES[c]

@@ -2,6 +2,7 @@
 """Development probe: the tracer's timeline of long rays (NSDF_COOP_TIMELINE=1): when the pixels ran out, when the launch
 ended, and for the longest rays when they were pushed, popped and how fast they stepped (ns per step between events)."""
 import ctypes as C, os, sys
+os.environ["NSDF_LIB"] = "dev"      # the timeline hooks exist in the development build only (make -C cudaneuralrender_b200/csrc dev)
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
