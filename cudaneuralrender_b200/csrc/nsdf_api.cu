@@ -64,6 +64,13 @@ int finish_model(nsdf_model* m) {
     if (fused && L - 2 > nsdf::FUSED_MAX_SQ) fused = false;
     m->fused = fused;
     m->n_sq = fused ? L - 2 : 0;
+    bool generic = L >= 1 && L <= 16 && m->in[0] >= 1 && m->in[0] <= 128 && m->act[L - 1] == NSDF_ACT_TANH_LINEAR;
+    for (int l = 0; l < L && generic; ++l) {
+        if (m->out[l] < 1 || m->out[l] > 128) generic = false;
+        if (l < L - 1 && m->act[l] != NSDF_ACT_RELU) generic = false;
+        if (l > 0 && m->in[l] != m->out[l - 1]) generic = false;
+    }
+    m->generic = generic;
     NSDF_TRY(cudaGetDevice(&m->device));
     NSDF_TRY(cudaDeviceGetAttribute(&m->sm_count, cudaDevAttrMultiProcessorCount, m->device));
     NSDF_TRY(cudaMalloc(&m->d_params, m->h_params.size() * sizeof(float)));
@@ -127,6 +134,7 @@ int forward_dispatch(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int
         case NSDF_PREC_FP32_WARP:
             if (!m->fused || m->in[0] != 3) {
                 if (lattice) return NSDF_EUNSUPPORTED;
+                if (m->generic) return nsdf::generic_forward(m, d_x, d_y, n, stream);   // other widths / depths: still ONE fused launch
                 return layered_forward(m, d_x, d_y, n, stream);
             }
             return nsdf::fp32_forward(m, d_x, d_y, n, precision, lattice, res, lo, hi, first, stream);

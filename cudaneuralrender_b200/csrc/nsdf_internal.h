@@ -15,6 +15,7 @@ struct nsdf_model {
     std::vector<size_t> w_off, b_off;     // offsets (floats) into the packed array
     float* d_params = nullptr;            // same layout on the device (per-layer operators)
     bool fused = false;                   // 3 -> 32 x k -> 1, ReLU hidden, linear last
+    bool generic = false;                 // any other stack mlp_generic.cuh covers: <= 16 layers of <= 128 neurons, ReLU hidden, linear last
     int n_sq = 0;                         // number of 32x32 layers
     float* d_blob = nullptr;              // fused fp32 blob (mlp_fp32.cuh)
     uint32_t blob_bytes = 0;
@@ -55,6 +56,9 @@ namespace nsdf {
 // fp32 rungs + per-layer operator (nsdf_mlp.cu)
 int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res,
                  float lo, float hi, int64_t first, cudaStream_t stream);
+int generic_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, cudaStream_t stream);
+struct GenericNet;
+void generic_net_of(const nsdf_model* m, GenericNet* g);
 int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const float* d_b, int M, int K,
                        int64_t num_batches, int activation, cudaStream_t stream);
 

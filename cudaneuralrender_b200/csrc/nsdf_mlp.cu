@@ -4,6 +4,7 @@
 // =====================================================================================
 #include "lattice.cuh"
 #include "mlp_fp32.cuh"
+#include "mlp_generic.cuh"
 #include "nsdf_internal.h"
 
 namespace nsdf {
@@ -529,6 +530,48 @@ int fp32_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int pre
 }
 
 #endif  // NSDF_DEV_SCHEDULES
+
+// ---- any other dense stack, one fused launch (mlp_generic.cuh) -------------------------------------------------------
+__global__ void __launch_bounds__(128) mlp_generic_kernel(const __grid_constant__ GenericNet g, const float* __restrict__ xin,
+                                                          float* __restrict__ yout, long long n) {
+    extern __shared__ __align__(16) float s_params[];
+    const float* P = generic_stage(g, s_params);
+    const int in0 = g.dims[0], outL = g.dims[g.n_layers];
+    float a[GENERIC_MAX_WIDTH], z[GENERIC_MAX_WIDTH];
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        for (int k = 0; k < in0; ++k) a[k] = __ldg(xin + i * in0 + k);
+        mlp_generic_eval(g, P, a, z);
+        for (int o = 0; o < outL; ++o) yout[i * outL + o] = a[o];
+    }
+}
+
+void generic_net_of(const nsdf_model* m, GenericNet* g) {
+    g->params = m->d_params;
+    g->n_layers = m->n_layers;
+    g->dims[0] = m->in[0];
+    for (int l = 0; l < m->n_layers; ++l) {
+        g->dims[l + 1] = m->out[l];
+        g->w_off[l] = (unsigned int)m->w_off[l];
+        g->b_off[l] = (unsigned int)m->b_off[l];
+    }
+    g->n_params = (unsigned int)m->h_params.size();
+    g->staged = (size_t)g->n_params * sizeof(float) <= GENERIC_SMEM_LIMIT ? 1 : 0;
+}
+
+int generic_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, cudaStream_t stream) {
+    if (!m->generic) return NSDF_EUNSUPPORTED;
+    if (n == 0) return NSDF_OK;
+    GenericNet g;
+    generic_net_of(m, &g);
+    const size_t smem = g.staged ? (size_t)g.n_params * sizeof(float) : 0;
+    cudaError_t e = cudaFuncSetAttribute(mlp_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GENERIC_SMEM_LIMIT);
+    if (e != cudaSuccess) return (int)e;
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    const long long want = (n + 127) / 128;
+    const long long cap = (long long)sms * (smem > 100 * 1024 ? 1 : 4);
+    mlp_generic_kernel<<<(unsigned int)(want < cap ? want : cap), 128, smem, stream>>>(g, d_x, d_y, (long long)n);
+    return (int)cudaGetLastError();
+}
 
 int dense_layer_launch(const float* d_W, const float* d_A, float* d_Z, const float* d_b, int M, int K,
                        int64_t num_batches, int activation, cudaStream_t stream) {

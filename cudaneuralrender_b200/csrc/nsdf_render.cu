@@ -541,7 +541,11 @@ static void resolve_tuning(const nsdf_render_opts* opts, unsigned int total_idx,
 int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream) {
-    if (!m->fused || (m->in[0] != 3 && m->in[0] != 4)) return NSDF_EUNSUPPORTED;
+    if (m->in[0] != 3 && m->in[0] != 4) return NSDF_EUNSUPPORTED;
+    // shapes other than (3|4) -> 32 x k -> 1: the generic fused evaluator, one thread per pixel (any widths up to 128)
+    const bool generic = !m->fused;
+    if (generic && !(m->generic && m->out[m->n_layers - 1] == 1)) return NSDF_EUNSUPPORTED;
+    if (generic && n_views > 1) return NSDF_EUNSUPPORTED;
     if (n_views < 1 || n_views > 128) return NSDF_EINVAL;
     if (n_views > 1 && (long long)W * H > (1LL << 24)) return NSDF_EINVAL;   // RaySlot::pix carries the view in its top byte
     // the A/B schedules, the mixed-precision far field and the caller-set hand-over threshold exist in development builds only
@@ -625,7 +629,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
     }
     // staged frame stores (render_kernels.cuh emit_pixel / flush_tile): for tile-partitioned calls, whose d_out is a peer
     // GPU's memory in the multi-GPU gather, or on request
-    if (!simple && (opts->tile_world > 1 || (opts->flags & NSDF_RENDER_STAGED_STORES))) {
+    if (!simple && !generic && (opts->tile_world > 1 || (opts->flags & NSDF_RENDER_STAGED_STORES))) {
         if ((size_t)n_jobs > m->frame_stage_jobs) {
             if (m->d_frame_stage) cudaFree(m->d_frame_stage);
             m->d_frame_stage = nullptr;
@@ -652,6 +656,19 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
         e = cudaFuncSetAttribute(tile_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_done = true;
+    }
+    if (generic) {
+        GenericNet g;
+        generic_net_of(m, &g);
+        NSDF_PER_DEVICE_FLAG(gen_attr);
+        if (!gen_attr) {
+            e = cudaFuncSetAttribute(trace_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GENERIC_SMEM_LIMIT);
+            if (e != cudaSuccess) return (int)e;
+            gen_attr = true;
+        }
+        const unsigned int blocks = (rp.total_idx + 127u) / 128u;
+        trace_generic_kernel<<<blocks, 128, g.staged ? (size_t)g.n_params * sizeof(float) : 0, stream>>>(rp, g);
+        return (int)cudaGetLastError();
     }
     if (simple) {
         const unsigned int blocks = (rp.total_idx + 127u) / 128u;

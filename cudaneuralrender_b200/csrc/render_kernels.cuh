@@ -22,6 +22,7 @@
 #include "device_math.cuh"
 #include "scene_program.cuh"
 #include "mlp_fp32.cuh"
+#include "mlp_generic.cuh"
 #include "../../include/nsdf.h"
 
 namespace nsdf {
@@ -468,6 +469,28 @@ __global__ void __launch_bounds__(128) trace_simple_kernel(const __grid_constant
         float x[1][3] = {{q.x, q.y, q.z}}, y[1];
         mlp32_eval_thread<1>(s_w, rp.n_sq, x, y, rp.t4, rp.n_in == 4);
         if (slot.mode >= 0) slot_update(slot, y[0], q, rp, st);
+    }
+    flush_stats(st, rp.stats);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Any other network the reference's renderer would run (3 or 4 inputs, one output, any widths up to 128): one thread per
+// enumeration index with the generic fused evaluator (mlp_generic.cuh).  Same per-ray arithmetic (slot_start / slot_update).
+__global__ void __launch_bounds__(128) trace_generic_kernel(const __grid_constant__ RenderParams rp, const __grid_constant__ GenericNet g) {
+    extern __shared__ __align__(16) float s_params[];
+    const float* P = generic_stage(g, s_params);
+    const unsigned int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    RaySlot slot;
+    slot.mode = -1;
+    LocalStats st = {0, 0, 0, 0, 0, 0};
+    if (idx < rp.total_idx) slot_start(slot, idx, rp, st);
+    float a[GENERIC_MAX_WIDTH], z[GENERIC_MAX_WIDTH];
+    while (__ballot_sync(0xffffffffu, slot.mode >= 0)) {
+        const f3 q = (slot.mode >= 0) ? slot_query_point(slot) : f3{0.0f, 0.0f, 0.0f};
+        a[0] = q.x; a[1] = q.y; a[2] = q.z;
+        if (rp.n_in == 4) a[3] = rp.t4;
+        mlp_generic_eval(g, P, a, z);
+        if (slot.mode >= 0) slot_update(slot, a[0], q, rp, st);
     }
     flush_stats(st, rp.stats);
 }

@@ -33,6 +33,15 @@ def _bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
 
 
+def _matrix(host, x):
+    """Matrix(Shape(in, B)) holding the rows of x (element [b*in + c]), on the device."""
+    m = host.Matrix(x.shape[1], x.shape[0])
+    m.allocateMemory()
+    m.hostData[:] = x.ravel()
+    m.copyHostToDevice()
+    return m
+
+
 def test_native_library_is_loaded(env):
     from cudaneuralrender_b200 import _capi
     assert os.path.exists(_capi.LIB_PATH)
@@ -159,10 +168,14 @@ def test_layered_operators_match_fused(env):
     assert nn.layers[0].getXDim() == 3 and nn.layers[0].getYDim() == 32 and nn.getNumWeightParams() == 7296
 
 
-def test_non_fused_shapes_fall_to_layer_kernels(env):
-    """Arbitrary widths/depths go through the per-layer CUDA operator (still no CPU path)."""
-    torch, host, oracle = env["torch"], env["host"], env["oracle"]
-    for dims in ([3, 16, 8, 1], [5, 64, 64, 2], [3, 32, 1], [3, 32, 32, 32, 1]):
+def test_other_shapes_run_fused_and_render(env, tmp_path):
+    """the reference's forward and renderer take ANY dense stack (src/layers/denseLayer.cu:180-227,
+    src/volumeRender_kernel.cu:652-689).  Shapes other than (3|4) -> 32 x k -> 1 run through the generic fused evaluator
+    (csrc/mlp_generic.cuh): ONE launch per forward, bits of the oracle, for widths 16 / 64 / 128, mixed widths, several
+    outputs, 4 inputs; and their frames -- networks written with nsdf_h5_write_keras and loaded back -- equal the oracle's
+    frames byte for byte (a 64- and a 128-wide net that embed car_1, a random 16-wide and a mixed-width net)."""
+    torch, host, oracle, capi = env["torch"], env["host"], env["oracle"], env["capi"]
+    for dims in ([3, 16, 8, 1], [5, 64, 64, 2], [3, 32, 1], [3, 32, 32, 32, 1], [3, 128, 128, 1], [4, 64, 16, 128, 1], [3, 1]):
         om = oracle.Model.random(dims, seed=len(dims))
         nn = host.NeuralNetwork()
         for i, (W, b) in enumerate(om.layers()):
@@ -170,6 +183,50 @@ def test_non_fused_shapes_fall_to_layer_kernels(env):
         x = np.random.default_rng(0).uniform(-1, 1, (3001, dims[0])).astype(np.float32)
         y = nn.forward_tensor(torch.from_numpy(x).cuda().contiguous()).cpu().numpy()
         assert np.array_equal(_bits(y), _bits(oracle.mlp_forward(om, x).ravel())), dims
+        z = nn.forward_layered(_matrix(host, x)).deviceData[: y.size].cpu().numpy()      # the per-layer operators agree
+        assert np.array_equal(_bits(z), _bits(y)), dims
+
+    def embed(layers, width):
+        """car_1's 32-wide layers inside `width`-wide ones (extra neurons have zero weights and biases)."""
+        out = []
+        for i, (k, b) in enumerate(layers):
+            kin = k.shape[0] if i == 0 else width
+            kout = k.shape[1] if i == len(layers) - 1 else width
+            K = np.zeros((kin, kout), np.float32)
+            B = np.zeros(kout, np.float32)
+            K[:k.shape[0], :k.shape[1]] = k
+            B[:b.size] = b
+            out.append((K, B))
+        return out
+
+    car = host.read_keras_h5(model_path("car_1"))
+    rng = np.random.default_rng(3)
+    nets = {"w64": embed(car, 64), "w128": embed(car[:4] + car[-1:], 128),
+            "w16": [(0.6 * rng.standard_normal((3, 16)).astype(np.float32), 0.1 * rng.standard_normal(16).astype(np.float32)),
+                    (0.4 * rng.standard_normal((16, 16)).astype(np.float32), 0.1 * rng.standard_normal(16).astype(np.float32)),
+                    (0.3 * rng.standard_normal((16, 1)).astype(np.float32), np.array([0.05], np.float32))],
+            "mixed": embed(car[:3], 64)[:2] + [(np.pad(car[2][0], ((0, 32), (0, 0))), car[2][1])] + car[3:]}
+    matcap = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    iv, nm = oracle.view_matrices(0.0, 25.0)
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.copyViewMatrices(iv, nm, 0, 3)
+    W, H = 120, 88
+    for name, layers in nets.items():
+        path = str(tmp_path / (name + ".h5"))
+        host.write_keras_h5(path, layers)
+        nn = host.NeuralNetwork()
+        assert nn.load(path)
+        assert capi.lib().nsdf_model_is_fused(nn.handle()) == 0
+        om = oracle.Model.from_h5(path)
+        for scene in (host.SCENE_TANH, host.SCENE_MANYSPHERE):
+            host.setSceneOptions(scene, 6000)
+            img, stats = host.render_host(nn, W, H, matcap)
+            ref = oracle.render(om, iv, nm, W, H, matcap=matcap, scene=oracle.SCENE_TANH if scene == host.SCENE_TANH else oracle.SCENE_MANYSPHERE)
+            assert np.array_equal(img, ref["image"]), (name, scene)
+            assert stats["queries"] == ref["queries"] and stats["pixels"] == W * H, (name, scene)
+        if name in ("w64", "w128"):
+            assert int((ref["image"] != 0).sum()) > 200      # the embedded car is there
+    host.setSceneOptions()
 
 
 def test_lattice_matches_explicit_points(env):
