@@ -763,3 +763,32 @@ def test_error_behaviour(env):
     y = torch.zeros(10, device="cuda")
     assert L.nsdf_mlp_forward(nn.handle(), x.data_ptr(), y.data_ptr(), 10, 99, None) == 10001
     assert L.nsdf_dense_layer_forward(x.data_ptr(), x.data_ptr(), y.data_ptr(), y.data_ptr(), 1, 2, 3, 1, 0, None) == 10002
+
+
+def test_render_beside_a_busy_stream(env):
+    """The tracer's warps wait on one another (queues, termination counters), so it is launched cooperatively: with another
+    kernel occupying SMs on a second stream the launch waits for room instead of spinning on CTAs that cannot become resident.
+    Frames rendered beside a stream of long-running kernels equal the frame rendered alone."""
+    torch, host = env["torch"], env["host"]
+    nn, _ = _load(env, "plane_1")
+    W, H = 640, 360
+    host.copyStaticSettings(host.COLOR_FACING, 3)
+    host.updateViewMatrices((0.0, 30.0, 0.0), (0.0, 0.0, -2.0), 0)
+    host.setSceneOptions(host.SCENE_MANYSPHERE, 6000)
+    alone = torch.zeros(W * H, dtype=torch.int32, device="cuda")
+    host.render_kernel(alone, W, H, nn)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    a = torch.randn(4096, 4096, device="cuda")
+    outs = []
+    with torch.cuda.stream(side):
+        for _ in range(40):               # ~100 ms of GEMMs that fill the machine
+            a = (a @ a) * 1e-3
+    for _ in range(6):                    # renders on the default stream while the side stream is busy
+        o = torch.full((W * H,), 0x55, dtype=torch.int32, device="cuda")
+        host.render_kernel(o, W, H, nn)
+        outs.append(o)
+    torch.cuda.synchronize()
+    for o in outs:
+        assert torch.equal(o, alone)
+    host.setSceneOptions()
