@@ -8,6 +8,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # NSDF_LIB=dev selects the development build (make -C csrc dev: A/B schedules, knobs from the environment) for tools/ sweeps
 LIB_PATH = os.path.join(_HERE, "libnsdf_dev.so" if os.environ.get("NSDF_LIB") == "dev" else "libnsdf.so")
+if os.environ.get("NSDF_LIB_PATH"):      # development: an experimental build of the library
+    LIB_PATH = os.environ["NSDF_LIB_PATH"]
 
 NSDF_OK = 0
 ACT_RELU, ACT_TANH_LINEAR = 0, 1

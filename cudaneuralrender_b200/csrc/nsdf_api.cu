@@ -427,7 +427,7 @@ void nsdf_tuning_default(nsdf_tuning* t) {
     t->express_from_bulk = 1;
     t->express_rays = 1;
     t->express_solo_steps = 768;
-    t->tile_priority_steps = 32;
+    t->tile_priority_steps = -1;
     t->tile_priority_min_jobs = 128;
     t->tail_lanes = 0;
     t->tail_push_max = 2;

@@ -526,10 +526,15 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
 
 #else  // ---- product build --------------------------------------------------------------------------------------------------
 
-static void resolve_tuning(const nsdf_render_opts* opts, unsigned int total_idx, nsdf_tuning* T) {
+static void resolve_tuning(const nsdf_render_opts* opts, unsigned int total_idx, int n_views, nsdf_tuning* T) {
     nsdf_tuning_default(T);
     if (opts->tuning) *T = *opts->tuning;
-    if (T->express_period < 0) T->express_period = total_idx >= 3000000u ? 24 : 12;   // large calls are bound by the bulk
+    // Automatic choices (measured, profiles/r02_tuning_sweeps.txt).  A call of many views is pure throughput: the tails of its
+    // views hide behind each other's bulk, and once the pixels are gone the last long rays run alone in thinning warps anyway,
+    // so express SMs and the priority probe only cost (64 views: 10.39 -> 9.70 ms per frame without them; 8 views: equal).
+    const bool many_views = n_views >= 12;
+    if (T->express_period < 0) T->express_period = many_views ? 0 : (total_idx >= 3000000u ? 24 : 8);
+    if (T->tile_priority_steps < 0) T->tile_priority_steps = many_views ? 0 : 32;
     if (T->express_rays < 1) T->express_rays = 1;
     if (T->express_rays > 8) T->express_rays = 8;
     if (T->express_warps < 1) T->express_warps = 1;
@@ -601,7 +606,7 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
     rp.evict_steps = 1 << 30;
     rp.evict_steps_hi = 1 << 30;
     nsdf_tuning T;
-    resolve_tuning(opts, rp.total_idx, &T);
+    resolve_tuning(opts, rp.total_idx, n_views, &T);
 
     int rc = ensure_scratch(m, 0, XQUEUE_ENTRIES * (size_t)n_views);
     if (rc) return rc;

@@ -53,7 +53,10 @@ __device__ __forceinline__ void timeline_event(int pix, int steps, int kind) {
     }
 }
 
-constexpr int COOP_THREADS = 512;   // ONE CTA per SM (the launch pads its shared memory past half an SM): 16 warps, 4 per scheduler
+#ifndef NSDF_COOP_THREADS
+#define NSDF_COOP_THREADS 512
+#endif
+constexpr int COOP_THREADS = NSDF_COOP_THREADS;   // ONE CTA per SM (the launch pads its shared memory past half an SM): 16 warps, 4 per scheduler
 #ifndef NSDF_COOP_R
 #define NSDF_COOP_R 16
 #endif

@@ -204,7 +204,8 @@ typedef struct nsdf_camera {
  * handful of rays that need thousands of DEPENDENT network evaluations: "express" SMs take no pixels and hold
  * one such ray per lane (warp), stepping it at ~1.3 us instead of the ~14 us a ray pays inside a full 16-ray warp.            */
 typedef struct nsdf_tuning {
-    int express_period;      /* every express_period-th SM is an express SM; 0 = none; -1 = 12 (24 for calls >= 3 M pixels)   */
+    int express_period;      /* every express_period-th SM is an express SM; 0 = none; -1 = automatic: 8, 24 for calls of >= 3 M
+                                pixels, none for calls of >= 12 views (pure throughput: their tails overlap)                    */
     int express_steps;       /* a ray that has marched this many steps moves to a free express lane (160)                      */
     int express_warps;       /* lanes per express SM (4: one per scheduler steps fastest)                                       */
     int express_old_steps;   /* rays older than this (192) ask for a lane whenever steps & express_old_mask == 0 ...            */
@@ -212,7 +213,8 @@ typedef struct nsdf_tuning {
     int express_from_bulk;   /* 1: warps that still take pixels hand rays over too                                             */
     int express_rays;        /* rays a lane marches together (1; more measured slower for the longest chains)                  */
     int express_solo_steps;  /* with express_rays > 1: a lane holding a ray this old takes no company (768)                    */
-    int tile_priority_steps; /* probe every 8th pixel for this many steps and trace jobs with grazing rays first (32; 0 = off) */
+    int tile_priority_steps; /* probe every 8th pixel for this many steps and trace jobs with grazing rays first (0 = off;
+                                -1 = automatic: 32, off for calls of >= 12 views)                                                 */
     int tile_priority_min_jobs; /* ... for calls of at least this many (view, tile) jobs (128)                                 */
     int tail_lanes;          /* once the pixels are gone, warps 0..tail_lanes-1 of every SM are lanes too (0 = off)             */
     int tail_push_max;       /* ... fed by warps that are down to this many marching rays (2)                                   */

@@ -15,7 +15,11 @@ from cudaneuralrender_b200 import host
 CASES = {"tanh0": ("plane_1", 1920, 1080, host.SCENE_TANH, 0.0), "head0": ("plane_1", 1920, 1080, host.SCENE_MANYSPHERE, 0.0),
          "head8": ("plane_1", 1920, 1080, host.SCENE_MANYSPHERE, 45.0), "head24": ("plane_1", 1920, 1080, host.SCENE_MANYSPHERE, 135.0),
          "car512": ("car_1", 512, 512, host.SCENE_MANYSPHERE, 0.0),
-         "k4": ("3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160, host.SCENE_MANYSPHERE, 0.0)}
+         "k4": ("3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160, host.SCENE_MANYSPHERE, 0.0),
+         "k4r8": ("3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160, host.SCENE_MANYSPHERE, 0.0),     # rank 0's share of an 8-way tile partition
+         "k4r4": ("3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160, host.SCENE_MANYSPHERE, 0.0),
+         "k4r8t": ("3a3d4a90a2db90b4203936772104a82d.obj", 3840, 2160, host.SCENE_TANH, 0.0)}
+WORLD = {"k4r8": 8, "k4r4": 4, "k4r8t": 8}
 reps, cases, configs = 5, ["tanh0", "head0", "head8"], []
 for a in sys.argv[1:]:
     if a.startswith("reps="): reps = int(a[5:])
@@ -46,12 +50,13 @@ for cfg in configs:
         host.updateViewMatrices((0.0, ry, 0.0), (0.0, 0.0, -2.0), 0)
         host.setSceneOptions(scene, 6000, 0, 0, host.MATH_REFERENCE)
         frame = torch.zeros(W * H, dtype=torch.int32, device="cuda")
-        for _ in range(2): host.render_kernel(frame, W, H, nn, matcap)
+        tw = WORLD.get(c, 1)
+        for _ in range(2): host.render_kernel(frame, W, H, nn, matcap, tile_world=tw)
         ts = []
         for _ in range(reps):
             flush.zero_()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(); host.render_kernel(frame, W, H, nn, matcap); b.record(); torch.cuda.synchronize()
+            a.record(); host.render_kernel(frame, W, H, nn, matcap, tile_world=tw); b.record(); torch.cuda.synchronize()
             ts.append(a.elapsed_time(b))
         img = frame.cpu().numpy()
         if c not in ref: ref[c] = img

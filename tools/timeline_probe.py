@@ -8,11 +8,12 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from cudaneuralrender_b200 import host, _capi as capi
 model, W, H = sys.argv[1], int(sys.argv[2]), int(sys.argv[3])
-scene, ry = host.SCENE_TANH, 0.0
+scene, ry, tile_world = host.SCENE_TANH, 0.0, 1
 for kv in sys.argv[4:]:
     k, v = kv.split("=")
     if k == "SCENE": scene = int(v)          # 0 tanh, 1 manySphere (the reference's HEAD)
     elif k == "RY": ry = float(v)
+    elif k == "TILE_WORLD": tile_world = int(v)   # time rank 0's share of a tile partition
     else: os.environ[k] = v
 nn = host.NeuralNetwork(); assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", model + ".h5"))
 matcap = host.Image(); assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", "blue.png"))
@@ -20,7 +21,7 @@ host.copyStaticSettings(host.COLOR_MATCAP, 3)
 host.updateViewMatrices((0.0, ry, 0.0), (0.0, 0.0, -2.0), 0)
 host.setSceneOptions(scene, 6000, 0, 0, host.MATH_REFERENCE)
 frame = torch.zeros(W * H, dtype=torch.int32, device="cuda")
-for _ in range(3): host.render_kernel(frame, W, H, nn, matcap)
+for _ in range(3): host.render_kernel(frame, W, H, nn, matcap, tile_rank=0, tile_world=tile_world)
 torch.cuda.synchronize()
 os.environ["NSDF_COOP_TIMELINE"] = "1"
 L = capi.lib()
@@ -28,7 +29,7 @@ n = 4 + 4 * 32768
 buf = np.zeros(n, dtype=np.uint64)
 L.nsdf_dev_timeline_read.argtypes = [C.c_void_p, C.c_int]
 L.nsdf_dev_timeline_read(buf.ctypes.data, n)     # clear
-host.render_kernel(frame, W, H, nn, matcap)
+host.render_kernel(frame, W, H, nn, matcap, tile_rank=0, tile_world=tile_world)
 assert L.nsdf_dev_timeline_read(buf.ctypes.data, n) == 0
 t0, t_dry, t_end, nev = (int(v) for v in buf[:4])
 print(f"launch {(t_end - t0) / 1e6:.2f} ms; last warp out of pixels at {(t_dry - t0) / 1e6:.2f} ms; events {nev}")

@@ -7,7 +7,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from cudaneuralrender_b200 import host
 W, H = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (1920, 1080)
-batches = [int(a) for a in sys.argv[3:]] or [2, 8, 16, 64]
+batches = [int(a) for a in sys.argv[3:] if "=" not in a] or [2, 8, 16, 64]
+tuning = {a.split("=")[0]: int(a.split("=")[1]) for a in sys.argv[3:] if "=" in a}     # nsdf_tuning knobs for the batched calls
 nn = host.NeuralNetwork(); assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", "plane_1.h5"))
 matcap = host.Image(); assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", "blue.png"))
 host.copyStaticSettings(host.COLOR_MATCAP, 3)
@@ -30,7 +31,9 @@ for B in batches:
         for s in range(0, N, B):
             cams = host.view_cameras(views[s:s + B])
             host.render_views(out[s * W * H:(s + B) * W * H], W, H, nn, cams, matcap)
+    host.setTuning(**tuning)
     out.zero_(); batched(); torch.cuda.synchronize()
     eq = bool(np.array_equal(out.cpu().numpy(), ref))
     a.record(); batched(); b.record(); torch.cuda.synchronize()
-    print(f"batches of {B:3d}: {a.elapsed_time(b) / N:.2f} ms per frame, bytes equal to one-by-one: {eq}", flush=True)
+    host.setTuning()
+    print(f"batches of {B:3d} {tuning or ''}: {a.elapsed_time(b) / N:.2f} ms per frame, bytes equal to one-by-one: {eq}", flush=True)
