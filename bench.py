@@ -583,8 +583,10 @@ def run_native(args):
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         if tj.get("tracer_source_sha") == tracer_source_sha():
             k = tj["trace_coop_kernel"]
-            traffic = k["dram_bytes_read"] + k["dram_bytes_write"]
-            traffic_note = f"dram bytes per launch from the ncu --set full capture {tj.get('capture', '')} of these tracer sources"
+            per_frame = (k["dram_bytes_read"] + k["dram_bytes_write"]) / k.get("frames_in_launch", 1)
+            traffic = per_frame * len(my_views)          # one launch per step and rank = len(my_views) frames
+            traffic_note = (f"dram bytes per launch ({len(my_views)} frames), scaled per frame from the ncu --set full capture "
+                            f"{tj.get('capture', '')} of these tracer sources")
         else:
             traffic_note = "profiles/ncu_traffic.json was captured from other tracer sources than the ones running: not quoted"
     except Exception:
