@@ -134,41 +134,32 @@ __device__ __forceinline__ void many_sphere_len2(f3 p, double zoff, float (&len2
         cx = (float)__dsub_rn((double)cx, 0.4);
     }
 }
-__device__ __forceinline__ float many_sphere_pre(f3 p, double zoff) {
-    float l[9];
-    many_sphere_len2(p, zoff, l);
-    float m = l[0];
-#pragma unroll
-    for (int i = 1; i < 9; ++i) m = (l[i] < m) ? l[i] : m;
-    bool ok = true;       // a NaN anywhere (a NaN point) sends the query the long way
-#pragma unroll
-    for (int i = 0; i < 9; ++i) ok = ok && (l[i] == l[i]);
-    return ok ? m : -1.0f;
-}
 // The chain itself for a point that IS near a sphere (rays grazing a sphere stay in this case for thousands of steps, so it
 // is the frame's critical path: measured 2.7 us per dependent step with the reference's loop against 1.3 us elsewhere).
-// Same nine smooth unions in the same order, but a sphere whose squared distance proves d_i - s >= k for every value s can
-// take along the chain (the running s never exceeds nSDF: a smooth union is <= min(d1, d2) up to an ulp, covered by the
-// margin) is the identity and is skipped without its square root or its double-precision blend; typically one sphere is left.
-__device__ __noinline__ float many_sphere_union_chain(f3 p, float nsdf, double zoff, bool ref) {
+// Same smooth unions in the same order, but a sphere whose squared distance proves d_i - s >= k for every value s can take
+// along the chain (the running s never exceeds nSDF: a smooth union is <= min(d1, d2) up to an ulp, covered by the margin) is
+// the identity and is skipped without its square root or its double-precision blend; typically one or two spheres are left.
+// len2 are the nine squared centre distances many_sphere_len2 has just produced; the loop walks the set bits of the
+// near-sphere mask (lanes of a warp work on different spheres in the same iteration), picking its len2 with selects.
+__device__ __forceinline__ float many_sphere_union_chain(const float (&len2)[9], float nsdf, bool ref) {
     const bool plain = nsdf != 0.0f && fabsf(nsdf) <= 1.0e30f;
     const float thr = nsdf + 0.11002f;
     const float thr2 = (thr * thr) * 1.000001f;
-    float s = nsdf;
-    float cx = p.x;
-    float cy = (float)__dsub_rn((double)p.y, 0.6);
-    const float cz = (float)__dadd_rn((double)p.z, zoff);
-    const float zz = cz * cz;
-#pragma unroll 1      // rolled on purpose: one copy of the blend keeps this function (and the registers its callers must save) small
+    unsigned int near = 0u;
+#pragma unroll
     for (int i = 0; i < 9; ++i) {
-        if (i % 3 == 0) {
-            cy = (float)__dadd_rn((double)cy, 0.4);
-            cx = p.x + 0.5f;
-        }
-        const float len2 = zz + fmaf(cx, cx, cy * cy);
-        const bool far = plain && len2 <= 1.0e30f && (thr <= 0.0f || len2 >= thr2);
-        if (!far) s = smooth_union(s, __fsqrt_rn(len2) + (-0.1f), 0.01f, ref);
-        cx = (float)__dsub_rn((double)cx, 0.4);
+        const bool far = plain && len2[i] <= 1.0e30f && (thr <= 0.0f || len2[i] >= thr2);
+        near |= far ? 0u : (1u << i);
+    }
+    float s = nsdf;
+#pragma unroll 1
+    while (near) {
+        const int i = __ffs(near) - 1;
+        near &= near - 1u;
+        float l = len2[0];
+#pragma unroll
+        for (int j = 1; j < 9; ++j) l = (i == j) ? len2[j] : l;
+        s = smooth_union(s, __fsqrt_rn(l) + (-0.1f), 0.01f, ref);
     }
     return s;
 }
@@ -183,12 +174,19 @@ __device__ __forceinline__ float many_sphere_union(f3 p, float nsdf, double zoff
     const bool plain = nsdf != 0.0f && fabsf(nsdf) <= 1.0e30f;
     const float thr = nsdf + 0.11002f;
     if (plain && rem >= 0.0f && (thr <= 0.0f || rem >= thr)) return nsdf;
-    const float m = many_sphere_pre(p, zoff);
-    const bool valid = m >= 0.0f && m <= 1.0e30f;
+    float l[9];
+    many_sphere_len2(p, zoff, l);
+    float m = l[0];
+    bool ok = true;       // a NaN anywhere (a NaN point) sends the query the long way
+#pragma unroll
+    for (int i = 1; i < 9; ++i) m = (l[i] < m) ? l[i] : m;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) ok = ok && (l[i] == l[i]);
+    const bool valid = ok && m <= 1.0e30f;
     rem = valid ? __fsqrt_rd(m) - 3.0e-6f : -1.0f;
     const float thr2 = nsdf + 0.11001f;
     if (plain && valid && (thr2 <= 0.0f || m >= (thr2 * thr2) * 1.000001f)) return nsdf;
-    return many_sphere_union_chain(p, nsdf, zoff, ref);
+    return many_sphere_union_chain(l, nsdf, ref);
 }
 
 enum { SCENE_TANH = 0, SCENE_MANYSPHERE = 1 };

@@ -203,7 +203,7 @@ template <> struct ActVec<4> {
     static __device__ __forceinline__ void get(const float4& v, float (&a)[4]) { a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w; }
 };
 // act: this thread's column (element k at act[k * stride]); P = 2 or 4 points per thread.
-template <int P>
+template <int P, int KU = 4>
 __device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw, int n_sq,
                                                     typename ActVec<P>::type* __restrict__ act, int stride,
                                                     const float (&x)[P][3], float (&y)[P], float t4 = 0.0f,
@@ -239,7 +239,7 @@ __device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw
             for (int p = 0; p < P; ++p) z[o][p] = 0.0f;
         }
         const float4* Wt = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS);
-#pragma unroll 4
+#pragma unroll KU
         for (int k = 0; k < 32; ++k) {
             float av[P];
             ActVec<P>::get(act[k * stride], av);

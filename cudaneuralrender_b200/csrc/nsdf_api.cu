@@ -431,6 +431,12 @@ void nsdf_tuning_default(nsdf_tuning* t) {
     t->tile_priority_min_jobs = 128;
     t->tail_lanes = 0;
     t->tail_push_max = 2;
+    t->bulk4 = -1;
+    t->bulk4_evict_steps = 256;
+    t->bulk4_period = 12;
+    t->bulk4_drain = 32;
+    t->bulk4_refill_min = 4;
+    t->bulk4_unroll = 2;
 }
 
 int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,

@@ -15,6 +15,7 @@
 #include "trace_tc.cuh"
 #endif
 #include "tile_priority.cuh"
+#include "trace_bulk4.cuh"
 
 namespace nsdf {
 
@@ -539,6 +540,13 @@ static void resolve_tuning(const nsdf_render_opts* opts, unsigned int total_idx,
     if (T->express_rays > 8) T->express_rays = 8;
     if (T->express_warps < 1) T->express_warps = 1;
     if (T->express_warps > COOP_THREADS / 32) T->express_warps = COOP_THREADS / 32;
+    if (T->bulk4 < 0) T->bulk4 = 0;
+    if (T->bulk4_evict_steps < 8) T->bulk4_evict_steps = 8;
+    if (T->bulk4_period == 1) T->bulk4_period = 2;     // somebody has to take pixels
+    if (T->bulk4_drain < 0) T->bulk4_drain = 0;
+    if (T->bulk4_drain > 128) T->bulk4_drain = 128;
+    if (T->bulk4_refill_min < 1) T->bulk4_refill_min = 1;
+    if (T->bulk4_refill_min > 64) T->bulk4_refill_min = 64;
 }
 
 // The product launcher: one schedule (the cooperative persistent tracer, trace_coop.cuh) plus the one-thread-per-pixel
@@ -702,6 +710,33 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
         e = cudaGetLastError();
         if (e != cudaSuccess) return (int)e;
         rp.tile_order = d_order;
+    }
+
+    // ---- calls of many views: the four-rays-per-lane throughput tracer (trace_bulk4.cuh), one CTA of 256 threads per SM
+    if (T.bulk4 > 0 && (size_t)rp.total_idx >= (size_t)sms * (B4_THREADS / 32) * 128u * 4u) {
+        NSDF_PER_DEVICE_FLAG(b4_attr);
+        const size_t smem = bulk4_smem(m->blob_bytes);
+        const void* b4_kernel = T.bulk4_unroll == 1 ? (const void*)trace_bulk4_kernel<1>
+                                : T.bulk4_unroll == 4 ? (const void*)trace_bulk4_kernel<4> : (const void*)trace_bulk4_kernel<2>;
+        if (!b4_attr) {
+            for (const void* k : {(const void*)trace_bulk4_kernel<1>, (const void*)trace_bulk4_kernel<2>, (const void*)trace_bulk4_kernel<4>}) {
+                e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return (int)e;
+            }
+            b4_attr = true;
+        }
+        rc = ensure_scratch(m, B4_RING_ENTRIES, 0);
+        if (rc) return rc;
+        e = cudaMemsetAsync(m->d_queue, 0, (size_t)B4_RING_ENTRIES * sizeof(StragglerEntry), stream);   // no stale `ready` stamps
+        if (e != cudaSuccess) return (int)e;
+        rp.queue = reinterpret_cast<StragglerEntry*>(m->d_queue);
+        rp.queue_capacity = B4_RING_ENTRIES;
+        rp.evict_steps_hi = T.bulk4_evict_steps;
+        rp.consumer_period = T.bulk4_period > 0 ? (unsigned int)T.bulk4_period : 0u;
+        rp.hybrid = T.bulk4_drain;
+        rp.b4_refill_min = T.bulk4_refill_min;
+        void* args[] = {&rp};
+        return (int)cudaLaunchCooperativeKernel(b4_kernel, dim3((unsigned int)sms), dim3(B4_THREADS), args, smem, stream);
     }
 
     // ---- one persistent, cooperative launch: one CTA per SM (trace_coop.cuh)

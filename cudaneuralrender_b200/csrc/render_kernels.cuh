@@ -96,6 +96,7 @@ struct RenderParams {
     int hybrid;                    // trace_coop_kernel: producing warps march one ray per LANE (mlp32_eval_thread, 32 rays per warp,
                                    // a third of the shared-memory wavefronts per query) and hand rays that reach evict_steps_hi
                                    // steps to the cooperative consumers on the quiet SMs; out of pixels they become consumers
+    int b4_refill_min;             // trace_bulk4_kernel: a producer warp asks for pixels once this many of its 128 slots are idle
     nsdf_render_stats* stats;
 };
 
