@@ -59,7 +59,7 @@ def tracer_source_sha():
     """sha of the tracer's sources: profiles/ncu_traffic.json is only quoted when it was captured from these bytes."""
     h = hashlib.sha256()
     d = os.path.join(ROOT, "cudaneuralrender_b200", "csrc")
-    for f in ("trace_coop.cuh", "render_kernels.cuh", "mlp_fp32.cuh", "device_math.cuh", "nsdf_render.cu"):
+    for f in ("trace_coop.cuh", "trace_bulk4.cuh", "render_kernels.cuh", "mlp_fp32.cuh", "device_math.cuh", "nsdf_render.cu"):
         try:
             h.update(open(os.path.join(d, f), "rb").read())
         except OSError:
@@ -578,11 +578,15 @@ def run_native(args):
                                           "queries_equal": bool(det["queries"] == r["queries"]), "queries": det["queries"],
                                           "note": "the timed frame's view 0 in NSDF_MATH_DETERMINISTIC against the CPU oracle's frame, all pixels"}
 
+    # which of the library's kernels a step launches (csrc/nsdf_render.cu resolve_tuning): calls of >= 4 views run on the
+    # four-rays-per-lane throughput tracer, smaller ones on the cooperative tracer; calls of < 12 views probe and sort the tiles first
+    top_kernel = "trace_bulk4_kernel" if len(my_views) >= 4 else "trace_coop_kernel"
+    launches_per_step = 1 if len(my_views) >= 12 else 3
     traffic, traffic_note = None, "no capture of the current tracer sources under profiles/ncu_traffic.json"
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        if tj.get("tracer_source_sha") == tracer_source_sha():
-            k = tj["trace_coop_kernel"]
+        if tj.get("tracer_source_sha") == tracer_source_sha() and top_kernel in tj:
+            k = tj[top_kernel]
             per_frame = (k["dram_bytes_read"] + k["dram_bytes_write"]) / k.get("frames_in_launch", 1)
             traffic = per_frame * len(my_views)          # one launch per step and rank = len(my_views) frames
             traffic_note = (f"dram bytes per launch ({len(my_views)} frames), scaled per frame from the ncu --set full capture "
@@ -604,8 +608,8 @@ def run_native(args):
         "ms_per_frame_per_gpu": ms_per_frame, "queries_per_s": q_set * K / (total_ms * 1e-3), "queries_per_frame_mean": q_frame,
         "hit_pixels_per_frame_mean": hits_set / N_VIEWS, "rank_time_min_over_max": min_ms / total_ms if total_ms else None,
         "e2e": {"value": e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": Ke},
-        "gpu_launches": 3 * K,   # per step and rank: tile_probe_kernel, tile_sort_kernel, trace_coop_kernel over all the rank's views
-        "roofline": {"kernel": "trace_coop_kernel", "bound": "tensor", "achieved": achieved, "peak": pk["tflops_burst"],
+        "gpu_launches": launches_per_step * K,   # per step and rank: (tile_probe_kernel, tile_sort_kernel,) the tracer over all the rank's views
+        "roofline": {"kernel": top_kernel, "bound": "tensor", "achieved": achieved, "peak": pk["tflops_burst"],
                      "unit": "TFLOP/s", "frac": achieved / pk["tflops_burst"], "traffic": traffic, "traffic_note": traffic_note,
                      "peak_source": pk["source"], "frac_of_fp32_alu": achieved / FP32_ALU_TFLOPS,
                      "note": "per GPU; algorithmic FLOP = MLP evaluations (counted on the device) x 14592 over the step's device time, against "

@@ -432,10 +432,10 @@ void nsdf_tuning_default(nsdf_tuning* t) {
     t->tail_lanes = 0;
     t->tail_push_max = 2;
     t->bulk4 = -1;
-    t->bulk4_evict_steps = 256;
-    t->bulk4_period = 12;
-    t->bulk4_drain = 32;
-    t->bulk4_refill_min = 4;
+    t->bulk4_evict_steps = 0;
+    t->bulk4_period = 0;
+    t->bulk4_drain = 16;
+    t->bulk4_refill_min = 16;
     t->bulk4_unroll = 2;
 }
 

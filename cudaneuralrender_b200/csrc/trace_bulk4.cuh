@@ -179,7 +179,10 @@ __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid
         // and the network outputs pass through the warp's activation block, which the evaluator only overwrites after reading x.
         float* const xq = reinterpret_cast<float*>(act4);      // xq[(j * 32) * 4 + p] = coordinate j of slot p (this lane's float4s)
 #pragma unroll 1
-        for (int p = 0; p < B4_P; ++p) sst[(p * B4_WORDS + 2) * 32] = (uint32_t)-1;
+        for (int p = 0; p < B4_P; ++p) {
+            sst[(p * B4_WORDS + 2) * 32] = (uint32_t)-1;
+            xq[0 * 128 + p] = 0.0f; xq[1 * 128 + p] = 0.0f; xq[2 * 128 + p] = 0.0f;
+        }
         bool exhausted = false;     // warp-uniform
         const int refill_min = rp.b4_refill_min;
         for (;;) {
@@ -209,7 +212,10 @@ __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid
                         if (idx < rp.total_idx) {
                             RaySlot s;
                             slot_start(s, idx, rp, st, flush_g);
-                            if (s.mode >= 0) b4_store(sst, p, s);
+                            if (s.mode >= 0) {
+                                b4_store(sst, p, s);
+                                xq[0 * 128 + p] = s.p.x; xq[1 * 128 + p] = s.p.y; xq[2 * 128 + p] = s.p.z;
+                            }
                         }
                         ++idx;
                     }
@@ -218,17 +224,8 @@ __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid
                 if (base + (unsigned int)total >= rp.total_idx) exhausted = true;
             }
             if (n_busy == 0) break;
-            // ---- query points of the busy slots
-#pragma unroll 1
-            for (int p = 0; p < B4_P; ++p) {
-                f3 q = f3{0.0f, 0.0f, 0.0f};
-                if ((int)sst[(p * B4_WORDS + 2) * 32] >= 0) {
-                    RaySlot s;
-                    b4_load(sst, p, s);
-                    q = slot_query_point(s);
-                }
-                xq[0 * 128 + p] = q.x; xq[1 * 128 + p] = q.y; xq[2 * 128 + p] = q.z;
-            }
+            // ---- one network evaluation for the four slots of every lane (their query points are in place: written when a ray
+            // started and by the previous update; zeros for idle slots)
             float x[B4_P][3], y[B4_P];
             {
                 const float4 x0 = act4[0], x1 = act4[32], x2 = act4[64];
@@ -236,17 +233,19 @@ __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid
                 x[0][1] = x1.x; x[1][1] = x1.y; x[2][1] = x1.z; x[3][1] = x1.w;
                 x[0][2] = x2.x; x[1][2] = x2.y; x[2][2] = x2.z; x[3][2] = x2.w;
             }
-            mlp32_eval_thread_s<B4_P, KU>(s_w, rp.n_sq, act4, 32, x, y, rp.t4, rp.n_in == 4);
+            mlp32_eval_thread_s<B4_P, KU, false>(s_w, rp.n_sq, act4, 32, x, y, rp.t4, rp.n_in == 4);
             act4[0] = make_float4(y[0], y[1], y[2], y[3]);
-            // ---- ray updates; long rays, and the remnants of a warp that has nothing to refill from, go to the consumers
+            // ---- ray updates and the next query points; long rays, and the remnants of a warp that has nothing to refill from,
+            // go to the consumers
             const bool drain = exhausted && n_busy <= rp.hybrid;
 #pragma unroll 1
             for (int p = 0; p < B4_P; ++p) {
                 int flush_g = -1;
                 RaySlot s;
                 s.mode = (int)sst[(p * B4_WORDS + 2) * 32];
+                const bool was_busy = s.mode >= 0;
                 bool go = false;
-                if (s.mode >= 0) {
+                if (was_busy) {
                     b4_load(sst, p, s);
                     const f3 q = slot_query_point(s);
                     slot_update(s, xq[p], q, rp, st, flush_g);
@@ -254,10 +253,16 @@ __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid
                 }
                 flush_completed(rp, flush_g, lane);
                 ring_push(s, go, rp, st);
-                if ((int)sst[(p * B4_WORDS + 2) * 32] >= 0) {
-                    if (s.mode >= 0) b4_store(sst, p, s);
-                    else sst[(p * B4_WORDS + 2) * 32] = (uint32_t)-1;
+                f3 qn = f3{0.0f, 0.0f, 0.0f};
+                if (was_busy) {
+                    if (s.mode >= 0) {
+                        b4_store(sst, p, s);
+                        qn = slot_query_point(s);
+                    } else {
+                        sst[(p * B4_WORDS + 2) * 32] = (uint32_t)-1;
+                    }
                 }
+                xq[0 * 128 + p] = qn.x; xq[1 * 128 + p] = qn.y; xq[2 * 128 + p] = qn.z;
             }
         }
         if (lane == 0) { __threadfence(); atomicAdd(pc + 3, 1u); }

@@ -218,13 +218,15 @@ typedef struct nsdf_tuning {
     int tile_priority_min_jobs; /* ... for calls of at least this many (view, tile) jobs (128)                                 */
     int tail_lanes;          /* once the pixels are gone, warps 0..tail_lanes-1 of every SM are lanes too (0 = off)             */
     int tail_push_max;       /* ... fed by warps that are down to this many marching rays (2)                                   */
-    int bulk4;               /* calls of many views on the four-rays-per-lane throughput tracer (csrc/trace_bulk4.cuh):
-                                1 = on, 0 = off, -1 = automatic                                                                  */
-    int bulk4_evict_steps;   /* ... a ray still marching after this many steps moves to the consumer warps (256)                */
-    int bulk4_period;        /* ... every bulk4_period-th SM consumes from the start (12)                                       */
-    int bulk4_drain;         /* ... a producer warp out of pixels hands its rays over once this few are left of its 128 (32)    */
-    int bulk4_refill_min;    /* ... a producer warp asks for new pixels once this many of its 128 slots are idle (4)            */
-    int bulk4_unroll;        /* ... k-unroll of the evaluator's inner loop: 1, 2 or 4 (instruction-cache footprint)             */
+    int bulk4;               /* calls of several views on the four-rays-per-lane throughput tracer (csrc/trace_bulk4.cuh):
+                                1 = on, 0 = off, -1 = automatic (calls of >= 4 views)                                            */
+    int bulk4_evict_steps;   /* ... a ray still marching after this many steps moves to the consumer warps (0 = never: measured
+                                best; consumers then only finish what thinned-out warps hand over at the end of the call)       */
+    int bulk4_period;        /* ... every bulk4_period-th SM consumes from the start (0 = none)                                 */
+    int bulk4_drain;         /* ... a warp that is out of pixels hands its rays over once this few are left of its 128 (16)     */
+    int bulk4_refill_min;    /* ... a warp asks for new pixels once this many of its 128 slots are idle (16)                    */
+    int bulk4_unroll;        /* ... k-unroll of the evaluator's inner loop: 1, 2 or 4 (2: the loop body must stay in the
+                                instruction cache next to the ray code)                                                          */
 } nsdf_tuning;
 void nsdf_tuning_default(nsdf_tuning* t);
 /* 1 if this library was built with -DNSDF_DEV_SCHEDULES (libnsdf_dev.so: superseded A/B schedules, mixed-precision far field,

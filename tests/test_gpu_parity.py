@@ -748,6 +748,55 @@ def test_batched_views_and_staged_stores(env):
     host.setSceneOptions()
 
 
+def test_throughput_tracer_for_many_views(env):
+    """Calls of >= 4 views of enough pixels run on trace_bulk4_kernel (four rays per lane, ring queue to cooperative consumers):
+    frames and query counts equal the cooperative tracer's (nsdf_tuning.bulk4 = 0) and one nsdf_render per view, in both scenes
+    and both math modes, with matcap shading, with staged stores, and with the ring queue and the consumer SMs forced into
+    heavy use (rays leave after 24 steps; every 4th SM consumes from the start)."""
+    torch, host, oracle = env["torch"], env["host"], env["oracle"]
+    nn, om = _load(env, "plane_1")
+    matcap = host.Image()
+    assert matcap.loadPNG(os.path.join(MATCAPS, "blue.png"))
+    matcap_np = oracle.load_matcap_png(os.path.join(MATCAPS, "blue.png"))
+    W, H = 512, 384
+    views = [(0.0, 0.0), (10.0, 45.0), (-20.0, 200.0), (0.0, 300.0), (5.0, 123.0)]
+    frames_no = [0, 3, 40, 0, 7]
+    keep = [0, 1, 2, 4, 5]
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    for scene, math in ((host.SCENE_MANYSPHERE, host.MATH_REFERENCE), (host.SCENE_TANH, host.MATH_DETERMINISTIC),
+                        (host.SCENE_MANYSPHERE, host.MATH_DETERMINISTIC)):
+        host.setSceneOptions(scene, 6000, 0, 0, math)
+        ref = torch.zeros(len(views) * W * H, dtype=torch.int32, device="cuda")
+        st1 = torch.zeros(6, dtype=torch.int64, device="cuda")
+        for v, (rx, ry) in enumerate(views):
+            host.updateViewMatrices((rx, ry, 0.0), (0.0, 0.0, -2.0), frames_no[v])
+            host.render_kernel(ref[v * W * H:(v + 1) * W * H], W, H, nn, matcap, stats=st1)
+        cams = host.view_cameras(views, frames_no)
+        for knobs in (dict(bulk4=0), dict(bulk4=1), dict(bulk4=1, bulk4_evict_steps=24, bulk4_period=4, bulk4_drain=64),
+                      dict(bulk4=1, bulk4_unroll=4, bulk4_refill_min=1), dict(bulk4=1, bulk4_unroll=1, bulk4_drain=128)):
+            host.setTuning(**knobs)
+            out = torch.full_like(ref, 0x55)
+            st2 = torch.zeros(6, dtype=torch.int64, device="cuda")
+            host.render_views(out, W, H, nn, cams, matcap, stats=st2)
+            host.setTuning()
+            assert torch.equal(out, ref), (scene, math, knobs)
+            assert torch.equal(st1[keep], st2[keep]), (scene, math, knobs)
+            if knobs.get("bulk4_evict_steps") and not host.dev_schedules_available():
+                assert int(st2[3]) > 1000      # the ring queue really carried rays
+        # default tuning picks the throughput tracer for this call; staged stores on top
+        host.setSceneOptions(scene, 6000, host.capi.RENDER_STAGED_STORES, 0, math)
+        out = torch.full_like(ref, 0x55)
+        host.render_views(out, W, H, nn, cams, matcap)
+        assert torch.equal(out, ref), (scene, math, "staged")
+        if math == host.MATH_DETERMINISTIC:     # one view of the batch against the oracle
+            iv, nm = oracle.view_matrices(10.0, 45.0)
+            o = oracle.render(om, iv, nm, W, H, matcap=matcap_np, frame=3,
+                              scene=oracle.SCENE_TANH if scene == host.SCENE_TANH else oracle.SCENE_MANYSPHERE)
+            assert np.array_equal(out[W * H:2 * W * H].cpu().numpy().view(np.uint32).reshape(H, W), o["image"])
+    host.setSceneOptions()
+    host.copyStaticSettings(host.COLOR_FACING, 3)
+
+
 def test_error_behaviour(env):
     torch, host = env["torch"], env["host"]
     from cudaneuralrender_b200 import _capi

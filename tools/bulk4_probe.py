@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Development probe: the 64-view 1080p turntable of bench.py through nsdf_render_views, default tuning against variants
-(bytes equal? ms per frame?).  usage: bulk4_probe.py [N_VIEWS] "k=v,k=v" "k=v" ..."""
+(bytes equal? ms per frame?).  usage: bulk4_probe.py [WxH] [N_VIEWS] "k=v,k=v" "k=v" ..."""
 import os, sys
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -8,6 +8,8 @@ sys.path.insert(0, ROOT)
 from cudaneuralrender_b200 import host
 W, H = 1920, 1080
 args = sys.argv[1:]
+if args and "x" in args[0] and "=" not in args[0]:
+    W, H = (int(v) for v in args.pop(0).split("x"))
 N = int(args.pop(0)) if args and args[0].isdigit() else 64
 variants = [dict((kv.split("=")[0], int(kv.split("=")[1])) for kv in a.split(",") if kv) for a in args]
 nn = host.NeuralNetwork(); assert nn.load(os.path.join(ROOT, "data", "neuralGeometries", "plane_1.h5"))
