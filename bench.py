@@ -578,9 +578,9 @@ def run_native(args):
                                           "queries_equal": bool(det["queries"] == r["queries"]), "queries": det["queries"],
                                           "note": "the timed frame's view 0 in NSDF_MATH_DETERMINISTIC against the CPU oracle's frame, all pixels"}
 
-    # which of the library's kernels a step launches (csrc/nsdf_render.cu resolve_tuning): calls of >= 4 views run on the
+    # which of the library's kernels a step launches (csrc/nsdf_render.cu resolve_tuning): calls of >= 4 views and >= 12 M pixels run on the
     # four-rays-per-lane throughput tracer, smaller ones on the cooperative tracer; calls of < 12 views probe and sort the tiles first
-    top_kernel = "trace_bulk4_kernel" if len(my_views) >= 4 else "trace_coop_kernel"
+    top_kernel = "trace_bulk4_kernel" if len(my_views) >= 4 and len(my_views) * W * H >= 12000000 else "trace_coop_kernel"
     launches_per_step = 1 if len(my_views) >= 12 else 3
     traffic, traffic_note = None, "no capture of the current tracer sources under profiles/ncu_traffic.json"
     try:

@@ -542,7 +542,10 @@ static void resolve_tuning(const nsdf_render_opts* opts, unsigned int total_idx,
     if (T->express_warps > COOP_THREADS / 32) T->express_warps = COOP_THREADS / 32;
     // ... and their bulk runs best on the four-rays-per-lane evaluator (trace_bulk4.cuh; measured per 1080p frame, cooperative
     // tracer -> bulk4: 4 views 14.03 -> 13.58 ms, 8: 13.48 -> 12.29, 16: 11.90 -> 10.77, 64: 9.47 -> 8.55; one view 17.8 -> 24.3)
-    if (T->bulk4 < 0) T->bulk4 = n_views >= 4 ? 1 : 0;
+    // Small calls stay on the cooperative tracer: a bulk4 warp steps its 128 slots in ~40 us whatever their occupancy, so the tail
+    // of a call must hide behind enough bulk (64 views of 512^2 = 16.8 M pixels: 1.377 -> 1.323 ms per frame; 16 views = 4.2 M and
+    // 8 views = 2.1 M pixels per call: 0.86 x and 0.39 x the cooperative tracer's rate, profiles/r02_scaling_summary.txt)
+    if (T->bulk4 < 0) T->bulk4 = (n_views >= 4 && total_idx >= 12000000u) ? 1 : 0;
     if (T->bulk4_evict_steps <= 0) T->bulk4_evict_steps = 1 << 30;
     if (T->bulk4_period == 1) T->bulk4_period = 2;     // somebody has to take pixels
     if (T->bulk4_drain < 0) T->bulk4_drain = 0;

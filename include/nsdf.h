@@ -219,7 +219,7 @@ typedef struct nsdf_tuning {
     int tail_lanes;          /* once the pixels are gone, warps 0..tail_lanes-1 of every SM are lanes too (0 = off)             */
     int tail_push_max;       /* ... fed by warps that are down to this many marching rays (2)                                   */
     int bulk4;               /* calls of several views on the four-rays-per-lane throughput tracer (csrc/trace_bulk4.cuh):
-                                1 = on, 0 = off, -1 = automatic (calls of >= 4 views)                                            */
+                                1 = on, 0 = off, -1 = automatic (calls of >= 4 views and >= 12 M pixels)                                            */
     int bulk4_evict_steps;   /* ... a ray still marching after this many steps moves to the consumer warps (0 = never: measured
                                 best; consumers then only finish what thinned-out warps hand over at the end of the call)       */
     int bulk4_period;        /* ... every bulk4_period-th SM consumes from the start (0 = none)                                 */

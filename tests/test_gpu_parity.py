@@ -749,7 +749,7 @@ def test_batched_views_and_staged_stores(env):
 
 
 def test_throughput_tracer_for_many_views(env):
-    """Calls of >= 4 views of enough pixels run on trace_bulk4_kernel (four rays per lane, ring queue to cooperative consumers):
+    """Calls of >= 4 views and >= 12 M pixels run on trace_bulk4_kernel (four rays per lane, ring queue to cooperative consumers):
     frames and query counts equal the cooperative tracer's (nsdf_tuning.bulk4 = 0) and one nsdf_render per view, in both scenes
     and both math modes, with matcap shading, with staged stores, and with the ring queue and the consumer SMs forced into
     heavy use (rays leave after 24 steps; every 4th SM consumes from the start)."""
@@ -783,10 +783,12 @@ def test_throughput_tracer_for_many_views(env):
             assert torch.equal(st1[keep], st2[keep]), (scene, math, knobs)
             if knobs.get("bulk4_evict_steps") and not host.dev_schedules_available():
                 assert int(st2[3]) > 1000      # the ring queue really carried rays
-        # default tuning picks the throughput tracer for this call; staged stores on top
+        # staged stores on top of the throughput tracer (forced: the automatic choice wants >= 12 M pixels per call)
         host.setSceneOptions(scene, 6000, host.capi.RENDER_STAGED_STORES, 0, math)
+        host.setTuning(bulk4=1)
         out = torch.full_like(ref, 0x55)
         host.render_views(out, W, H, nn, cams, matcap)
+        host.setTuning()
         assert torch.equal(out, ref), (scene, math, "staged")
         if math == host.MATH_DETERMINISTIC:     # one view of the batch against the oracle
             iv, nm = oracle.view_matrices(10.0, 45.0)
