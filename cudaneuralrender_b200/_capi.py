@@ -102,6 +102,7 @@ PROTOTYPES = {
     "nsdf_scene_eval": (_i, [C.POINTER(SceneOp), _i, _vp, _vp, _i, _i, _vp, _i64, _vp]),
     "nsdf_camera_from_view": (None, [_f, _f, _f, _f, _f, _i, C.POINTER(Camera)]),
     "nsdf_render": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
+    "nsdf_render_noalloc": (_i, [_vp, C.POINTER(Camera), _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
     "nsdf_render_views": (_i, [_vp, C.POINTER(Camera), _i, _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i, _vp, _vp]),
     "nsdf_render_views_host": (_i, [_vp, C.POINTER(Camera), _i, _vp, _i, _i, C.POINTER(RenderOpts), _vp, _i, _i,
                                     C.POINTER(RenderStats)]),

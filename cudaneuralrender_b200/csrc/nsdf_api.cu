@@ -165,6 +165,7 @@ const char* nsdf_error_string(int status) {
         case NSDF_EUNSUPPORTED: return "nsdf: model shape not supported by the requested kernel";
         case NSDF_EIO: return "nsdf: file could not be read or parsed";
         case NSDF_ENOMEM: return "nsdf: out of host memory";
+        case NSDF_ETOOLARGE: return "nsdf: size beyond the fixed maximum of an allocation-free entry point (NSDF_NOALLOC_MAX_TILES)";
         default: return cudaGetErrorString((cudaError_t)status);
     }
 }
@@ -491,6 +492,15 @@ int nsdf_render_views(const nsdf_model* m, const nsdf_camera* cams, int n_views,
 int nsdf_render(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
                 const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream) {
     return nsdf_render_views(m, cam, 1, d_matcap, mw, mh, opts, d_out, W, H, d_stats, stream);
+}
+
+int nsdf_render_noalloc(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                        const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream) {
+    if (!m || !cam || !d_out || W <= 0 || H <= 0) return NSDF_EINVAL;
+    nsdf_render_opts o;
+    if (opts) o = *opts;
+    else nsdf_render_opts_default(&o);
+    return nsdf::render_noalloc_launch(m, cam, d_matcap, mw, mh, &o, d_out, W, H, d_stats, (cudaStream_t)stream);
 }
 
 int nsdf_render_views_host(const nsdf_model* cm, const nsdf_camera* cams, int n_views, const uint32_t* h_matcap, int mw, int mh,

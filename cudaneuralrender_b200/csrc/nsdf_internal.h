@@ -69,6 +69,10 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
                   const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
                   cudaStream_t stream);
 void render_release(nsdf_model* m);
+// allocation-free single-view render on the file-scope scratch array of nsdf_render.cu (nsdf_render_noalloc)
+int render_noalloc_launch(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                          const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                          cudaStream_t stream);
 
 // tensor-core path (mlp_tc.cu)
 int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int precision, bool lattice, int res, float lo,

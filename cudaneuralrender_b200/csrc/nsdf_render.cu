@@ -780,6 +780,126 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
 }
 #endif  // NSDF_DEV_SCHEDULES
 
+// =====================================================================================
+// Allocation-free variant (nsdf_render_noalloc).  No counterpart in the reference: added
+// for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+// The cooperative tracer's scratch -- its job counters and the tile-priority scores / order -- lives in ONE file-scope device
+// array of fixed size instead of the model handle's cudaMalloc'ed buffers, which bounds the frame at NSDF_NOALLOC_MAX_TILES
+// 64x64 tiles (3840x2160 fits).  No express lanes (their queue is 6 MB per view): the frame's bytes are the same -- the schedule
+// never changes them -- but the serial tail of a frame is not shortened.  Every call on a device shares the array: the counters
+// and scores are cleared on the stream at the start of each call; two calls that overlap on the GPU race.
+// =====================================================================================
+constexpr int NOALLOC_COUNTER_WORDS = 64;         // 8 used; the tile arrays start 256 bytes in
+static __device__ __align__(256) unsigned int g_noalloc_scratch[NOALLOC_COUNTER_WORDS + 2 * NSDF_NOALLOC_MAX_TILES];
+
+struct NoallocDevice {        // per device: set up on the first call with that device current
+    unsigned int* scratch = nullptr;     // DEVICE address of g_noalloc_scratch (cudaGetSymbolAddress; the symbol itself is a host-side stand-in)
+    int sms = 0;
+    int occ = 0;
+};
+static NoallocDevice g_noalloc_dev[64];
+
+int render_noalloc_launch(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                          const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                          cudaStream_t stream) {
+    if (!m->fused || (m->in[0] != 3 && m->in[0] != 4)) return NSDF_EUNSUPPORTED;
+    if (opts->flags != 0 || opts->evict_steps != 0 || opts->tile_world != 1 || opts->tile_rank != 0) return NSDF_EUNSUPPORTED;
+    if (opts->color_type == NSDF_COLOR_MATCAP && (!d_matcap || mw <= 0 || mh <= 0)) return NSDF_EINVAL;
+    if (opts->math != NSDF_MATH_REFERENCE && opts->math != NSDF_MATH_DETERMINISTIC) return NSDF_EINVAL;
+    const long long tiles_x = ((long long)W + TILE - 1) / TILE, tiles_y = ((long long)H + TILE - 1) / TILE;
+    if (tiles_x * tiles_y > NSDF_NOALLOC_MAX_TILES) return NSDF_ETOOLARGE;
+
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return (int)e;
+    if (dev < 0 || dev >= 64) return NSDF_EUNSUPPORTED;
+    NoallocDevice& D = g_noalloc_dev[dev];
+    if (!D.scratch) {
+        unsigned int* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return NSDF_EUNSUPPORTED;
+        e = cudaFuncSetAttribute(trace_coop_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaFuncSetAttribute(tile_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        int sms = 0, occ = 0;
+        e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (e != cudaSuccess) return (int)e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, trace_coop_kernel, COOP_THREADS, coop_smem(m));
+        if (e != cudaSuccess) return (int)e;
+        if (sms < 1 || occ < 1) return NSDF_EUNSUPPORTED;
+        D.sms = sms;
+        D.occ = occ;
+        D.scratch = ptr;
+    }
+
+    RenderParams rp;
+    std::memset(&rp, 0, sizeof(rp));
+    std::memcpy(rp.cam.inv_view, cam->inv_view, sizeof(rp.cam.inv_view));
+    std::memcpy(rp.cam.normal, cam->normal, sizeof(rp.cam.normal));
+    rp.cam.frame = cam->frame;
+    rp.cam.zoff = many_sphere_zoff(cam->frame);
+    rp.n_views = 1;
+    rp.view_pixels = (unsigned int)((long long)W * H);
+    rp.blob = m->d_blob;
+    rp.n_sq = m->n_sq;
+    rp.blob_bytes = m->blob_bytes;
+    rp.matcap = d_matcap;
+    rp.mw = mw;
+    rp.mh = mh;
+    rp.color_type = opts->color_type;
+    rp.scene = opts->scene;
+    if (opts->scene == NSDF_SCENE_PROGRAM) {
+        const int rc_prog = scene_program_pack(opts->program, opts->n_ops, &rp.prog);
+        if (rc_prog) return rc_prog;
+    } else if (opts->scene != NSDF_SCENE_TANH && opts->scene != NSDF_SCENE_MANYSPHERE) {
+        return NSDF_EINVAL;
+    }
+    rp.out = d_out;
+    rp.W = W;
+    rp.H = H;
+    rp.tiles_x = (int)tiles_x;
+    rp.n_tiles = (int)(tiles_x * tiles_y);
+    rp.tile_rank = 0;
+    rp.tile_world = 1;
+    rp.my_tiles = rp.n_tiles;
+    rp.total_idx = (unsigned int)rp.n_tiles * TILE_PIXELS;
+    rp.max_steps = opts->max_steps;
+    rp.n_in = m->in[0];
+    rp.t4 = (float)cam->frame;
+    rp.refmath = opts->math == NSDF_MATH_REFERENCE ? 1 : 0;
+    rp.stats = d_stats;
+    rp.evict_steps = 1 << 30;
+    rp.evict_steps_hi = 1 << 30;
+    rp.frame_seq = 1u;
+    rp.pixel_counter = D.scratch;
+    int* const d_score = reinterpret_cast<int*>(D.scratch + NOALLOC_COUNTER_WORDS);
+    int* const d_order = d_score + NSDF_NOALLOC_MAX_TILES;
+
+    nsdf_tuning T;
+    nsdf_tuning_default(&T);
+    if (opts->tuning) T = *opts->tuning;
+    if (T.tile_priority_steps < 0) T.tile_priority_steps = 32;
+    const int n_jobs = rp.n_tiles;
+    const bool priority = T.tile_priority_steps > 0 && n_jobs >= T.tile_priority_min_jobs;
+    // the array keeps the last call's contents: counters, and the scores the probe adds to, start at zero
+    e = cudaMemsetAsync(D.scratch, 0, (size_t)(NOALLOC_COUNTER_WORDS + (priority ? n_jobs : 0)) * sizeof(unsigned int), stream);
+    if (e != cudaSuccess) return (int)e;
+    if (priority) {
+        const unsigned int probes = (unsigned int)n_jobs * PROBES_PER_TILE;
+        tile_probe_kernel<<<(probes + 127u) / 128u, 128, m->blob_bytes, stream>>>(rp, n_jobs, T.tile_priority_steps, d_score);
+        tile_sort_kernel<<<1, 256, 0, stream>>>(d_score, n_jobs, d_order);
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return (int)e;
+        rp.tile_order = d_order;
+    }
+    const unsigned int per_cta = (COOP_THREADS / 32) * COOP_R;
+    const unsigned int cap = (unsigned int)(D.sms * D.occ);
+    const unsigned int want = (rp.total_idx + per_cta - 1) / per_cta;
+    return (int)launch_coop(rp, want < cap ? want : cap, coop_smem(m), stream);
+}
+
 }  // namespace nsdf
 
 extern "C" int nsdf_build_has_dev_schedules(void) {

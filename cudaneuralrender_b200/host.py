@@ -478,6 +478,20 @@ def render_kernel(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNe
                "nsdf_render")
 
 
+def render_kernel_noalloc(d_output: torch.Tensor, imageW: int, imageH: int, nn: NeuralNetwork, matcap: Optional[Image] = None,
+                          stats: Optional[torch.Tensor] = None):
+    """nsdf_render_noalloc: render_kernel for callers that must not allocate device memory during the call (no counterpart in
+    the reference; the tracer's scratch is a fixed device array inside the library, frames of at most 2048 64x64 tiles).
+    Same frame bytes as render_kernel; calls that overlap on the GPU race on the shared scratch."""
+    opts = _opts(0, 1)
+    mat_ptr, mw, mh = None, 0, 0
+    if matcap is not None and matcap.deviceData is not None:
+        mat_ptr, mw, mh = matcap.deviceData.data_ptr(), matcap.shape.x, matcap.shape.y
+    capi.check(capi.lib().nsdf_render_noalloc(nn.handle(), C.byref(_state.cam), mat_ptr, mw, mh, C.byref(opts), d_output.data_ptr(),
+                                              imageW, imageH, stats.data_ptr() if stats is not None else None, _stream_ptr()),
+               "nsdf_render_noalloc")
+
+
 def view_cameras(views, frames=None):
     """[(rx_deg, ry_deg) ...] (+ optional frame numbers) -> (Camera * n) array: updateViewMatrices (src/main.cpp:207-222) per view,
     default viewTranslation (0, 0, -2)."""

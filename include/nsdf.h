@@ -35,6 +35,7 @@ extern "C" {
 #define NSDF_EUNSUPPORTED 10002 /* model shape not handled by the requested kernel        */
 #define NSDF_EIO 10003          /* file could not be read / parsed                        */
 #define NSDF_ENOMEM 10004
+#define NSDF_ETOOLARGE 10005   /* size beyond the fixed maximum of an allocation-free entry point */
 
 /* Activation ids: the reference's `enum Activation { ReLU, Tanh }` (src/layers/denseLayer.hh:6-9).
  * "Tanh" selects the LINEAR epilogue in the reference (src/layers/denseLayer.cu:93-113,150-166);
@@ -307,6 +308,20 @@ int nsdf_render(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_m
  * nsdf_render.  Only the default schedule (opts->flags without the A/B bits). */
 int nsdf_render_views(const nsdf_model* m, const nsdf_camera* cams, int n_views, const uint32_t* d_matcap, int mw, int mh,
                       const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats, void* stream);
+/* nsdf_render for callers that cannot allocate device memory.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same arguments and
+ * the same frame, byte for byte, as nsdf_render; the call performs no cudaMalloc / cudaFree and calls no allocating library
+ * routine: the tracer's scratch (job counters, tile-priority scores and order, 16.6 KB) is a file-scope device array that
+ * every GPU which loads the library holds until exit.  Limits: the frame has at most NSDF_NOALLOC_MAX_TILES 64x64 tiles
+ * (3840x2160 fits; beyond that NSDF_ETOOLARGE); (3|4) -> 32 x k -> 1 models, whole frames (tile_world 1), opts->flags 0; no
+ * express lanes, so a single frame's serial tail is not shortened (the bytes do not depend on that).  Every call on a device
+ * shares the array: it is cleared on `stream` at the start of each call, so calls on one stream may follow each other
+ * freely, but two calls that OVERLAP on the GPU (different streams, or a different process using the same device through
+ * this library instance) race.  The model handle m, d_matcap, d_out and d_stats are the caller's, as for nsdf_render. */
+#define NSDF_NOALLOC_MAX_TILES 2048
+int nsdf_render_noalloc(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* d_matcap, int mw, int mh,
+                        const nsdf_render_opts* opts, uint32_t* d_out, int W, int H, nsdf_render_stats* d_stats,
+                        void* stream);
 /* Host-buffer variant: uploads the matcap, renders, copies the frame back; synchronous.
  * h_stats may be NULL. */
 int nsdf_render_host(const nsdf_model* m, const nsdf_camera* cam, const uint32_t* h_matcap, int mw, int mh,
