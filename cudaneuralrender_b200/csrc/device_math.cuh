@@ -119,19 +119,26 @@ __host__ __device__ inline double many_sphere_zoff(int frame) {
     volatile double q = num / 360.0;
     return -0.7 + q;
 }
+// The reference walks the 3 x 3 grid with a running cx / cy (:183-195): cx restarts at p.x + 0.5f in every row and loses 0.4 (a
+// double literal: the subtraction is done in double and rounded back to float) per sphere, cy gains 0.4 per row.  The nine centres
+// therefore have only three distinct x and three distinct y offsets, each the same chain of roundings whatever the row: computed
+// once here (a dependent chain of 2 + 4 conversions instead of 13), same bits.
 __device__ __forceinline__ void many_sphere_len2(f3 p, double zoff, float (&len2)[9]) {
-    float cx = p.x;
-    float cy = (float)__dsub_rn((double)p.y, 0.6);
+    float xs[3], ys[3];
+    xs[0] = p.x + 0.5f;
+    xs[1] = (float)__dsub_rn((double)xs[0], 0.4);
+    xs[2] = (float)__dsub_rn((double)xs[1], 0.4);
+    const float y_init = (float)__dsub_rn((double)p.y, 0.6);
+    ys[0] = (float)__dadd_rn((double)y_init, 0.4);
+    ys[1] = (float)__dadd_rn((double)ys[0], 0.4);
+    ys[2] = (float)__dadd_rn((double)ys[1], 0.4);
     const float cz = (float)__dadd_rn((double)p.z, zoff);
     const float zz = cz * cz;
 #pragma unroll
-    for (int i = 0; i < 9; ++i) {
-        if (i % 3 == 0) {
-            cy = (float)__dadd_rn((double)cy, 0.4);
-            cx = p.x + 0.5f;
-        }
-        len2[i] = zz + fmaf(cx, cx, cy * cy);
-        cx = (float)__dsub_rn((double)cx, 0.4);
+    for (int r = 0; r < 3; ++r) {
+        const float yy = ys[r] * ys[r];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) len2[3 * r + c] = zz + fmaf(xs[c], xs[c], yy);
     }
 }
 // The chain itself for a point that IS near a sphere (rays grazing a sphere stay in this case for thousands of steps, so it
