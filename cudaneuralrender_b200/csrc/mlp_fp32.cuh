@@ -203,7 +203,7 @@ template <> struct ActVec<4> {
     static __device__ __forceinline__ void get(const float4& v, float (&a)[4]) { a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w; }
 };
 // act: this thread's column (element k at act[k * stride]); P = 2 or 4 points per thread.
-template <int P, int KU = 4, bool PEEL = true>
+template <int P, int KU = 4, int PEEL = 1>
 __device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw, int n_sq,
                                                     typename ActVec<P>::type* __restrict__ act, int stride,
                                                     const float (&x)[P][3], float (&y)[P], float t4 = 0.0f,
@@ -235,12 +235,12 @@ __device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw
         const float4* Wt = reinterpret_cast<const float4*>(sw + FUSED_L0_FLOATS + l * FUSED_SQ_FLOATS);
         // PEEL: k = 0 apart -- its activation is still in registers, and fma(w, a, +0) starts every chain without 32 x P clears
         // (dense 256^3 sweep 3.44 -> 3.63 Gq/s); callers that need the smallest instruction footprint keep the plain loop
-        if (PEEL) {
-            float a0[P];
+        if (PEEL > 0) {      // PEEL = 2 takes k = 1 from registers as well (an even trip count is left for a k-unroll of 2)
+            float a0[P], a1[P];
 #pragma unroll
-            for (int p = 0; p < P; ++p) a0[p] = z[0][p];
+            for (int p = 0; p < P; ++p) { a0[p] = z[0][p]; a1[p] = z[1][p]; }
 #pragma unroll
-            for (int o = 1; o < 32; ++o) act[o * stride] = ActVec<P>::make(z[o]);
+            for (int o = PEEL; o < 32; ++o) act[o * stride] = ActVec<P>::make(z[o]);
 #pragma unroll
             for (int oc = 0; oc < 8; ++oc) {
                 const float4 w = Wt[oc];
@@ -252,6 +252,19 @@ __device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw
                     z[4 * oc + 3][p] = fmaf(w.w, a0[p], 0.0f);
                 }
             }
+            if (PEEL > 1) {
+#pragma unroll
+                for (int oc = 0; oc < 8; ++oc) {
+                    const float4 w = Wt[8 + oc];
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        z[4 * oc + 0][p] = fmaf(w.x, a1[p], z[4 * oc + 0][p]);
+                        z[4 * oc + 1][p] = fmaf(w.y, a1[p], z[4 * oc + 1][p]);
+                        z[4 * oc + 2][p] = fmaf(w.z, a1[p], z[4 * oc + 2][p]);
+                        z[4 * oc + 3][p] = fmaf(w.w, a1[p], z[4 * oc + 3][p]);
+                    }
+                }
+            }
         } else {
 #pragma unroll
             for (int o = 0; o < 32; ++o) {
@@ -261,7 +274,7 @@ __device__ __forceinline__ void mlp32_eval_thread_s(const float* __restrict__ sw
             }
         }
 #pragma unroll KU
-        for (int k = PEEL ? 1 : 0; k < 32; ++k) {
+        for (int k = PEEL; k < 32; ++k) {
             float av[P];
             ActVec<P>::get(act[k * stride], av);
 #pragma unroll

@@ -153,7 +153,7 @@ __device__ __forceinline__ float b4_consumer_eval(const float* s_w, float* abuf,
     return coop_eval<1>(s_w, rp.n_sq, abuf, q, src, rank, lane, rp.t4, rp.n_in == 4);
 }
 
-template <int KU>
+template <int KU, int PEEL = 0>
 __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid_constant__ RenderParams rp) {
     extern __shared__ __align__(16) float s_w[];
     __shared__ uint64_t s_bar;
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(B4_THREADS, 1) trace_bulk4_kernel(const __grid
                 x[0][1] = x1.x; x[1][1] = x1.y; x[2][1] = x1.z; x[3][1] = x1.w;
                 x[0][2] = x2.x; x[1][2] = x2.y; x[2][2] = x2.z; x[3][2] = x2.w;
             }
-            mlp32_eval_thread_s<B4_P, KU, false>(s_w, rp.n_sq, act4, 32, x, y, rp.t4, rp.n_in == 4);
+            mlp32_eval_thread_s<B4_P, KU, PEEL>(s_w, rp.n_sq, act4, 32, x, y, rp.t4, rp.n_in == 4);
             act4[0] = make_float4(y[0], y[1], y[2], y[3]);
             // ---- ray updates and the next query points; long rays, and the remnants of a warp that has nothing to refill from,
             // go to the consumers
