@@ -20,6 +20,7 @@ import argparse
 import hashlib
 import json
 import os
+import re
 import subprocess
 import sys
 import threading
@@ -55,16 +56,26 @@ def peaks():
     return {"hbm_gbs": 6650.0, "tflops_burst": 1590.0, "tflops_sustained": 1400.0, "source": "fallback"}
 
 
-def tracer_source_sha():
-    """sha of the tracer's sources: profiles/ncu_traffic.json is only quoted when it was captured from these bytes."""
-    h = hashlib.sha256()
-    d = os.path.join(ROOT, "cudaneuralrender_b200", "csrc")
-    for f in ("trace_coop.cuh", "trace_bulk4.cuh", "render_kernels.cuh", "mlp_fp32.cuh", "device_math.cuh", "nsdf_render.cu"):
-        try:
-            h.update(open(os.path.join(d, f), "rb").read())
-        except OSError:
-            pass
-    return h.hexdigest()[:16]
+def kernel_sass_sha(kernel):
+    """sha of the SASS of the library's `kernel` instantiation that the bench launches (instruction text without addresses'
+    encodings): profiles/ncu_traffic.json is only quoted when it was captured from the same machine code.  None without cuobjdump."""
+    want = {"trace_bulk4_kernel": "trace_bulk4_kernelILi2E", "trace_coop_kernel": "trace_coop_kernelE"}.get(kernel, kernel)
+    lib = os.path.join(ROOT, "cudaneuralrender_b200", "libnsdf.so")
+    try:
+        out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True, timeout=120).stdout
+    except Exception:
+        return None
+    h, inside, n = hashlib.sha256(), False, 0
+    for line in out.splitlines():
+        if "Function :" in line:
+            inside = want in line
+            continue
+        if inside:
+            m = re.match(r"\s+/\*[0-9a-f]{4}\*/\s+(.*?)\s*/\* 0x[0-9a-f]+ \*/", line)
+            if m:
+                h.update(m.group(1).encode() + b"\n")
+                n += 1
+    return h.hexdigest()[:16] if n else None
 
 
 class ClockSampler:
@@ -585,14 +596,14 @@ def run_native(args):
     traffic, traffic_note = None, "no capture of the current tracer sources under profiles/ncu_traffic.json"
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        if tj.get("tracer_source_sha") == tracer_source_sha() and top_kernel in tj:
-            k = tj[top_kernel]
+        k = tj.get(top_kernel)
+        if k and k.get("sass_sha") and k.get("sass_sha") == kernel_sass_sha(top_kernel):
             per_frame = (k["dram_bytes_read"] + k["dram_bytes_write"]) / k.get("frames_in_launch", 1)
             traffic = per_frame * len(my_views)          # one launch per step and rank = len(my_views) frames
             traffic_note = (f"dram bytes per launch ({len(my_views)} frames), scaled per frame from the ncu --set full capture "
-                            f"{tj.get('capture', '')} of these tracer sources")
+                            f"{tj.get('capture', '')} of this kernel's machine code (equal SASS)")
         else:
-            traffic_note = "profiles/ncu_traffic.json was captured from other tracer sources than the ones running: not quoted"
+            traffic_note = "profiles/ncu_traffic.json was captured from other machine code of this kernel than the library that is running holds: not quoted"
     except Exception:
         pass
     q_frame = q_set / N_VIEWS
