@@ -1,5 +1,5 @@
 // =====================================================================================
-// trace_bulk4.cuh -- the THROUGHPUT tracer for calls of many views (nsdf_render_views, n_views >= 12).
+// trace_bulk4.cuh -- the THROUGHPUT tracer for calls of many views (nsdf_render_views: >= 4 views and >= 12 M pixels).
 //
 // Replaces, like trace_coop.cuh, the host loop of render_kernel (src/volumeRender_kernel.cu:608-692) and its
 // per-iteration scan + createBatch (:504-563).  A call of many views is a pure throughput problem: the serial tails of

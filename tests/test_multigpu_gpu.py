@@ -88,6 +88,12 @@ def test_multi_renderer_over_all_gpus(gpu):
         out = torch.full_like(ref, 0x55)
         st = mr.render(out, W, H, host.view_cameras(views), matcap_np)
         assert torch.equal(out, ref) and st["pixels"] == len(views) * W * H, (W, H)
+        if W * H >= 500000:      # every device's share on the throughput tracer (trace_bulk4.cuh), forced through the tuning struct
+            host.setTuning(bulk4=1)
+            out = torch.full_like(ref, 0x55)
+            st = mr.render(out, W, H, host.view_cameras(views), matcap_np)
+            host.setTuning()
+            assert torch.equal(out, ref) and st["pixels"] == len(views) * W * H, (W, H, "bulk4")
         one = torch.full((W * H,), 0x55, dtype=torch.int32, device="cuda")
         st = mr.render(one, W, H, host.view_cameras(views[:1]), matcap_np)
         assert torch.equal(one, ref[:W * H]) and st["pixels"] == W * H, (W, H)
