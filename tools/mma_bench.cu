@@ -49,6 +49,65 @@ __global__ void __launch_bounds__(128) bench(int N, int per, int iters, int lbo,
     if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 64);
 }
 
+
+// ONE CTA per SM, `chains` warps; warp w loops {`per` UMMAs into its own 32 accumulator columns, commit, wait} like a tile-layer of
+// the dense kernel without any epilogue.  Shows whether the 75 clk per tile-layer of eight chains is the chains' latency (then more
+// chains in flight lower it towards the tensor pipe's 3 x 17 clk) or a rate limit of the issue / commit path (then it stays).
+__global__ void __launch_bounds__(512) bench_chains(int per, int iters, long long* out) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t bar[16];
+    __shared__ uint32_t s_tmem;
+    for (int i = threadIdx.x; i < 8192 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u;
+    if (threadIdx.x == 0) { for (int i = 0; i < 16; ++i) mbar_init(&bar[i], 1); mbar_fence_init(); }
+    __syncthreads();
+    if (threadIdx.x < 32) tc::tmem_alloc(&s_tmem, 512);
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const uint32_t tmem = s_tmem;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncthreads();
+    const int warp = threadIdx.x >> 5;
+    const uint32_t idesc = tc::make_idesc(0, 128, 32);
+    const uint64_t d = tc::make_bdesc(smem_u32(smem), 32 * 16);
+    const uint32_t acc = tmem + 32u * (uint32_t)warp;      // chains 0..14: columns 0..479; the A operand: columns 480..511
+    uint32_t phase = 0;
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+        if (tc::elect_one()) {
+            for (int j = 0; j < per; ++j) tc::mma_ts(acc, tmem + 480 + 8 * (j & 1), d, idesc, j ? 1u : 0u);
+            tc::mma_commit(&bar[warp]);
+        }
+        __syncwarp();
+        tc::mbar_wait_guard(&bar[warp], phase);
+        phase ^= 1;
+    }
+    const long long t1 = clock64();
+    if ((threadIdx.x & 31) == 0) atomicMax((unsigned long long*)&out[blockIdx.x], (unsigned long long)(t1 - t0));
+    __syncthreads();
+    if (threadIdx.x < 32) tc::tmem_dealloc(tmem, 512);
+}
+
+static void run_chains(long long* d_out) {
+    cudaFuncSetAttribute(bench_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    for (int per : {3, 2}) {
+        for (int chains : {1, 2, 4, 8, 10, 12, 15}) {
+            const int iters = 512;
+            cudaMemset(d_out, 0, 148 * 8);
+            bench_chains<<<148, chains * 32, 24 * 1024>>>(per, iters, d_out);
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) { printf("chains: error %s\n", cudaGetErrorString(e)); return; }
+            long long h[148];
+            cudaMemcpy(h, d_out, sizeof(h), cudaMemcpyDeviceToHost);
+            double avg = 0;
+            for (int i = 0; i < 148; ++i) avg += h[i];
+            avg /= 148;
+            printf("chains/SM %2d, %d UMMAs (M128 N32 K16) + commit + wait per chain step: %.1f clk per chain step, %.1f clk per tile-layer SM-wide\n",
+                   chains, per, avg / iters, avg / iters / chains);
+        }
+    }
+}
+
 int main() {
     long long* d_out;
     cudaMalloc(&d_out, 148 * 8 * 8);
@@ -73,5 +132,6 @@ int main() {
                        avg / iters, avg / iters / per, avg / iters / per / ctas);
             }
         }
+    run_chains(d_out);
     return 0;
 }
