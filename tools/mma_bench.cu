@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(128) bench(int N, int per, int iters, int lbo,
 // ONE CTA per SM, `chains` warps; warp w loops {`per` UMMAs into its own 32 accumulator columns, commit, wait} like a tile-layer of
 // the dense kernel without any epilogue.  Shows whether the 75 clk per tile-layer of eight chains is the chains' latency (then more
 // chains in flight lower it towards the tensor pipe's 3 x 17 clk) or a rate limit of the issue / commit path (then it stays).
-__global__ void __launch_bounds__(512) bench_chains(int per, int iters, long long* out) {
+__global__ void __launch_bounds__(512) bench_chains(int per, int iters, long long* out, int poll) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ uint64_t bar[16];
     __shared__ uint32_t s_tmem;
@@ -79,7 +79,7 @@ __global__ void __launch_bounds__(512) bench_chains(int per, int iters, long lon
             tc::mma_commit(&bar[warp]);
         }
         __syncwarp();
-        tc::mbar_wait_guard(&bar[warp], phase);
+        if (poll) wait_poll(&bar[warp], phase); else tc::mbar_wait_guard(&bar[warp], phase);
         phase ^= 1;
     }
     const long long t1 = clock64();
@@ -90,11 +90,12 @@ __global__ void __launch_bounds__(512) bench_chains(int per, int iters, long lon
 
 static void run_chains(long long* d_out) {
     cudaFuncSetAttribute(bench_chains, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    for (int poll = 0; poll < 2; ++poll)
     for (int per : {3, 2}) {
-        for (int chains : {1, 2, 4, 8, 10, 12, 15}) {
+        for (int chains : {1, 2, 4, 5, 6, 7, 8, 9, 10, 12, 15}) {
             const int iters = 512;
             cudaMemset(d_out, 0, 148 * 8);
-            bench_chains<<<148, chains * 32, 24 * 1024>>>(per, iters, d_out);
+            bench_chains<<<148, chains * 32, 24 * 1024>>>(per, iters, d_out, poll);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("chains: error %s\n", cudaGetErrorString(e)); return; }
             long long h[148];
@@ -102,8 +103,8 @@ static void run_chains(long long* d_out) {
             double avg = 0;
             for (int i = 0; i < 148; ++i) avg += h[i];
             avg /= 148;
-            printf("chains/SM %2d, %d UMMAs (M128 N32 K16) + commit + wait per chain step: %.1f clk per chain step, %.1f clk per tile-layer SM-wide\n",
-                   chains, per, avg / iters, avg / iters / chains);
+            printf("%s chains/SM %2d, %d UMMAs (M128 N32 K16) + commit + wait per chain step: %.1f clk per chain step, %.1f clk per tile-layer SM-wide\n",
+                   poll ? "test_wait spin" : "try_wait      ", chains, per, avg / iters, avg / iters / chains);
         }
     }
 }
