@@ -21,6 +21,7 @@
 #include "tc_mlp.cuh"
 #include "tc_mlp3.cuh"
 #include "tc_mlp4.cuh"
+#include "tc_mlp5.cuh"
 
 namespace nsdf {
 

@@ -230,6 +230,48 @@ int launch4(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y
     return (int)cudaGetLastError();
 }
 
+template <int MODE, int G, int CPS>
+int launch5(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp, cudaStream_t stream) {
+    tc::Tc4Params p;
+    p.image = t->d[MODE];
+    p.image_bytes = t->bytes[MODE];
+    p.blob = m->d_blob;
+    p.n_sq = m->n_sq;
+    p.x = d_x;
+    p.y = d_y;
+    p.n = n;
+    p.lp = lp;
+    size_t smem = p.image_bytes;
+    const size_t min_smem = (size_t)(227 * 1024) / (size_t)(CPS + 1) + 1;   // never more than CPS CTAs (and their TMEM) per SM
+    if (smem < min_smem) smem = min_smem;
+    if (smem > 200 * 1024) return NSDF_EUNSUPPORTED;
+    NSDF_PER_DEVICE_FLAG(attr_done);
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc5_kernel<MODE, G, CPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    const long long n_tiles = (n + 127) / 128;
+    const long long want = (n_tiles + G - 1) / G;
+    const long long cap = (long long)sms * CPS;
+    const int grid = (int)(want < cap ? want : cap);
+    tc::mlp_tc5_kernel<MODE, G, CPS><<<grid, G * 128, smem, stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <int MODE>
+int launch5_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
+                cudaStream_t stream) {
+    switch (cfg) {
+        case 0: return launch5<MODE, 5, 2>(m, t, d_x, d_y, n, lp, stream);   // ten tiles in flight per SM
+        case 1: return launch5<MODE, 4, 2>(m, t, d_x, d_y, n, lp, stream);   // eight
+        case 2: return launch5<MODE, 2, 4>(m, t, d_x, d_y, n, lp, stream);   // eight, in four CTAs
+        case 3: return launch5<MODE, 1, 8>(m, t, d_x, d_y, n, lp, stream);   // eight, one per CTA
+        default: return NSDF_EINVAL;
+    }
+}
+
 template <int MODE>
 int launch4_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
                 cudaStream_t stream) {
@@ -264,9 +306,10 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
     const TcDeviceImages* t = static_cast<const TcDeviceImages*>(m->d_tc);
     LatticeParams lp{lattice ? 1 : 0, res, lo, hi, (long long)first};
     if (precision == NSDF_PREC_TC_FP16_ACC16) return launch<MODE_FP16, 1, true>(m, t, d_x, d_y, n, lp, stream);
-    // Defaults from the measurements in profiles/r01_tc_schedule_notes.md: the fp16/bf16 rungs sit on the TMEM-read
-    // ceiling with the v2 schedule; the fp16x3 rung (6 UMMAs per layer) is fastest on v4 with 7 groups in one CTA per SM.
-    const int kernel = env_int("NSDF_TC_KERNEL", precision == NSDF_PREC_TC_FP16X3 ? 4 : 2);
+    // Defaults from the measurements (profiles/r01_tc_schedule_notes.md, r02_tc5_diag.txt): the fp16/bf16 rungs are fastest on the v5
+    // schedule with 2 tile groups x 4 CTAs per SM (41.6 Gq/s; v2 35.8, bit-equal); the fp16x3 rung (6 UMMAs per layer) on v4 with
+    // 7 groups in one CTA per SM.
+    const int kernel = env_int("NSDF_TC_KERNEL", precision == NSDF_PREC_TC_FP16X3 ? 4 : 5);
     if (kernel == 4) {
         const int cfg = env_int("NSDF_TC4_CFG", 1);
         switch (precision) {
@@ -275,6 +318,11 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
             case NSDF_PREC_TC_FP16X3: return launch4_cfg<MODE_FP16X3>(cfg, m, t, d_x, d_y, n, lp, stream);
             default: return NSDF_EINVAL;
         }
+    }
+    if (kernel == 5 && precision != NSDF_PREC_TC_FP16X3) {
+        const int cfg = env_int("NSDF_TC5_CFG", 2);
+        return precision == NSDF_PREC_TC_FP16 ? launch5_cfg<MODE_FP16>(cfg, m, t, d_x, d_y, n, lp, stream)
+                                              : launch5_cfg<MODE_BF16>(cfg, m, t, d_x, d_y, n, lp, stream);
     }
 #ifdef NSDF_DEV_SCHEDULES      // the v3 schedule measured slower than v2 in every configuration: development builds only
     if (kernel == 3) {
