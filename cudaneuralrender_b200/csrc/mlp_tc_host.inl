@@ -268,6 +268,12 @@ int launch5_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_
         case 1: return launch5<MODE, 4, 2>(m, t, d_x, d_y, n, lp, stream);   // eight
         case 2: return launch5<MODE, 2, 4>(m, t, d_x, d_y, n, lp, stream);   // eight, in four CTAs
         case 3: return launch5<MODE, 1, 8>(m, t, d_x, d_y, n, lp, stream);   // eight, one per CTA
+#ifdef NSDF_DEV_SCHEDULES      // rate against tiles in flight (profiles/r02_tc5_diag.txt)
+        case 4: return launch5<MODE, 2, 3>(m, t, d_x, d_y, n, lp, stream);
+        case 5: return launch5<MODE, 2, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 6: return launch5<MODE, 2, 1>(m, t, d_x, d_y, n, lp, stream);
+        case 7: return launch5<MODE, 1, 4>(m, t, d_x, d_y, n, lp, stream);
+#endif
         default: return NSDF_EINVAL;
     }
 }
