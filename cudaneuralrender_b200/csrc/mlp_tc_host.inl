@@ -199,7 +199,7 @@ int launch3_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_
 }
 
 // ---- v4: grouped CTAs, bias pre-loaded into the accumulator, UMMAs issued in parallel (tc_mlp4.cuh) ---------
-template <int MODE, int G, int CPS>
+template <int MODE, int G, int CPS, bool SP = false>
 int launch4(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
             cudaStream_t stream) {
     tc::Tc4Params p;
@@ -217,7 +217,7 @@ int launch4(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y
     if (smem > 200 * 1024) return NSDF_EUNSUPPORTED;
     NSDF_PER_DEVICE_FLAG(attr_done);
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc4_kernel<MODE, G, CPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc4_kernel<MODE, G, CPS, SP>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         if (e != cudaSuccess) return (int)e;
         attr_done = true;
     }
@@ -226,7 +226,7 @@ int launch4(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y
     const long long want = (n_tiles + G - 1) / G;
     const long long cap = (long long)sms * CPS;
     const int grid = (int)(want < cap ? want : cap);
-    tc::mlp_tc4_kernel<MODE, G, CPS><<<grid, G * 128, smem, stream>>>(p);
+    tc::mlp_tc4_kernel<MODE, G, CPS, SP><<<grid, G * 128, smem, stream>>>(p);
     return (int)cudaGetLastError();
 }
 
@@ -288,6 +288,9 @@ int launch4_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_
         case 2: return launch4<MODE, 4, 2>(m, t, d_x, d_y, n, lp, stream);
         case 3: return launch4<MODE, 2, 4>(m, t, d_x, d_y, n, lp, stream);
         case 4: return launch4<MODE, 3, 2>(m, t, d_x, d_y, n, lp, stream);
+        case 5: return launch4<MODE, 7, 1, true>(m, t, d_x, d_y, n, lp, stream);
+        case 6: return launch4<MODE, X3 ? 4 : 5, 2, true>(m, t, d_x, d_y, n, lp, stream);
+        case 7: return launch4<MODE, X3 ? 2 : 2, X3 ? 3 : 4, true>(m, t, d_x, d_y, n, lp, stream);
         default: return NSDF_EINVAL;
     }
 }
@@ -317,7 +320,7 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
     // 7 groups in one CTA per SM.
     const int kernel = env_int("NSDF_TC_KERNEL", precision == NSDF_PREC_TC_FP16X3 ? 4 : 5);
     if (kernel == 4) {
-        const int cfg = env_int("NSDF_TC4_CFG", 1);
+        const int cfg = env_int("NSDF_TC4_CFG", 5);   // 7 groups x 1 CTA, one polling warp per group (17.5 Gq/s; every warp polling: 17.0)
         switch (precision) {
             case NSDF_PREC_TC_FP16: return launch4_cfg<MODE_FP16>(cfg, m, t, d_x, d_y, n, lp, stream);
             case NSDF_PREC_TC_BF16: return launch4_cfg<MODE_BF16>(cfg, m, t, d_x, d_y, n, lp, stream);

@@ -118,7 +118,7 @@ __device__ __forceinline__ void epilogue4_halves(uint32_t t_slot, const float* b
     }
 }
 
-template <int MODE, int G, int CPS>
+template <int MODE, int G, int CPS, bool SINGLE_POLLER = false>
 __global__ void __launch_bounds__(G * 128, CPS) mlp_tc4_kernel(const __grid_constant__ Tc4Params p) {
     constexpr uint32_t SLOT = Cols3<MODE>::SLOT;
     constexpr uint32_t TMEM_COLS = pow2_cols(G * SLOT);
@@ -219,7 +219,12 @@ __global__ void __launch_bounds__(G * 128, CPS) mlp_tc4_kernel(const __grid_cons
                 }
                 __syncwarp();
             }
-            mbar_wait_spin(bar_d, phase);
+            if (SINGLE_POLLER) {          // one warp of the group polls, the group barrier releases the other three (tc_mlp5.cuh)
+                if (q == 0) mbar_wait_spin(bar_d, phase);
+                group_sync(g);
+            } else {
+                mbar_wait_spin(bar_d, phase);
+            }
             phase ^= 1u;
             fence_after_sync();
             if (step <= n_sq) {
