@@ -260,6 +260,51 @@ int launch5(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y
     return (int)cudaGetLastError();
 }
 
+#ifdef NSDF_DEV_SCHEDULES      // v6 (two tile slots per warpgroup) measured slower than v5: development builds only
+template <int MODE, int G, int CPS>
+int launch6(nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp, cudaStream_t stream) {
+    tc::Tc4Params p;
+    p.image = t->d[MODE];
+    p.image_bytes = t->bytes[MODE];
+    p.blob = m->d_blob;
+    p.n_sq = m->n_sq;
+    p.x = d_x;
+    p.y = d_y;
+    p.n = n;
+    p.lp = lp;
+    size_t smem = p.image_bytes;
+    const size_t min_smem = (size_t)(227 * 1024) / (size_t)(CPS + 1) + 1;   // never more than CPS CTAs (and their TMEM) per SM
+    if (smem < min_smem) smem = min_smem;
+    if (smem > 200 * 1024) return NSDF_EUNSUPPORTED;
+    NSDF_PER_DEVICE_FLAG(attr_done);
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(tc::mlp_tc6_kernel<MODE, G, CPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return (int)e;
+        attr_done = true;
+    }
+    const int sms = m->sm_count > 0 ? m->sm_count : 148;
+    const long long n_tiles = (n + 127) / 128;
+    const long long want = (n_tiles + 2 * G - 1) / (2 * G);
+    const long long cap = (long long)sms * CPS;
+    const int grid = (int)(want < cap ? want : cap);
+    tc::mlp_tc6_kernel<MODE, G, CPS><<<grid, G * 128, smem, stream>>>(p);
+    return (int)cudaGetLastError();
+}
+
+template <int MODE>
+int launch6_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
+                cudaStream_t stream) {
+    switch (cfg) {
+        case 0: return launch6<MODE, 5, 1>(m, t, d_x, d_y, n, lp, stream);   // ten tiles in flight per SM, 640 threads
+        case 1: return launch6<MODE, 2, 2>(m, t, d_x, d_y, n, lp, stream);   // eight, 512 threads
+        case 2: return launch6<MODE, 1, 4>(m, t, d_x, d_y, n, lp, stream);   // eight, 512 threads in four CTAs
+        case 3: return launch6<MODE, 4, 1>(m, t, d_x, d_y, n, lp, stream);   // eight, one CTA
+        default: return NSDF_EINVAL;
+    }
+}
+
+#endif
+
 template <int MODE>
 int launch5_cfg(int cfg, nsdf_model* m, const TcDeviceImages* t, const float* d_x, float* d_y, int64_t n, const LatticeParams& lp,
                 cudaStream_t stream) {
@@ -328,6 +373,13 @@ int tc_forward(nsdf_model* m, const float* d_x, float* d_y, int64_t n, int preci
             default: return NSDF_EINVAL;
         }
     }
+#ifdef NSDF_DEV_SCHEDULES
+    if (kernel == 6 && precision != NSDF_PREC_TC_FP16X3) {
+        const int cfg = env_int("NSDF_TC6_CFG", 0);
+        return precision == NSDF_PREC_TC_FP16 ? launch6_cfg<MODE_FP16>(cfg, m, t, d_x, d_y, n, lp, stream)
+                                              : launch6_cfg<MODE_BF16>(cfg, m, t, d_x, d_y, n, lp, stream);
+    }
+#endif
     if (kernel == 5 && precision != NSDF_PREC_TC_FP16X3) {
         const int cfg = env_int("NSDF_TC5_CFG", 2);
         return precision == NSDF_PREC_TC_FP16 ? launch5_cfg<MODE_FP16>(cfg, m, t, d_x, d_y, n, lp, stream)

@@ -173,5 +173,147 @@ __global__ void __launch_bounds__(G * 128, CPS) mlp_tc5_kernel(const __grid_cons
     if (warp == 0) tmem_dealloc(tmem, TMEM_COLS);
 }
 
+#ifdef NSDF_DEV_SCHEDULES
+// ---- schedule v6: v5 with TWO tile slots per warpgroup (ping-pong); development builds only: measured SLOWER than v5 ----------------
+// (fp16, 256^3: ten tiles with 640 threads 34.3 Gq/s, eight tiles with 512 threads 29.5-31.0; v5 41.6): the chain of a tile-layer is
+// mostly the warpgroup's own serial work -- barrier, tcgen05.ld, convert, tcgen05.st, fence, barrier, issue: ~560 clk -- not the UMMA
+// round trip, so halving the threads per tile in flight costs more than the overlap gains.
+// A tile needs four warps (one per TMEM lane quadrant), so ten tiles in flight cost v5 1280 threads and the two-pass epilogue.  Here a
+// warpgroup owns two 48-column slots and alternates between them: while the UMMAs of one slot are in flight (~400 clk round trip) it
+// runs the other slot's epilogue and issue.  G warpgroups x CPS CTAs per SM hold 2 * G * CPS tiles: 5 x 1 = ten tiles with 640 threads.
+// Arithmetic, weight image and results as v5 / v2.
+template <int MODE, int G, int CPS>
+__global__ void __launch_bounds__(G * 128, CPS) mlp_tc6_kernel(const __grid_constant__ Tc4Params p) {
+    static_assert(MODE != MODE_FP16X3, "v6 carries the 16-bit rungs only");
+    constexpr uint32_t SLOT = 48;
+    constexpr uint32_t ONES_COL = 2 * G * SLOT;
+    constexpr uint32_t TMEM_COLS = pow2_cols(ONES_COL + 8);
+    static_assert(TMEM_COLS * CPS <= 512, "TMEM over-subscribed");
+    constexpr int NTHREADS = G * 128;
+
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ uint64_t s_bar_w, s_bar_d[2 * G];
+    __shared__ uint32_t s_tmem;
+    __shared__ __align__(16) uint64_t s_desc[(FUSED_MAX_SQ + 2) * 8];
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int n_sq = p.n_sq;
+    if (tid == 0) {
+        mbar_init(&s_bar_w, 1);
+        for (int s = 0; s < 2 * G; ++s) mbar_init(&s_bar_d[s], 1);
+        mbar_fence_init();
+    }
+    tile_build_desc<MODE>(s_desc, smem_u32(smem), n_sq, tid, NTHREADS);
+    __syncthreads();
+    if (tid == 0) {
+        mbar_arrive_expect_tx(&s_bar_w, p.image_bytes);
+        uint32_t off = 0;
+        while (off < p.image_bytes) {
+            const uint32_t nb = (p.image_bytes - off) < 32768u ? (p.image_bytes - off) : 32768u;
+            tma_bulk_g2s(smem + off, p.image + off, nb, &s_bar_w);
+            off += nb;
+        }
+    }
+    __syncwarp();
+    if (warp == 0) tmem_alloc(&s_tmem, TMEM_COLS);
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = s_tmem;
+
+    const int g = warp >> 2, q = warp & 3;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    const uint32_t t_ones = tmem + ONES_COL;
+    if (g == 0) {          // the CTA's ones block: [1 1 0 ...] in every row, written once
+        const uint32_t r[8] = {ones_word<MODE>(), 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+        tmem_st8(t_ones + lane_off, r);
+        wait_st();
+    }
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    mbar_wait_guard(&s_bar_w, 0);
+
+    const int row_in_tile = q * 32 + lane;
+    constexpr uint32_t ID32 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 32);
+    constexpr uint32_t ID16 = make_idesc(MODE == MODE_BF16 ? 1 : 0, 128, 16);
+    uint32_t phase = 0;                 // bit s = parity of slot s's accumulator barrier
+
+    // issue of step `step` of slot s: the slot's issuing warp is warp s of the group, so the two slots' issues overlap
+    auto issue = [&](int s, int step) {
+        if (q == s) {
+            if (elect_one()) {
+                fence_after_sync();
+                const uint32_t t_grp = tmem + (uint32_t)(2 * g + s) * SLOT;
+                const uint64_t* d = s_desc + step * 8;
+                const uint32_t idesc = step > n_sq ? ID16 : ID32;
+                const uint32_t tD = t_grp + Cols3<MODE>::D;
+                mma_ts(tD, t_grp + Cols3<MODE>::A_HI, d[0], idesc, 0u);
+                if (step > 0) {
+                    mma_ts(tD, t_grp + Cols3<MODE>::A_HI + 8, d[1], idesc, 1u);
+                    mma_ts(tD, t_ones, d[2], idesc, 1u);
+                }
+                mma_commit_addr(smem_u32(&s_bar_d[2 * g + s]));
+            }
+            __syncwarp();
+        }
+    };
+
+    const long long n_tiles = (p.n + 127) >> 7;
+    const long long stride = (long long)gridDim.x * (2 * G);
+    for (long long tile0 = ((long long)blockIdx.x * G + g) * 2; tile0 < n_tiles; tile0 += stride) {
+        long long row[2];
+#pragma unroll
+        for (int s = 0; s < 2; ++s) {
+            row[s] = ((tile0 + s) << 7) + row_in_tile;       // a tile past the end computes on zeros and stores nothing
+            float x[3] = {0.0f, 0.0f, 0.0f};
+            if (row[s] < p.n) {
+                if (p.lp.enabled) lattice_point_fast(p.lp, p.lp.first + row[s], x);
+                else { x[0] = __ldg(p.x + 3 * row[s]); x[1] = __ldg(p.x + 3 * row[s] + 1); x[2] = __ldg(p.x + 3 * row[s] + 2); }
+            }
+            store_query3<MODE>(tmem + (uint32_t)(2 * g + s) * SLOT + lane_off, x);
+        }
+        wait_st();
+        fence_before_sync();
+        group_sync(g);
+        issue(0, 0);
+        issue(1, 0);
+#pragma unroll 1
+        for (int step = 0; step <= n_sq + 1; ++step) {
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+                const uint32_t t_slot = tmem + (uint32_t)(2 * g + s) * SLOT + lane_off;
+                if (q == s) mbar_wait_spin(smem_u32(&s_bar_d[2 * g + s]), (phase >> s) & 1u);     // the slot's issuing warp polls
+                group_sync(g);
+                phase ^= 1u << s;
+                fence_after_sync();
+                if (step <= n_sq) {
+                    uint32_t v[32];
+                    tmem_ld32(t_slot + Cols3<MODE>::D, v);
+                    wait_ld();
+                    uint32_t a[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) a[j] = pack2_relu<MODE>(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]));
+                    tmem_st16(t_slot + Cols3<MODE>::A_HI, a);
+                    wait_st();
+                    fence_before_sync();
+                    group_sync(g);
+                    issue(s, step + 1);
+                } else {
+                    const float y = __uint_as_float(tmem_ld1(t_slot + Cols3<MODE>::D));
+                    wait_ld();
+                    if (row[s] < p.n) p.y[row[s]] = y;
+                }
+            }
+        }
+    }
+
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem, TMEM_COLS);
+}
+
+#endif  // NSDF_DEV_SCHEDULES (v6)
+
 }  // namespace tc
 }  // namespace nsdf

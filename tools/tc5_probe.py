@@ -24,9 +24,15 @@ def run(prec, env):
 for name, prec in (("fp16", host.PREC_TC_FP16),):
     ref, best, mean = run(prec, {"NSDF_TC_KERNEL": 2})
     print(f"{name} v2            : {best:.2f} Gq/s best, {mean:.2f} mean", flush=True)
-    for cfg, label in ((0, "5 groups x 2 CTAs"), (1, "4 groups x 2 CTAs"), (2, "2 groups x 4 CTAs"), (3, "1 group  x 8 CTAs"), (4, "2 groups x 3 CTAs"), (5, "2 groups x 2 CTAs"), (6, "2 groups x 1 CTA "), (7, "1 group  x 4 CTAs")):
+    for cfg, label in ((0, "5 groups x 2 CTAs"), (1, "4 groups x 2 CTAs"), (2, "2 groups x 4 CTAs"), (3, "1 group  x 8 CTAs")):
         try:
             y, best, mean = run(prec, {"NSDF_TC_KERNEL": 5, "NSDF_TC5_CFG": cfg})
             print(f"{name} v5 {label}: {best:.2f} Gq/s best, {mean:.2f} mean, bits equal v2: {bool(torch.equal(y.view(torch.int32), ref.view(torch.int32)))}", flush=True)
         except Exception as e:
             print(f"{name} v5 {label}: failed: {e}", flush=True)
+    for cfg, label in ((0, "5 groups x 1 CTA, 10 tiles"), (1, "2 x 2, 8 tiles"), (2, "1 x 4, 8 tiles"), (3, "4 x 1, 8 tiles")):
+        try:
+            y, best, mean = run(prec, {"NSDF_TC_KERNEL": 6, "NSDF_TC6_CFG": cfg})
+            print(f"{name} v6 {label}: {best:.2f} Gq/s best, {mean:.2f} mean, bits equal v2: {bool(torch.equal(y.view(torch.int32), ref.view(torch.int32)))}", flush=True)
+        except Exception as e:
+            print(f"{name} v6 {label}: failed: {e}", flush=True)
