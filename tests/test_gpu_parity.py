@@ -842,4 +842,24 @@ def test_render_beside_a_busy_stream(env):
     torch.cuda.synchronize()
     for o in outs:
         assert torch.equal(o, alone)
+    # the throughput tracer (trace_bulk4_kernel) is a cooperative launch as well: a batch of views beside the busy stream
+    views = [(0.0, 30.0), (0.0, 75.0), (10.0, 200.0), (0.0, 300.0)]
+    cams = host.view_cameras(views)
+    host.setTuning(bulk4=1)
+    ref4 = torch.zeros(len(views) * W * H, dtype=torch.int32, device="cuda")
+    host.render_views(ref4, W, H, nn, cams)
+    torch.cuda.synchronize()
+    assert torch.equal(ref4[:W * H], alone)
+    outs = []
+    with torch.cuda.stream(side):
+        for _ in range(40):
+            a = (a @ a) * 1e-3
+    for _ in range(4):
+        o = torch.full_like(ref4, 0x55)
+        host.render_views(o, W, H, nn, cams)
+        outs.append(o)
+    torch.cuda.synchronize()
+    host.setTuning()
+    for o in outs:
+        assert torch.equal(o, ref4)
     host.setSceneOptions()
