@@ -666,6 +666,75 @@ def run_tiles(args):
     D.close()
 
 
+def run_turntable4k(args):
+    """--workload turntable4k: the 64-view turntable of the 4K model (BASELINE config 4's shape and size, config 5's view set), view v ->
+    rank v % N, a rank's views of a step in ONE nsdf_render_views call: 4K FRAMES spread over the GPUs by view (strong scaling; the
+    frame4k_tiles workload splits ONE 4K frame by tiles instead)."""
+    from cudaneuralrender_b200 import host, multigpu
+    D = Dist()
+    torch = D.torch
+    model, Wt, Ht = SHAPES[4], 3840, 2160
+    nn = host.NeuralNetwork()
+    assert nn.load(geom(model))
+    matcap = host.Image()
+    assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.setSceneOptions(host.SCENE_MANYSPHERE, args.max_steps, 0, 0, host.MATH_REFERENCE)
+    my_views = multigpu.views_of_rank(N_VIEWS, D.rank, D.world)
+    cams = host.view_cameras([(0.0, v * VIEW_STEP_DEG) for v in my_views])
+    out = torch.zeros(len(my_views) * Wt * Ht, dtype=torch.int32, device="cuda")
+    pinned = torch.empty(len(my_views) * Wt * Ht, dtype=torch.int32, pin_memory=True)
+    stats = torch.zeros(6, dtype=torch.int64, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    host.render_views(out, Wt, Ht, nn, cams, matcap, stats=stats)          # accounting pass (also a warm-up)
+    torch.cuda.synchronize()
+    q_set = D.reduce(float(stats[0].item()), "sum")
+    for _ in range(max(args.warmup - 1, 2)):
+        host.render_views(out, Wt, Ht, nn, cams, matcap)
+    sampler = ClockSampler(D.local)
+    if D.rank == 0:
+        sampler.start()
+    D.barrier()
+    ms = timed(torch, lambda: host.render_views(out, Wt, Ht, nn, cams, matcap), args.steps, flush)
+    D.barrier()
+    total_ms = D.reduce(sum(ms), "max")
+    min_ms = D.reduce(sum(ms), "min")
+    clocks = sampler.stop() if D.rank == 0 else None
+    # end to end: the rank's frames back in pinned host memory inside the timed region
+    D.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        host.render_views(out, Wt, Ht, nn, cams, matcap)
+        pinned.copy_(out, non_blocking=True)
+        torch.cuda.synchronize()
+    e2e_s = D.reduce(time.perf_counter() - t0, "max")
+    if D.rank == 0:
+        pk = peaks()
+        K = args.steps
+        ms_per_step = total_ms / K
+        achieved = q_set * FLOP_PER_QUERY / (ms_per_step * 1e-3) / 1e12 / D.world
+        top_kernel = "trace_bulk4_kernel" if len(my_views) >= 4 else "trace_coop_kernel"
+        line = {"metric": "4K frames/sec (3a3d4a90.obj, FD normals + matcap), 64-view turntable, views over the GPUs",
+                "value": N_VIEWS * K / (total_ms * 1e-3), "unit": "frames/s", "n_gpus": D.world, "steps": K, "warmup": args.warmup,
+                "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic",
+                "config": {"workload": f"{model}.h5 {Wt}x{Ht} sphere-traced frames, {N_VIEWS}-view turntable ry=k*{VIEW_STEP_DEG}deg per step, FD "
+                                       f"normals + matcap {MATCAP}, scene=manySphere (reference HEAD), max_steps={args.max_steps}",
+                           "parallelism": f"views{D.world}: view v -> rank v % {D.world}", "frames_per_step": N_VIEWS,
+                           "l2": "256 MiB memset between timed steps (outside the per-step events)"},
+                "ms_per_frame_per_gpu": ms_per_step * D.world / N_VIEWS, "queries_per_frame_mean": q_set / N_VIEWS,
+                "rank_time_min_over_max": min_ms / total_ms if total_ms else None,
+                "e2e": {"value": N_VIEWS * K / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": 128 * N_VIEWS,
+                        "d2h_bytes_per_step": Wt * Ht * 4 * N_VIEWS},
+                "gpu_launches": K,
+                "roofline": {"kernel": top_kernel, "bound": "tensor", "achieved": achieved, "peak": pk["tflops_burst"], "unit": "TFLOP/s",
+                             "frac": achieved / pk["tflops_burst"], "traffic": None, "peak_source": pk["source"],
+                             "frac_of_fp32_alu": achieved / FP32_ALU_TFLOPS},
+                "clocks": clocks}
+        print(json.dumps(line), flush=True)
+    D.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -683,7 +752,7 @@ def main():
     ap.add_argument("--cpu-port", action="store_true", help="--impl reference: time the CPU oracle port even if the reference's "
                                                             "CUDA build (oracle/_ref) is present")
     ap.add_argument("--no-ref-cuda", action="store_false", dest="ref_cuda")
-    ap.add_argument("--workload", default="turntable1080", choices=["turntable1080", "frame4k_tiles"],
+    ap.add_argument("--workload", default="turntable1080", choices=["turntable1080", "frame4k_tiles", "turntable4k"],
                     help="turntable1080: BASELINE config 2 over the fixed 64-view set (default).  frame4k_tiles: BASELINE config 4 "
                          "alone, ONE 3840x2160 frame tile-partitioned over the N GPUs (also a leg of every default line)")
     args = ap.parse_args()
@@ -693,6 +762,8 @@ def main():
         run_reference(args)
     elif args.workload == "frame4k_tiles":
         run_tiles(args)
+    elif args.workload == "turntable4k":
+        run_turntable4k(args)
     else:
         run_native(args)
 
