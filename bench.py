@@ -448,9 +448,10 @@ def run_native(args):
     d2h = W * H * 4 * N_VIEWS + 48 * world
     img_batch_view0 = frames[:W * H].cpu().numpy().view(np.uint32).reshape(H, W).copy() if rank == 0 else None
 
-    # ---- legs every N carries: C4 (one 4K frame, tile-partitioned) and C5 (64 views x 5 shapes)
+    # ---- legs every N carries: C4 (one 4K frame, tile-partitioned), C5 (64 views x 5 shapes) and the 4K turntable (4K frames by view)
     tiles = tiles_leg(D, args, host, multigpu, flush, max(3, min(K, 5))) if args.tiles else None
     c5 = turntable_c5_leg(D, args, host, flush, (512, 512)) if args.c5 else None
+    tt4k = turntable4k_leg(D, args, host, multigpu, flush) if args.tt4k else None
 
     if rank != 0:
         D.close()
@@ -634,9 +635,36 @@ def run_native(args):
         line["frame4k_tiles"] = tiles
     if c5:
         line["turntable_c5"] = c5
+    if tt4k:
+        line["turntable_4k"] = tt4k
     line.update(line_extra)
     print(json.dumps(line), flush=True)
     D.close()
+
+
+def turntable4k_leg(D, args, host, multigpu, flush):
+    """4K frames by view (the --workload turntable4k measurement as a leg of the default line): the 64-view turntable of the 4K model at
+    3840x2160, view v -> rank v % N, a rank's views in one nsdf_render_views call; one warm-up pass, one timed pass."""
+    torch = D.torch
+    model, Wt, Ht = SHAPES[4], 3840, 2160
+    nn = host.NeuralNetwork()
+    assert nn.load(geom(model))
+    matcap = host.Image()
+    assert matcap.loadPNG(os.path.join(ROOT, "data", "matcaps", MATCAP))
+    host.copyStaticSettings(host.COLOR_MATCAP, 3)
+    host.setSceneOptions(host.SCENE_MANYSPHERE, args.max_steps, 0, 0, host.MATH_REFERENCE)
+    my_views = multigpu.views_of_rank(N_VIEWS, D.rank, D.world)
+    cams = host.view_cameras([(0.0, v * VIEW_STEP_DEG) for v in my_views])
+    out = torch.zeros(len(my_views) * Wt * Ht, dtype=torch.int32, device="cuda")
+    host.render_views(out, Wt, Ht, nn, cams, matcap)
+    D.barrier()
+    ms = timed(torch, lambda: host.render_views(out, Wt, Ht, nn, cams, matcap), 1, flush)[0]
+    D.barrier()
+    total = D.reduce(ms, "max")
+    del out
+    return {"workload": f"{model}.h5 {Wt}x{Ht}, {N_VIEWS}-view turntable ry=k*{VIEW_STEP_DEG}deg, scene=manySphere (reference HEAD), view v -> rank v % "
+                        f"{D.world}, one nsdf_render_views call per rank", "frames": N_VIEWS, "ms_total": total,
+            "frames_per_s": N_VIEWS / (total * 1e-3), "ms_per_frame_per_gpu": total * D.world / N_VIEWS}
 
 
 def run_tiles(args):
@@ -749,6 +777,7 @@ def main():
     ap.add_argument("--no-c1", action="store_false", dest="c1")
     ap.add_argument("--no-c5", action="store_false", dest="c5")
     ap.add_argument("--no-tiles", action="store_false", dest="tiles")
+    ap.add_argument("--no-4k", action="store_false", dest="tt4k", help="skip the 4K turntable leg (4K frames by view)")
     ap.add_argument("--cpu-port", action="store_true", help="--impl reference: time the CPU oracle port even if the reference's "
                                                             "CUDA build (oracle/_ref) is present")
     ap.add_argument("--no-ref-cuda", action="store_false", dest="ref_cuda")
