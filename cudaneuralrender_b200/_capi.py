@@ -34,7 +34,7 @@ class Tuning(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("express_period", "express_steps", "express_warps", "express_old_steps", "express_old_mask",
                                        "express_from_bulk", "express_rays", "express_solo_steps", "tile_priority_steps",
                                        "tile_priority_min_jobs", "tail_lanes", "tail_push_max", "bulk4", "bulk4_evict_steps",
-                                       "bulk4_period", "bulk4_drain", "bulk4_refill_min", "bulk4_unroll")]
+                                       "bulk4_period", "bulk4_drain", "bulk4_refill_min", "bulk4_unroll", "max_ctas")]
 
 
 class RenderOpts(C.Structure):

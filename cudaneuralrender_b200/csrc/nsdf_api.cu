@@ -438,6 +438,7 @@ void nsdf_tuning_default(nsdf_tuning* t) {
     t->bulk4_drain = 16;
     t->bulk4_refill_min = 16;
     t->bulk4_unroll = 2;
+    t->max_ctas = 0;
 }
 
 int nsdf_scene_eval(const nsdf_scene_op* program, int n_ops, const float* d_xyz, const float* d_nsdf, int frame, int math,

@@ -741,7 +741,8 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
         rp.hybrid = T.bulk4_drain;
         rp.b4_refill_min = T.bulk4_refill_min;
         void* args[] = {&rp};
-        return (int)cudaLaunchCooperativeKernel(b4_kernel, dim3((unsigned int)sms), dim3(B4_THREADS), args, smem, stream);
+        const unsigned int b4_grid = (T.max_ctas > 0 && T.max_ctas < sms) ? (unsigned int)T.max_ctas : (unsigned int)sms;
+        return (int)cudaLaunchCooperativeKernel(b4_kernel, dim3(b4_grid), dim3(B4_THREADS), args, smem, stream);
     }
 
     // ---- one persistent, cooperative launch: one CTA per SM (trace_coop.cuh)
@@ -750,7 +751,8 @@ int render_launch(nsdf_model* m, const nsdf_camera* cams, int n_views, const uin
     if (e != cudaSuccess) return (int)e;
     if (occ < 1) return NSDF_EUNSUPPORTED;
     const unsigned int per_cta = (COOP_THREADS / 32) * COOP_R;
-    const unsigned int cap = (unsigned int)(sms * occ);
+    unsigned int cap = (unsigned int)(sms * occ);
+    if (T.max_ctas > 0 && (unsigned int)T.max_ctas < cap) cap = (unsigned int)T.max_ctas;
     const unsigned int want = (rp.total_idx + per_cta - 1) / per_cta;
     m->frame_seq = m->frame_seq + 1u ? m->frame_seq + 1u : 1u;
     rp.frame_seq = m->frame_seq;

@@ -228,6 +228,8 @@ typedef struct nsdf_tuning {
     int bulk4_refill_min;    /* ... a warp asks for new pixels once this many of its 128 slots are idle (16)                    */
     int bulk4_unroll;        /* ... k-unroll of the evaluator's inner loop: 1, 2 or 4 (2: the loop body must stay in the
                                 instruction cache next to the ray code)                                                          */
+    int max_ctas;            /* the persistent tracers launch at most this many CTAs (= SMs); 0 = all.  Several calls with a share of
+                                the SMs each, on different streams and model handles, run side by side: their tails overlap            */
 } nsdf_tuning;
 void nsdf_tuning_default(nsdf_tuning* t);
 /* 1 if this library was built with -DNSDF_DEV_SCHEDULES (libnsdf_dev.so: superseded A/B schedules, mixed-precision far field,

@@ -799,6 +799,37 @@ def test_throughput_tracer_for_many_views(env):
     host.copyStaticSettings(host.COLOR_FACING, 3)
 
 
+def test_calls_side_by_side_with_max_ctas(env):
+    """nsdf_tuning.max_ctas caps a call's persistent grid; calls of different model handles on different streams then run side by side
+    (both tracers are cooperative launches of their own grid) and write the bytes the calls write alone."""
+    torch, host = env["torch"], env["host"]
+    nets = [_load(env, n)[0] for n in ("plane_1", "car_1", "plane_2")]
+    W, H = 384, 320
+    host.copyStaticSettings(host.COLOR_FACING, 3)
+    host.setSceneOptions(host.SCENE_MANYSPHERE, 6000, 0, 0, host.MATH_REFERENCE)
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    for views, knobs in (([(0.0, 0.0), (0.0, 90.0)], {}), ([(0.0, 10.0 * k) for k in range(8)], dict(bulk4=1))):
+        cams = host.view_cameras(views)
+        n = len(views) * W * H
+        alone = [torch.zeros(n, dtype=torch.int32, device="cuda") for _ in nets]
+        host.setTuning(**knobs) if knobs else host.setTuning()
+        for nn, o in zip(nets, alone):
+            host.render_views(o, W, H, nn, cams)
+        torch.cuda.synchronize()
+        outs = [torch.full((n,), 0x55, dtype=torch.int32, device="cuda") for _ in nets]
+        streams = [torch.cuda.Stream() for _ in nets]
+        host.setTuning(max_ctas=sms // len(nets), **knobs)
+        for _ in range(3):
+            for nn, o, st in zip(nets, outs, streams):
+                with torch.cuda.stream(st):
+                    host.render_views(o, W, H, nn, cams)
+        torch.cuda.synchronize()
+        host.setTuning()
+        for o, a in zip(outs, alone):
+            assert torch.equal(o, a), (len(views), knobs)
+    host.setSceneOptions()
+
+
 def test_error_behaviour(env):
     torch, host = env["torch"], env["host"]
     from cudaneuralrender_b200 import _capi
