@@ -8,12 +8,14 @@
 // the evaluator that is FMA-bound on dense batches (mlp32_eval_thread_s<4>: one lane = FOUR rays x all 32 neurons, the
 // weights as warp-uniform LDS.128, 0.6 B per FFMA, 67.5 % of the FFMA pipe on the 256^3 sweep):
 //
-//   producer warps   128 ray slots per warp (4 per lane, their state in a warp-private shared-memory block), refilled from
-//                    the global job counter by ballot compaction.  A warp step costs ~40 us, so a ray that is still
-//                    marching after `b4_evict` steps -- and whatever is left when the pixels are gone and the warp has
-//                    thinned out -- goes to a ring queue in L2;
-//   consumer warps   (all warps of every `b4_period`-th CTA from the start, and every producer warp once it has drained)
-//                    pop rays from the ring and march them 16 / 8 / 4 / 2 / 1 at a time with the cooperative evaluators of
+//   producer warps   128 ray slots per warp (4 per lane, their state in a warp-private shared-memory block).  Idle slots are refilled
+//                    from the global job counter with ONE atomic per warp (prefix sum over the lanes' idle counts) once
+//                    `b4_refill_min` (16) of them are free.  Slot work runs in rolled loops over the four slot rows (one copy of
+//                    slot_start / slot_update in the instruction stream).  A warp step costs ~40 us whatever the occupancy, so a
+//                    warp that is out of pixels and down to `rp.hybrid` (16) rays hands them to a ring queue in L2; rays may also
+//                    leave after `evict_steps_hi` steps (off by default: with many views the tails hide anyway);
+//   consumer warps   (every producer warp once it has drained; optionally all warps of every `consumer_period`-th CTA from the
+//                    start) pop rays from the ring and march them 16 / 8 / 4 / 2 / 1 at a time with the cooperative evaluators of
 //                    trace_coop.cuh (a lone ray: ~1.3 us per dependent step).
 //
 // Per ray the arithmetic is slot_start / slot_update of render_kernels.cuh, whoever evaluates it: frames are bit-identical

@@ -113,6 +113,30 @@ def test_library_exports_every_declared_symbol(built):
     assert L.nsdf_error_string(10002).startswith(b"nsdf:")
 
 
+def test_ctypes_structs_mirror_the_header(built):
+    """The ctypes mirrors of nsdf_tuning / nsdf_render_opts / nsdf_render_stats (cudaneuralrender_b200/_capi.py) list the fields of
+    include/nsdf.h in the same order (all int-sized or pointer members: order and count fix the layout)."""
+    capi = _capi()
+    hdr = open(os.path.join(ROOT, "include", "nsdf.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+
+    def fields(name):
+        body = re.search(r"typedef struct " + name + r"\s*\{(.*?)\}\s*" + name + r"\s*;", hdr, flags=re.S).group(1)
+        out = []
+        for decl in body.split(";"):
+            decl = decl.strip()
+            if decl:
+                out.append(re.findall(r"([A-Za-z_][A-Za-z0-9_]*)\s*(?:\[[^\]]*\])?$", decl)[0])
+        return out
+
+    assert fields("nsdf_tuning") == [n for n, _ in capi.Tuning._fields_]
+    assert fields("nsdf_render_opts") == [n for n, _ in capi.RenderOpts._fields_]
+    assert fields("nsdf_render_stats") == [n for n, _ in capi.RenderStats._fields_]
+    t = capi.Tuning()
+    capi.lib().nsdf_tuning_default(C.byref(t))
+    assert t.max_ctas == 0 and t.bulk4 == -1 and t.express_steps == 160      # first, a middle and the last member land where C wrote them
+
+
 def test_product_h5_reader_matches_independent_reader(built):
     """libnsdf's C++ reader (include/nsdf_h5.hpp) vs oracle/h5mini.py, host only."""
     L = _capi().lib()
